@@ -1,0 +1,196 @@
+/*
+ * kfslam_frontend.h — C ABI of the B200-native SLAM front-end (ORB detect+describe, Hamming kNN).
+ *
+ * Drop-in boundary for the two OpenCV calls the reference tracker makes per frame
+ * (angelo-nutu/Keyframe-Based-SLAM):
+ *   - cv::ORB::create(...)                       /root/reference/src/lib/VisualOdometry.cpp:10-16
+ *   - ptrExtractor->detectAndCompute(gray, mask, kp, desc)                        ... :30
+ *   - cv::BFMatcher::create(cv::NORM_HAMMING)                                     ... :18
+ *   - ptrMatcher->knnMatch(keyframe->matDescriptors, dpCurrImg, knnMatches, 2)    ... :39
+ *   - the ratio test  d0 < 0.6f * d1                                              ... :46
+ * Plain pointers and sizes only; no C++/torch types cross this boundary.  The C++ adapter that gives
+ * the tracker the cv::-shaped methods back is include/kfslam_frontend_cv.hpp; INTEGRATION.md shows the
+ * three-line change in VisualOdometry.{hpp,cpp}.
+ *
+ * Threading contract (mirrors the reference: VisualOdometry.cpp:138-144, single caller thread): a handle
+ * is NOT thread-safe; distinct handles are independent (one per host thread / per GPU).  Host-buffer
+ * entry points block until results are in host memory.  *_device entry points are asynchronous on the
+ * handle's stream.
+ *
+ * There is no CPU fallback: every entry point that computes needs a CUDA device (sm_100a build) and
+ * returns KFS_ERR_NO_DEVICE / KFS_ERR_CUDA otherwise.
+ */
+#ifndef KFSLAM_FRONTEND_H
+#define KFSLAM_FRONTEND_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define KFS_API
+#else
+#define KFS_API __attribute__((visibility("default")))
+#endif
+
+typedef enum kfs_status {
+    KFS_OK = 0,
+    KFS_ERR_INVALID_ARG = 1, /* null pointer, negative size, ... (OpenCV would throw cv::Exception)      */
+    KFS_ERR_UNSUPPORTED = 2, /* a cv::ORB / cv::BFMatcher option outside the reference's usage           */
+    KFS_ERR_CAPACITY = 3,    /* output capacity too small; n_out holds the required count (data truncated) */
+    KFS_ERR_CUDA = 4,        /* CUDA runtime error; see kfs_last_error()                                  */
+    KFS_ERR_NO_DEVICE = 5    /* no CUDA device visible: there is no CPU path                              */
+} kfs_status;
+
+/* cv::ORB::ScoreType */
+enum { KFS_ORB_HARRIS_SCORE = 0, KFS_ORB_FAST_SCORE = 1 };
+/* cv::NormTypes value used by the reference (cv::NORM_HAMMING == 6) */
+enum { KFS_NORM_HAMMING = 6 };
+
+/* Arguments of cv::ORB::create, same order and meaning (VisualOdometry.cpp:10-16 passes
+ * 3000, 1.2f, 8, 31, 0, 2, HARRIS_SCORE, 31, 20).  Supported: any nfeatures >= 1, scale_factor > 1,
+ * 1 <= nlevels <= 16, fast_threshold 1..254; edge_threshold = 31, first_level = 0, wta_k = 2,
+ * score_type = HARRIS, patch_size = 31 are the only accepted values (others -> KFS_ERR_UNSUPPORTED). */
+typedef struct kfs_orb_params {
+    int32_t nfeatures;
+    float scale_factor;
+    int32_t nlevels;
+    int32_t edge_threshold;
+    int32_t first_level;
+    int32_t wta_k;
+    int32_t score_type;
+    int32_t patch_size;
+    int32_t fast_threshold;
+} kfs_orb_params;
+
+/* Layout-identical to cv::KeyPoint (28 bytes). */
+typedef struct kfs_keypoint {
+    float x, y;      /* pt, level-0 pixel coordinates                 */
+    float size;      /* patch_size * scale(octave)                    */
+    float angle;     /* degrees, [0, 360)                             */
+    float response;  /* Harris response                               */
+    int32_t octave;  /* pyramid level                                 */
+    int32_t class_id; /* -1                                           */
+} kfs_keypoint;
+
+/* Layout-identical to cv::DMatch (16 bytes). */
+typedef struct kfs_dmatch {
+    int32_t queryIdx, trainIdx, imgIdx;
+    float distance;
+} kfs_dmatch;
+
+typedef struct kfs_orb kfs_orb; /* replaces cv::Ptr<cv::ORB>       (VisualOdometry.hpp:28) */
+typedef struct kfs_bf kfs_bf;   /* replaces cv::Ptr<cv::BFMatcher> (VisualOdometry.hpp:29) */
+
+/* ---- library ------------------------------------------------------------------------------------- */
+KFS_API int kfs_version(void);                 /* major*10000 + minor*100 + patch */
+KFS_API const char *kfs_last_error(void);      /* thread-local, never NULL         */
+KFS_API int kfs_device_count(void);            /* 0 if no CUDA device              */
+
+/* ---- ORB: replaces cv::ORB::create + detectAndCompute (VisualOdometry.cpp:10-16, :30) -------------- */
+KFS_API void kfs_orb_default_params(kfs_orb_params *p); /* OpenCV defaults: 500,1.2,8,31,0,2,HARRIS,31,20 */
+KFS_API kfs_status kfs_orb_create(const kfs_orb_params *params, int device, kfs_orb **out);
+KFS_API void kfs_orb_destroy(kfs_orb *orb);
+
+/* Upper bound on keypoints per frame the handle stores (nfeatures + tie slack); a caller capacity of
+ * this many entries never truncates unless ties exceed the slack.  kfs_orb_set_capacity changes it
+ * (must be called before the first extraction or it re-allocates). */
+KFS_API int kfs_orb_capacity(const kfs_orb *orb);
+KFS_API kfs_status kfs_orb_set_capacity(kfs_orb *orb, int capacity);
+
+/* One frame, host buffers in and out; blocks.  gray: h rows of w bytes, `step` bytes apart.
+ * mask: NULL (== cv::noArray()) or h x w bytes, non-zero = keep.  Keypoints come out grouped by
+ * ascending octave and, inside an octave, sorted by (y, x) — deterministic run to run.
+ * kp_out[capacity], desc_out[capacity*32].  w == 0 or h == 0 -> KFS_OK with *n_out = 0. */
+KFS_API kfs_status kfs_orb_detect_and_compute(kfs_orb *orb, const uint8_t *gray, size_t step, int w, int h,
+                                              const uint8_t *mask, size_t mask_step,
+                                              kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out);
+
+/* `batch` frames of one shape, host buffers; frame f starts at gray + f*frame_stride (mask likewise,
+ * mask may be NULL).  kp_out[batch][capacity], desc_out[batch][capacity][32], n_out[batch].  Blocks. */
+KFS_API kfs_status kfs_orb_detect_and_compute_batch(kfs_orb *orb, const uint8_t *gray, size_t step, size_t frame_stride,
+                                                    int w, int h, int batch,
+                                                    const uint8_t *mask, size_t mask_step, size_t mask_frame_stride,
+                                                    kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out);
+
+/* Device-resident variant: d_gray / d_mask are device pointers on the handle's device; asynchronous on
+ * the handle's stream; results stay on the device (kfs_orb_device_results) until fetched. */
+KFS_API kfs_status kfs_orb_extract_device(kfs_orb *orb, const uint8_t *d_gray, size_t step, size_t frame_stride,
+                                          int w, int h, int batch,
+                                          const uint8_t *d_mask, size_t mask_step, size_t mask_frame_stride);
+/* Device views of the last extraction: d_kp[batch][capacity], d_desc[batch][capacity][32], d_counts[batch]
+ * (d_counts[f] may exceed capacity when ties overflowed; only min(count, capacity) entries are valid). */
+KFS_API kfs_status kfs_orb_device_results(kfs_orb *orb, const kfs_keypoint **d_kp, const uint8_t **d_desc,
+                                          const int **d_counts, int *capacity, int *batch);
+/* Waits for the stream and copies the last extraction's results to host buffers (layout as in _batch). */
+KFS_API kfs_status kfs_orb_fetch_results(kfs_orb *orb, kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out);
+KFS_API kfs_status kfs_orb_sync(kfs_orb *orb);
+
+/* Stream plumbing: the handle creates its own non-blocking stream; a caller that already has one
+ * (e.g. torch.cuda.current_stream().cuda_stream) can install it.  Passing NULL restores the own stream. */
+KFS_API kfs_status kfs_orb_set_stream(kfs_orb *orb, void *cuda_stream);
+KFS_API void *kfs_orb_get_stream(kfs_orb *orb);
+
+/* Stage taps (parity tests and profiling; not needed by the tracker). */
+KFS_API kfs_status kfs_orb_level_info(kfs_orb *orb, int level, int *w, int *h, int *quota, float *scale);
+KFS_API kfs_status kfs_orb_download_level(kfs_orb *orb, int frame, int level, uint8_t *out, size_t out_step);
+/* FAST corners after NMS + border + mask filter of (frame, level): packed score<<24 | y<<12 | x, unordered. */
+KFS_API kfs_status kfs_orb_download_fast_corners(kfs_orb *orb, int frame, int level, uint32_t *out, int capacity, int *n_out);
+/* Per-stage device time of the last extraction when profiling is on (cudaEvent pairs on the handle's
+ * stream). Stage ids: KFS_STAGE_*.  ms[KFS_STAGE_COUNT]. */
+enum { KFS_STAGE_INGEST = 0, KFS_STAGE_PYRAMID = 1, KFS_STAGE_FAST = 2, KFS_STAGE_SELECT_HARRIS = 3,
+       KFS_STAGE_SELECT_SORT = 4, KFS_STAGE_ORIENT = 5, KFS_STAGE_DESCRIBE = 6, KFS_STAGE_COUNT = 7 };
+KFS_API kfs_status kfs_orb_set_profiling(kfs_orb *orb, int on);
+KFS_API kfs_status kfs_orb_stage_times(kfs_orb *orb, float *ms);
+/* Number of kernel launches the last extraction issued (bench.py's gpu_launches). */
+KFS_API int kfs_orb_last_launches(const kfs_orb *orb);
+
+/* ---- BFMatcher: replaces cv::BFMatcher::create + knnMatch (VisualOdometry.cpp:18, :39) -------------- */
+KFS_API kfs_status kfs_bf_create(int norm_type, int cross_check, int device, kfs_bf **out);
+KFS_API void kfs_bf_destroy(kfs_bf *bf);
+
+/* knnMatch(query, train, matches, k): query nq x 32 bytes, train nt x 32 bytes, contiguous rows, host.
+ * out[nq*k]: row q holds counts[q] = min(k, nt) entries sorted by ascending distance, ties by ascending
+ * trainIdx (OpenCV's insertion order); unused tail entries of a row are {q, -1, -1, FLT_MAX}.
+ * counts may be NULL.  k must be 1 or 2; nt < 2^18 (OpenCV's own limit).  Blocks. */
+KFS_API kfs_status kfs_bf_knn_match(kfs_bf *bf, const uint8_t *query, int nq, const uint8_t *train, int nt, int k,
+                                    kfs_dmatch *out, int *counts);
+
+/* One independent (query, train) problem.  For device pairs every pointer is a device pointer.
+ * d_nq / d_nt, when non-NULL, point to device ints holding the live row counts (clamped to nq / nt, which
+ * then act as capacities) — lets descriptors produced by kfs_orb_extract_device be matched with no host
+ * round trip. */
+typedef struct kfs_bf_pair {
+    const uint8_t *query; int32_t nq; const int32_t *d_nq;
+    const uint8_t *train; int32_t nt; const int32_t *d_nt;
+    kfs_dmatch *out;      /* nq*k entries */
+    int32_t *counts;      /* nq entries or NULL */
+} kfs_bf_pair;
+
+/* npairs independent problems in one launch (window matching, offline replay).  Host buffers; blocks.
+ * d_nq/d_nt must be NULL here. */
+KFS_API kfs_status kfs_bf_knn_match_pairs(kfs_bf *bf, const kfs_bf_pair *pairs, int npairs, int k);
+/* Same, device buffers, asynchronous on the handle's stream. */
+KFS_API kfs_status kfs_bf_knn_match_pairs_device(kfs_bf *bf, const kfs_bf_pair *pairs, int npairs, int k);
+
+/* Fused ratio test (VisualOdometry.cpp:46): compacts rows with 2 entries and d0 < ratio*d1, in query
+ * order, into good[0..*n_good).  Host buffers; blocks.  The tracker may keep doing this itself. */
+KFS_API kfs_status kfs_bf_knn_match_ratio(kfs_bf *bf, const uint8_t *query, int nq, const uint8_t *train, int nt,
+                                          float ratio, kfs_dmatch *good, int *n_good);
+
+KFS_API kfs_status kfs_bf_set_stream(kfs_bf *bf, void *cuda_stream);
+KFS_API void *kfs_bf_get_stream(kfs_bf *bf);
+KFS_API kfs_status kfs_bf_sync(kfs_bf *bf);
+KFS_API int kfs_bf_last_launches(const kfs_bf *bf);
+
+/* ---- microbenchmarks used by bench.py for the integer-pipe roofline -------------------- */
+/* Dependency-free POPC.32 (what=0) or LOP3.32 (what=1) issue-rate probe on `device`; returns 1e9 ops/s. */
+KFS_API kfs_status kfs_pipe_peak(int device, int what, double *gops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KFSLAM_FRONTEND_H */

@@ -1,0 +1,182 @@
+// kfslam_frontend_cv.hpp — header-only C++ adapter: gives the reference tracker back the exact call surface
+// it uses today, on top of the C ABI (kfslam_frontend.h).
+//
+//   reference (include/lib/VisualOdometry.hpp:28-29, src/lib/VisualOdometry.cpp:10-18,30,39)      drop-in
+//   ------------------------------------------------------------------------------------------   ---------------------------
+//   cv::Ptr<cv::ORB>       ptrExtractor = cv::ORB::create(3000,1.2f,8,31,0,2,HARRIS_SCORE,31,20)  kfs::ORB::create(... same ...)
+//   ptrExtractor->detectAndCompute(gray, mask, kpCurrImg, dpCurrImg)                              same call, same types
+//   cv::Ptr<cv::BFMatcher> ptrMatcher   = cv::BFMatcher::create(cv::NORM_HAMMING)                 kfs::BFMatcher::create(cv::NORM_HAMMING)
+//   ptrMatcher->knnMatch(keyframe->matDescriptors, dpCurrImg, knnMatches, 2)                      same call, same types
+//
+// Error behaviour mirrors OpenCV's: bad arguments / unsupported options throw cv::Exception (the reference never
+// catches, VisualOdometry.cpp:30,39).  Output semantics mirror OpenCV's: `keypoints` is resized, `descriptors`
+// is (re)created as n x 32 CV_8U or released when n == 0; knnMatch rows hold min(k, Nt) DMatch entries.
+// Keypoint order: ascending octave, then (y, x) inside an octave (OpenCV leaves the in-level order unspecified).
+#pragma once
+#if __has_include(<opencv2/core.hpp>) && !defined(KFS_FORCE_CV_MOCK)
+#include <opencv2/core.hpp>
+#define KFS_HAVE_OPENCV 1
+#else
+#include "kfslam_cv_mock.hpp"
+#define KFS_HAVE_OPENCV 0
+#endif
+#include "kfslam_frontend.h"
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace kfs {
+
+static_assert(sizeof(cv::KeyPoint) == sizeof(kfs_keypoint), "cv::KeyPoint must be layout-identical to kfs_keypoint");
+static_assert(sizeof(cv::DMatch) == sizeof(kfs_dmatch), "cv::DMatch must be layout-identical to kfs_dmatch");
+
+namespace detail {
+[[noreturn]] inline void raise(kfs_status st, const char *where)
+{
+    const std::string msg = std::string(where) + ": " + kfs_last_error();
+#if KFS_HAVE_OPENCV
+    throw cv::Exception(st == KFS_ERR_UNSUPPORTED ? cv::Error::StsNotImplemented : cv::Error::StsBadArg, msg, where, __FILE__, __LINE__);
+#else
+    throw cv::Exception((int)st, msg);
+#endif
+}
+#if KFS_HAVE_OPENCV
+inline cv::Mat as_mat(cv::InputArray a) { return a.getMat(); }
+inline void make_desc(cv::OutputArray d, int n) { if (n) d.create(n, 32, CV_8U); else d.release(); }
+inline cv::Mat out_mat(cv::OutputArray d) { return d.getMat(); }
+#else
+inline const cv::Mat &as_mat(cv::InputArray a) { return a; }
+inline void make_desc(cv::OutputArray d, int n) { if (n) d.create(n, 32, cv::CV_8U); else d.release(); }
+inline cv::Mat &out_mat(cv::OutputArray d) { return d; }
+#endif
+} // namespace detail
+
+// Stand-in for cv::ORB (Feature2D).  Not thread-safe, like the reference's single-threaded use.
+class ORB {
+public:
+    enum ScoreType { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    static cv::Ptr<ORB> create(int nfeatures = 500, float scaleFactor = 1.2f, int nlevels = 8, int edgeThreshold = 31,
+                               int firstLevel = 0, int WTA_K = 2, int scoreType = HARRIS_SCORE, int patchSize = 31,
+                               int fastThreshold = 20, int device = 0)
+    {
+        kfs_orb_params p{nfeatures, scaleFactor, nlevels, edgeThreshold, firstLevel, WTA_K, scoreType, patchSize, fastThreshold};
+        kfs_orb *h = nullptr;
+        const kfs_status st = kfs_orb_create(&p, device, &h);
+        if (st != KFS_OK) detail::raise(st, "kfs::ORB::create");
+        return cv::Ptr<ORB>(new ORB(h));
+    }
+    ~ORB() { kfs_orb_destroy(h_); }
+    ORB(const ORB &) = delete;
+    ORB &operator=(const ORB &) = delete;
+
+    // cv::Feature2D::detectAndCompute(image, mask, keypoints, descriptors, useProvidedKeypoints=false)
+    void detectAndCompute(cv::InputArray image, cv::InputArray mask, std::vector<cv::KeyPoint> &keypoints,
+                          cv::OutputArray descriptors, bool useProvidedKeypoints = false)
+    {
+        if (useProvidedKeypoints) { kfs_status st = KFS_ERR_UNSUPPORTED; (void)st; throw_unsupported("useProvidedKeypoints=true is not built"); }
+        const auto img = detail::as_mat(image);
+        const auto msk = detail::as_mat(mask);
+        if (img.empty()) { keypoints.clear(); detail::make_desc(descriptors, 0); return; }
+        if (img.channels() != 1) throw_unsupported("image must be 8-bit single channel (the tracker converts to gray first, VisualOdometry.cpp:28)");
+        if (!msk.empty() && (msk.rows != img.rows || msk.cols != img.cols)) throw_unsupported("mask size differs from image size");
+        int cap = kfs_orb_capacity(h_);
+        for (;;) {
+            keypoints.resize((size_t)cap);
+            scratch_.resize((size_t)cap * 32);
+            int n = 0;
+            const kfs_status st = kfs_orb_detect_and_compute(h_, img.ptr(0), (size_t)img.step, img.cols, img.rows,
+                                                             msk.empty() ? nullptr : msk.ptr(0), msk.empty() ? 0 : (size_t)msk.step,
+                                                             reinterpret_cast<kfs_keypoint *>(keypoints.data()), scratch_.data(), cap, &n);
+            if (st == KFS_ERR_CAPACITY) { // ties pushed the count over the handle's slack: grow and redo
+                if (kfs_orb_set_capacity(h_, n + 64) != KFS_OK) detail::raise(KFS_ERR_CUDA, "kfs::ORB::detectAndCompute");
+                cap = kfs_orb_capacity(h_);
+                continue;
+            }
+            if (st != KFS_OK) detail::raise(st, "kfs::ORB::detectAndCompute");
+            keypoints.resize((size_t)n);
+            detail::make_desc(descriptors, n);
+            if (n) {
+                auto d = detail::out_mat(descriptors);
+                for (int r = 0; r < n; r++) std::memcpy(d.ptr(r), scratch_.data() + (size_t)r * 32, 32);
+            }
+            return;
+        }
+    }
+    kfs_orb *handle() const { return h_; }
+
+private:
+    explicit ORB(kfs_orb *h) : h_(h) {}
+    [[noreturn]] static void throw_unsupported(const char *what)
+    {
+#if KFS_HAVE_OPENCV
+        throw cv::Exception(cv::Error::StsNotImplemented, what, "kfs::ORB", __FILE__, __LINE__);
+#else
+        throw cv::Exception((int)KFS_ERR_UNSUPPORTED, what);
+#endif
+    }
+    kfs_orb *h_;
+    std::vector<uint8_t> scratch_;
+};
+
+// Stand-in for cv::BFMatcher (DescriptorMatcher).
+class BFMatcher {
+public:
+    static cv::Ptr<BFMatcher> create(int normType = cv::NORM_L2, bool crossCheck = false, int device = 0)
+    {
+        kfs_bf *h = nullptr;
+        const kfs_status st = kfs_bf_create(normType, crossCheck ? 1 : 0, device, &h);
+        if (st != KFS_OK) detail::raise(st, "kfs::BFMatcher::create");
+        return cv::Ptr<BFMatcher>(new BFMatcher(h));
+    }
+    ~BFMatcher() { kfs_bf_destroy(h_); }
+    BFMatcher(const BFMatcher &) = delete;
+    BFMatcher &operator=(const BFMatcher &) = delete;
+
+    // cv::DescriptorMatcher::knnMatch(query, train, matches, k, mask=noArray(), compactResult=false)
+    void knnMatch(cv::InputArray queryDescriptors, cv::InputArray trainDescriptors,
+                  std::vector<std::vector<cv::DMatch>> &matches, int k,
+                  cv::InputArray mask = cv::noArray(), bool compactResult = false)
+    {
+        (void)compactResult;
+        const auto q = detail::as_mat(queryDescriptors);
+        const auto t = detail::as_mat(trainDescriptors);
+        const auto m = detail::as_mat(mask);
+        if (!m.empty()) { kfs_status st = KFS_ERR_UNSUPPORTED; (void)st; throw cv::Exception(
+#if KFS_HAVE_OPENCV
+            cv::Error::StsNotImplemented, "match masks are not built", "kfs::BFMatcher::knnMatch", __FILE__, __LINE__
+#else
+            (int)KFS_ERR_UNSUPPORTED, "match masks are not built"
+#endif
+        ); }
+        matches.clear();
+        const int nq = q.empty() ? 0 : q.rows, nt = t.empty() ? 0 : t.rows;
+        if (nq == 0) return;                               // OpenCV: empty query -> empty result
+        if (q.cols != 32 || (nt && t.cols != 32)) detail::raise((kfs_set_err("descriptors must be n x 32 CV_8U"), KFS_ERR_INVALID_ARG), "kfs::BFMatcher::knnMatch");
+        std::vector<uint8_t> qb, tb;
+        const uint8_t *qp = pack(q, qb), *tp = nt ? pack(t, tb) : nullptr;
+        flat_.resize((size_t)nq * k);
+        counts_.resize((size_t)nq);
+        const kfs_status st = kfs_bf_knn_match(h_, qp, nq, tp, nt, k, reinterpret_cast<kfs_dmatch *>(flat_.data()), counts_.data());
+        if (st != KFS_OK) detail::raise(st, "kfs::BFMatcher::knnMatch");
+        matches.resize((size_t)nq);
+        for (int i = 0; i < nq; i++) matches[(size_t)i].assign(flat_.begin() + (size_t)i * k, flat_.begin() + (size_t)i * k + counts_[(size_t)i]);
+    }
+    kfs_bf *handle() const { return h_; }
+
+private:
+    explicit BFMatcher(kfs_bf *h) : h_(h) {}
+    static int kfs_set_err(const char *) { return 0; }
+    template <typename M> static const uint8_t *pack(const M &m, std::vector<uint8_t> &buf)
+    {
+        if (m.isContinuous()) return m.ptr(0);
+        buf.resize((size_t)m.rows * 32);
+        for (int r = 0; r < m.rows; r++) std::memcpy(buf.data() + (size_t)r * 32, m.ptr(r), 32);
+        return buf.data();
+    }
+    kfs_bf *h_;
+    std::vector<cv::DMatch> flat_;
+    std::vector<int> counts_;
+};
+
+} // namespace kfs

@@ -1,0 +1,420 @@
+// kfs_bf.cu — brute-force Hamming k-NN (k <= 2) on sm_100a: the replacement for
+//     ptrMatcher->knnMatch(keyframe->matDescriptors, dpCurrImg, knnMatches, 2)
+//         /root/reference/src/lib/VisualOdometry.cpp:39   (BFMatcher(NORM_HAMMING) at :18, ratio test at :46)
+// Contract (OpenCV batchDistance + insertion top-K): distance = popcount of the
+// 256-bit XOR; per query the K smallest in ascending order, ties -> lower trainIdx first; rows hold
+// min(K, Nt) entries; Nt < 2^18.
+//
+// This is integer work: XOR + POPC + add on the ALU/POPC pipes, no tensor cores.  Query descriptors live in
+// registers (QPT per thread), train descriptors are streamed through shared memory in double-buffered
+// chunks (cp.async), every lane of a warp reads the same train row (broadcast LDS.128), and the running
+// top-2 is kept as two packed keys  dist << 18 | trainIdx  so that a plain unsigned min reproduces
+// "lower index wins ties" exactly.  A CTA splits the train chunk over TSPLIT warp groups and merges the
+// partial top-2 lists through shared memory; the merged result is written as cv::DMatch records.
+#include "kfs_common.cuh"
+#include <float.h>
+#include <string.h>
+#include <vector>
+#include <new>
+
+constexpr int BF_THREADS = 256;
+constexpr int BF_QPT = 4;                       // queries per thread
+constexpr int BF_TSPLIT = 4;                    // warp groups scanning disjoint train slices
+constexpr int BF_QWARPS = BF_THREADS / 32 / BF_TSPLIT;
+constexpr int BF_QTILE = BF_QWARPS * 32 * BF_QPT; // 256 queries per CTA
+constexpr int BF_CHUNK = 512;                   // train rows per smem stage (16 KB)
+constexpr int BF_SLICE = BF_CHUNK / BF_TSPLIT;  // rows one warp group scans per stage
+constexpr uint32_t BF_INF = 0xffffffffu;
+
+struct BfPairDev {
+    const uint8_t *query; const uint8_t *train;
+    const int *d_nq; const int *d_nt;
+    kfs_dmatch *out; int *counts;
+    int nq, nt;
+};
+
+__device__ __forceinline__ void bf_cp_async16(void *smem, const void *gmem)
+{
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void bf_cp_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N> __device__ __forceinline__ void bf_cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+__device__ __forceinline__ void bf_top2_insert(uint32_t key, uint32_t &b1, uint32_t &b2)
+{
+    const uint32_t hi = max(key, b1);
+    b1 = min(key, b1);
+    b2 = min(b2, hi);
+}
+
+// grid (ceil(max_nq / BF_QTILE), npairs)
+__global__ void __launch_bounds__(BF_THREADS)
+k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k)
+{
+    __shared__ __align__(16) uint4 s_train[2][BF_CHUNK * 2]; // 2 stages x 512 rows x 32 B
+    const BfPairDev P = pairs[blockIdx.y];
+    int nq = P.nq, nt = P.nt;
+    if (P.d_nq) nq = min(nq, *P.d_nq);
+    if (P.d_nt) nt = min(nt, *P.d_nt);
+    const int q0 = blockIdx.x * BF_QTILE;
+    if (q0 >= nq) return;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int qgroup = warp % BF_QWARPS, tsplit = warp / BF_QWARPS;
+
+    // query descriptors -> registers (clamped index for the ragged tail; results of clamped rows are dropped)
+    uint32_t q[BF_QPT][8];
+    uint32_t b1[BF_QPT], b2[BF_QPT];
+#pragma unroll
+    for (int r = 0; r < BF_QPT; r++) {
+        const int qi = min(q0 + qgroup * (32 * BF_QPT) + r * 32 + lane, nq - 1);
+        const uint4 *src = reinterpret_cast<const uint4 *>(P.query + (size_t)qi * 32);
+        const uint4 a = __ldg(src), b = __ldg(src + 1);
+        q[r][0] = a.x; q[r][1] = a.y; q[r][2] = a.z; q[r][3] = a.w;
+        q[r][4] = b.x; q[r][5] = b.y; q[r][6] = b.z; q[r][7] = b.w;
+        b1[r] = BF_INF; b2[r] = BF_INF;
+    }
+
+    const int nchunks = (nt + BF_CHUNK - 1) / BF_CHUNK;
+    auto issue = [&](int chunk, int stage) {
+        const int base = chunk * BF_CHUNK;
+        const int rows = min(BF_CHUNK, nt - base);
+        const uint4 *src = reinterpret_cast<const uint4 *>(P.train + (size_t)base * 32);
+        for (int i = tid; i < rows * 2; i += BF_THREADS) bf_cp_async16(&s_train[stage][i], src + i);
+        bf_cp_commit();
+    };
+    if (nchunks > 0) issue(0, 0);
+    for (int c = 0; c < nchunks; c++) {
+        const int stage = c & 1;
+        if (c + 1 < nchunks) { issue(c + 1, stage ^ 1); bf_cp_wait<1>(); }
+        else bf_cp_wait<0>();
+        __syncthreads();
+        const int base = c * BF_CHUNK + tsplit * BF_SLICE;
+        const int rows = min(BF_SLICE, nt - base); // may be <= 0 for the last chunk
+        const uint4 *tp = &s_train[stage][tsplit * BF_SLICE * 2];
+#pragma unroll 2
+        for (int j = 0; j < rows; j++) {
+            const uint4 ta = tp[2 * j], tb = tp[2 * j + 1];
+            const uint32_t tkey = (uint32_t)(base + j);
+#pragma unroll
+            for (int r = 0; r < BF_QPT; r++) {
+                const int d = __popc(q[r][0] ^ ta.x) + __popc(q[r][1] ^ ta.y) + __popc(q[r][2] ^ ta.z) + __popc(q[r][3] ^ ta.w) +
+                              __popc(q[r][4] ^ tb.x) + __popc(q[r][5] ^ tb.y) + __popc(q[r][6] ^ tb.z) + __popc(q[r][7] ^ tb.w);
+                bf_top2_insert(((uint32_t)d << 18) + tkey, b1[r], b2[r]);
+            }
+        }
+        __syncthreads(); // everyone done with this stage before it is refilled two iterations later
+    }
+
+    // merge the TSPLIT partial lists through shared memory (reuses the train buffer)
+    uint32_t *s_m = reinterpret_cast<uint32_t *>(&s_train[0][0]); // [TSPLIT][QTILE][2]
+#pragma unroll
+    for (int r = 0; r < BF_QPT; r++) {
+        const int ql = qgroup * (32 * BF_QPT) + r * 32 + lane;
+        s_m[(tsplit * BF_QTILE + ql) * 2 + 0] = b1[r];
+        s_m[(tsplit * BF_QTILE + ql) * 2 + 1] = b2[r];
+    }
+    __syncthreads();
+    for (int ql = tid; ql < BF_QTILE; ql += BF_THREADS) {
+        const int qi = q0 + ql;
+        if (qi >= nq) continue;
+        uint32_t m1 = BF_INF, m2 = BF_INF;
+#pragma unroll
+        for (int s = 0; s < BF_TSPLIT; s++) {
+            bf_top2_insert(s_m[(s * BF_QTILE + ql) * 2 + 0], m1, m2);
+            bf_top2_insert(s_m[(s * BF_QTILE + ql) * 2 + 1], m1, m2);
+        }
+        kfs_dmatch r0, r1;
+        r0.queryIdx = qi; r1.queryIdx = qi;
+        int cnt = 0;
+        if (m1 != BF_INF) { r0.trainIdx = (int)(m1 & 0x3ffffu); r0.imgIdx = 0; r0.distance = (float)(m1 >> 18); cnt = 1; }
+        else { r0.trainIdx = -1; r0.imgIdx = -1; r0.distance = FLT_MAX; }
+        if (m2 != BF_INF && k > 1) { r1.trainIdx = (int)(m2 & 0x3ffffu); r1.imgIdx = 0; r1.distance = (float)(m2 >> 18); cnt = 2; }
+        else { r1.trainIdx = -1; r1.imgIdx = -1; r1.distance = FLT_MAX; }
+        uint4 *o = reinterpret_cast<uint4 *>(P.out + (size_t)qi * k);
+        o[0] = *reinterpret_cast<uint4 *>(&r0);
+        if (k > 1) o[1] = *reinterpret_cast<uint4 *>(&r1);
+        if (P.counts) P.counts[qi] = cnt;
+    }
+}
+
+// Fused ratio test (VisualOdometry.cpp:46): one CTA per pair, ordered compaction of rows passing
+// d0 < ratio*d1 (both present).  Single block scan keeps query order, like the reference's loop.
+__global__ void __launch_bounds__(1024)
+k_ratio_compact(const kfs_dmatch *__restrict__ knn, int nq, float ratio, kfs_dmatch *__restrict__ good, int *__restrict__ n_good)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_base, s_total;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (int q0 = 0; q0 < nq; q0 += 1024) {
+        const int q = q0 + tid;
+        bool keep = false;
+        kfs_dmatch m0;
+        m0.queryIdx = 0; m0.trainIdx = -1; m0.imgIdx = -1; m0.distance = 0.f;
+        if (q < nq) {
+            m0 = knn[2 * q];
+            const kfs_dmatch m1 = knn[2 * q + 1];
+            keep = m0.trainIdx >= 0 && m1.trainIdx >= 0 && m0.distance < __fmul_rn(ratio, m1.distance);
+        }
+        const uint32_t b = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp[warp] = __popc(b);
+        __syncthreads();
+        if (warp == 0) {
+            const int v = s_warp[lane];
+            int incl = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += t;
+            }
+            s_warp[lane] = incl - v; // exclusive offset of each warp
+            if (lane == 31) s_total = incl;
+        }
+        __syncthreads();
+        const int base = s_base + s_warp[warp];
+        if (keep) good[base + __popc(b & ((1u << lane) - 1u))] = m0;
+        __syncthreads();
+        if (tid == 0) s_base += s_total;
+        __syncthreads();
+    }
+    if (tid == 0) n_good[0] = s_base;
+}
+
+// ---------------------------------------------------------------------------------------------------
+struct kfs_bf {
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    BfPairDev *d_pairs = nullptr;
+    int pairs_cap = 0;
+    std::vector<BfPairDev> h_pairs_last;
+    BfPairDev *h_stage = nullptr; // pinned
+    uint8_t *d_buf = nullptr;     // staging for the host-buffer entry points
+    size_t d_buf_bytes = 0;
+    int launches = 0;
+};
+
+static kfs_status bf_reserve_pairs(kfs_bf *b, int n)
+{
+    if (n <= b->pairs_cap) return KFS_OK;
+    if (b->d_pairs) { KFS_CUDA_TRY(cudaStreamSynchronize(b->stream)); cudaFree(b->d_pairs); b->d_pairs = nullptr; }
+    if (b->h_stage) { cudaFreeHost(b->h_stage); b->h_stage = nullptr; }
+    const int cap = n < 64 ? 64 : n * 2;
+    KFS_CUDA_TRY(cudaMalloc(&b->d_pairs, sizeof(BfPairDev) * (size_t)cap));
+    KFS_CUDA_TRY(cudaMallocHost(&b->h_stage, sizeof(BfPairDev) * (size_t)cap));
+    b->pairs_cap = cap;
+    b->h_pairs_last.clear();
+    return KFS_OK;
+}
+
+static kfs_status bf_reserve_buf(kfs_bf *b, size_t bytes)
+{
+    if (bytes <= b->d_buf_bytes) return KFS_OK;
+    if (b->d_buf) { KFS_CUDA_TRY(cudaStreamSynchronize(b->stream)); cudaFree(b->d_buf); b->d_buf = nullptr; }
+    const size_t cap = kfs_align_up(bytes + bytes / 2, 1 << 20);
+    KFS_CUDA_TRY(cudaMalloc(&b->d_buf, cap));
+    b->d_buf_bytes = cap;
+    return KFS_OK;
+}
+
+static kfs_status bf_check_pairs(const kfs_bf_pair *pairs, int npairs, int k, bool device)
+{
+    if (!pairs || npairs < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "pairs is NULL or npairs < 0");
+    if (k != 1 && k != 2) KFS_FAIL(KFS_ERR_UNSUPPORTED, "knnMatch: only k = 1 or 2 is built (the reference uses k = 2)");
+    if (npairs > 65535) KFS_FAIL(KFS_ERR_UNSUPPORTED, "more than 65535 pairs in one call");
+    for (int i = 0; i < npairs; i++) {
+        const kfs_bf_pair &p = pairs[i];
+        if (p.nq < 0 || p.nt < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "pair %d: negative row count", i);
+        if (p.nt >= (1 << 18)) KFS_FAIL(KFS_ERR_INVALID_ARG, "pair %d: train rows %d >= 2^18 (OpenCV's IMGIDX_ONE limit)", i, p.nt);
+        if (p.nq > 0 && (!p.query || !p.out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "pair %d: query/out is NULL", i);
+        if (p.nq > 0 && p.nt > 0 && !p.train) KFS_FAIL(KFS_ERR_INVALID_ARG, "pair %d: train is NULL", i);
+        if (!device && (p.d_nq || p.d_nt)) KFS_FAIL(KFS_ERR_INVALID_ARG, "pair %d: d_nq/d_nt are device-only", i);
+        if (device && (((uintptr_t)p.query | (uintptr_t)p.train | (uintptr_t)p.out) & 15))
+            KFS_FAIL(KFS_ERR_INVALID_ARG, "pair %d: device pointers must be 16-byte aligned", i);
+    }
+    return KFS_OK;
+}
+
+static kfs_status bf_launch(kfs_bf *b, const BfPairDev *h, int npairs, int k)
+{
+    int max_nq = 0;
+    for (int i = 0; i < npairs; i++) max_nq = h[i].nq > max_nq ? h[i].nq : max_nq;
+    if (npairs == 0 || max_nq == 0) return KFS_OK;
+    kfs_status s = bf_reserve_pairs(b, npairs);
+    if (s) return s;
+    const bool same = (int)b->h_pairs_last.size() == npairs && memcmp(b->h_pairs_last.data(), h, sizeof(BfPairDev) * (size_t)npairs) == 0;
+    if (!same) {
+        KFS_CUDA_TRY(cudaStreamSynchronize(b->stream)); // pinned staging may still be in flight
+        memcpy(b->h_stage, h, sizeof(BfPairDev) * (size_t)npairs);
+        KFS_CUDA_TRY(cudaMemcpyAsync(b->d_pairs, b->h_stage, sizeof(BfPairDev) * (size_t)npairs, cudaMemcpyHostToDevice, b->stream));
+        b->h_pairs_last.assign(h, h + npairs);
+    }
+    k_hamming_knn2<<<dim3(kfs_div_up(max_nq, BF_QTILE), npairs), BF_THREADS, 0, b->stream>>>(b->d_pairs, k);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_hamming_knn2 launch: %s", cudaGetErrorString(e));
+    b->launches++;
+    return KFS_OK;
+}
+
+extern "C" {
+
+kfs_status kfs_bf_create(int norm_type, int cross_check, int device, kfs_bf **out)
+{
+    if (!out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_bf_create: out is NULL");
+    *out = nullptr;
+    if (norm_type != KFS_NORM_HAMMING) KFS_FAIL(KFS_ERR_UNSUPPORTED, "only NORM_HAMMING (6) is built (VisualOdometry.cpp:18)");
+    if (cross_check) KFS_FAIL(KFS_ERR_UNSUPPORTED, "crossCheck=true is not built (the reference uses the default false)");
+    const int ndev = kfs_device_count();
+    if (ndev == 0) KFS_FAIL(KFS_ERR_NO_DEVICE, "no CUDA device visible; this library has no CPU path");
+    if (device < 0 || device >= ndev) KFS_FAIL(KFS_ERR_INVALID_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    kfs_bf *b = new (std::nothrow) kfs_bf();
+    if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "out of host memory");
+    b->device = device;
+    KfsDeviceGuard guard(device);
+    cudaError_t e = cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete b; KFS_FAIL(KFS_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+    b->stream = b->own_stream;
+    *out = b;
+    return KFS_OK;
+}
+
+void kfs_bf_destroy(kfs_bf *b)
+{
+    if (!b) return;
+    KfsDeviceGuard guard(b->device);
+    cudaStreamSynchronize(b->stream);
+    if (b->d_pairs) cudaFree(b->d_pairs);
+    if (b->h_stage) cudaFreeHost(b->h_stage);
+    if (b->d_buf) cudaFree(b->d_buf);
+    if (b->own_stream) cudaStreamDestroy(b->own_stream);
+    delete b;
+}
+
+kfs_status kfs_bf_set_stream(kfs_bf *b, void *s)
+{
+    if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
+    KfsDeviceGuard guard(b->device);
+    KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    b->stream = s ? (cudaStream_t)s : b->own_stream;
+    return KFS_OK;
+}
+void *kfs_bf_get_stream(kfs_bf *b) { return b ? (void *)b->stream : nullptr; }
+kfs_status kfs_bf_sync(kfs_bf *b)
+{
+    if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
+    KfsDeviceGuard guard(b->device);
+    KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    return KFS_OK;
+}
+int kfs_bf_last_launches(const kfs_bf *b) { return b ? b->launches : 0; }
+
+kfs_status kfs_bf_knn_match_pairs_device(kfs_bf *b, const kfs_bf_pair *pairs, int npairs, int k)
+{
+    if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
+    kfs_status s = bf_check_pairs(pairs, npairs, k, true);
+    if (s) return s;
+    KfsDeviceGuard guard(b->device);
+    b->launches = 0;
+    std::vector<BfPairDev> h((size_t)npairs);
+    for (int i = 0; i < npairs; i++) {
+        h[i].query = pairs[i].query; h[i].train = pairs[i].train; h[i].d_nq = pairs[i].d_nq; h[i].d_nt = pairs[i].d_nt;
+        h[i].out = pairs[i].out; h[i].counts = pairs[i].counts; h[i].nq = pairs[i].nq; h[i].nt = pairs[i].nt;
+    }
+    return bf_launch(b, h.data(), npairs, k);
+}
+
+kfs_status kfs_bf_knn_match_pairs(kfs_bf *b, const kfs_bf_pair *pairs, int npairs, int k)
+{
+    if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
+    kfs_status s = bf_check_pairs(pairs, npairs, k, false);
+    if (s) return s;
+    if (npairs == 0) return KFS_OK;
+    KfsDeviceGuard guard(b->device);
+    b->launches = 0;
+    // device staging layout: [queries | trains | outs | counts], every block 256-byte aligned;
+    // identical host pointers (one query set against a window of train sets) are uploaded once.
+    std::vector<size_t> oq((size_t)npairs), ot((size_t)npairs), oo((size_t)npairs), oc((size_t)npairs);
+    std::vector<char> upq((size_t)npairs), upt((size_t)npairs);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t r = off; off = kfs_align_up(off + bytes + 1, 256); return r; };
+    for (int i = 0; i < npairs; i++) {
+        int jq = -1, jt = -1;
+        for (int j = 0; j < i; j++) {
+            if (jq < 0 && pairs[j].query == pairs[i].query && pairs[j].nq == pairs[i].nq) jq = j;
+            if (jt < 0 && pairs[j].train == pairs[i].train && pairs[j].nt == pairs[i].nt) jt = j;
+        }
+        upq[i] = jq < 0; upt[i] = jt < 0;
+        oq[i] = jq >= 0 ? oq[jq] : take((size_t)pairs[i].nq * 32);
+        ot[i] = jt >= 0 ? ot[jt] : take((size_t)pairs[i].nt * 32);
+        oo[i] = take((size_t)pairs[i].nq * k * sizeof(kfs_dmatch));
+        oc[i] = take((size_t)pairs[i].nq * sizeof(int));
+    }
+    s = bf_reserve_buf(b, off + 256);
+    if (s) return s;
+    std::vector<BfPairDev> h((size_t)npairs);
+    for (int i = 0; i < npairs; i++) {
+        if (upq[i] && pairs[i].nq) KFS_CUDA_TRY(cudaMemcpyAsync(b->d_buf + oq[i], pairs[i].query, (size_t)pairs[i].nq * 32, cudaMemcpyHostToDevice, b->stream));
+        if (upt[i] && pairs[i].nt) KFS_CUDA_TRY(cudaMemcpyAsync(b->d_buf + ot[i], pairs[i].train, (size_t)pairs[i].nt * 32, cudaMemcpyHostToDevice, b->stream));
+        h[i].query = b->d_buf + oq[i]; h[i].train = b->d_buf + ot[i]; h[i].d_nq = nullptr; h[i].d_nt = nullptr;
+        h[i].out = (kfs_dmatch *)(b->d_buf + oo[i]); h[i].counts = (int *)(b->d_buf + oc[i]);
+        h[i].nq = pairs[i].nq; h[i].nt = pairs[i].nt;
+    }
+    s = bf_launch(b, h.data(), npairs, k);
+    if (s) return s;
+    for (int i = 0; i < npairs; i++) {
+        if (!pairs[i].nq) continue;
+        KFS_CUDA_TRY(cudaMemcpyAsync(pairs[i].out, b->d_buf + oo[i], (size_t)pairs[i].nq * k * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, b->stream));
+        if (pairs[i].counts) KFS_CUDA_TRY(cudaMemcpyAsync(pairs[i].counts, b->d_buf + oc[i], (size_t)pairs[i].nq * sizeof(int), cudaMemcpyDeviceToHost, b->stream));
+    }
+    KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    return KFS_OK;
+}
+
+kfs_status kfs_bf_knn_match(kfs_bf *b, const uint8_t *query, int nq, const uint8_t *train, int nt, int k, kfs_dmatch *out, int *counts)
+{
+    kfs_bf_pair p;
+    p.query = query; p.nq = nq; p.d_nq = nullptr; p.train = train; p.nt = nt; p.d_nt = nullptr; p.out = out; p.counts = counts;
+    return kfs_bf_knn_match_pairs(b, &p, 1, k);
+}
+
+kfs_status kfs_bf_knn_match_ratio(kfs_bf *b, const uint8_t *query, int nq, const uint8_t *train, int nt, float ratio, kfs_dmatch *good, int *n_good)
+{
+    if (!b || !n_good) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_bf_knn_match_ratio: bad arguments");
+    *n_good = 0;
+    kfs_bf_pair p;
+    p.query = query; p.nq = nq; p.d_nq = nullptr; p.train = train; p.nt = nt; p.d_nt = nullptr; p.out = good; p.counts = nullptr;
+    kfs_status s = bf_check_pairs(&p, 1, 2, false);
+    if (s) return s;
+    if (nq == 0) return KFS_OK;
+    KfsDeviceGuard guard(b->device);
+    b->launches = 0;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t r = off; off = kfs_align_up(off + bytes, 256); return r; };
+    const size_t oq = take((size_t)nq * 32), ot = take((size_t)nt * 32), oo = take((size_t)nq * 2 * sizeof(kfs_dmatch));
+    const size_t og = take((size_t)nq * sizeof(kfs_dmatch)), on = take(2 * sizeof(int));
+    s = bf_reserve_buf(b, off + 256);
+    if (s) return s;
+    KFS_CUDA_TRY(cudaMemcpyAsync(b->d_buf + oq, query, (size_t)nq * 32, cudaMemcpyHostToDevice, b->stream));
+    if (nt) KFS_CUDA_TRY(cudaMemcpyAsync(b->d_buf + ot, train, (size_t)nt * 32, cudaMemcpyHostToDevice, b->stream));
+    BfPairDev h;
+    h.query = b->d_buf + oq; h.train = b->d_buf + ot; h.d_nq = nullptr; h.d_nt = nullptr;
+    h.out = (kfs_dmatch *)(b->d_buf + oo); h.counts = nullptr; h.nq = nq; h.nt = nt;
+    s = bf_launch(b, &h, 1, 2);
+    if (s) return s;
+    k_ratio_compact<<<1, 1024, 0, b->stream>>>(h.out, nq, ratio, (kfs_dmatch *)(b->d_buf + og), (int *)(b->d_buf + on));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_ratio_compact launch: %s", cudaGetErrorString(e));
+    b->launches++;
+    int ng[2] = {0, 0};
+    KFS_CUDA_TRY(cudaMemcpyAsync(ng, b->d_buf + on, sizeof(ng), cudaMemcpyDeviceToHost, b->stream));
+    KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    *n_good = ng[0];
+    if (ng[0] > 0) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(good, b->d_buf + og, (size_t)ng[0] * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, b->stream));
+        KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    }
+    return KFS_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,1151 @@
+// kfs_orb.cu — ORB detect-and-describe on sm_100a: the replacement for
+//     ptrExtractor->detectAndCompute(gray, mask, kp, desc)   /root/reference/src/lib/VisualOdometry.cpp:30
+// Stage contracts are SURVEY.md §8(a) rows a1.1–a1.10 (OpenCV's ORB, which the reference links but does
+// not vendor).  Every kernel carries a leading batch dimension (blockIdx.y / .z = frame) so that one
+// launch covers a whole batch of frames; nothing on this path ever goes back to the host for a count.
+//
+// Kernel chain per batch:
+//   k_mask_binarise*  k_resize x(L-1) [x2 with a mask]  k_fast  k_select_fast  k_harris  k_select_sort
+//   k_orient  k_describe
+#include "kfs_common.cuh"
+#include "kfs_math.cuh"
+#include <math.h>
+#include <string.h>
+#include <vector>
+#include <new>
+
+#define KFS_MAX_LEVELS 16
+#define KFS_BORDER 31
+
+struct LevelDev {
+    const uint8_t *img;      // frame f of this level at img + f*img_fs
+    const uint8_t *mask;     // nullptr when no mask
+    long long img_fs, mask_fs;
+    int pitch, mask_pitch;
+    int w, h, quota;
+    float scale;
+    int list_off, list_cap;  // this level's slice inside a frame's list segment
+    int tiles_x, tiles_y, tile_base;
+};
+
+struct OrbDev {
+    int nlevels, batch, fast_thr, cap_out, list_fs, total_tiles;
+    uint32_t *raw;       // [batch][list_fs]  FAST corners after NMS/border/mask: score<<24 | y<<12 | x
+    uint32_t *cand_xy;   // [batch][list_fs]  survivors of retainBest(2*quota) on the FAST score
+    float *cand_resp;    // [batch][list_fs]  their Harris responses
+    uint32_t *kept_xy;   // [batch][list_fs]  survivors of retainBest(quota) on Harris, sorted by (y,x)
+    float *kept_resp;
+    int *raw_count, *cand_count, *kept_count; // [batch][KFS_MAX_LEVELS]
+    int *n_out;          // [batch]
+    kfs_keypoint *kp;    // [batch][cap_out]
+    uint8_t *desc;       // [batch][cap_out][32]
+    float2 *rot;         // [batch][cap_out]  (cos, sin) of the keypoint angle
+    uint32_t *slot_meta; // [batch][cap_out]  x | y<<12 | level<<24
+    LevelDev lv[KFS_MAX_LEVELS];
+};
+
+__device__ __align__(4) const int8_t d_pattern[1024] = {
+#include "orb_pattern.inc"
+};
+
+// ======================================================================================================
+// a1.1 / a1.2  pyramid: INTER_LINEAR_EXACT, 8.8 fixed point, chained level to level
+// ======================================================================================================
+// xtab/ytab entry: source offset (low 16 bits) | m1 (high 16 bits, 0..256).  xtab is padded to a multiple
+// of 4 entries with (sw-1, 0) so the pad bytes of a row replicate the last column.
+// mask_mode: after the resize keep only ==255 (threshold(254, TOZERO) of a 0/255 mask).
+__global__ void __launch_bounds__(256)
+k_resize(const uint8_t *__restrict__ src, long long sfs, int spitch, int sw, int sh,
+         uint8_t *__restrict__ dst, long long dfs, int dpitch, int dw, int dh,
+         const uint32_t *__restrict__ xtab, const uint32_t *__restrict__ ytab, int mask_mode)
+{
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 8 + threadIdx.y;
+    const int f = blockIdx.z;
+    if (x4 >= dw || y >= dh) return;
+    const uint32_t yt = __ldg(ytab + y);
+    const int y0 = yt & 0xffff, n1 = yt >> 16, n0 = 256 - n1;
+    const int y1 = min(y0 + 1, sh - 1);
+    const uint8_t *r0 = src + (long long)f * sfs + (long long)y0 * spitch;
+    const uint8_t *r1 = src + (long long)f * sfs + (long long)y1 * spitch;
+    const uint4 xt = __ldg(reinterpret_cast<const uint4 *>(xtab + x4));
+    const uint32_t t[4] = {xt.x, xt.y, xt.z, xt.w};
+    uint32_t outw = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int a = t[j] & 0xffff, m1 = t[j] >> 16, m0 = 256 - m1;
+        const int b = min(a + 1, sw - 1);
+        const uint32_t h0 = m0 * __ldg(r0 + a) + m1 * __ldg(r0 + b);
+        const uint32_t h1 = m0 * __ldg(r1 + a) + m1 * __ldg(r1 + b);
+        uint32_t v = (n0 * h0 + n1 * h1 + 32768u) >> 16;
+        if (mask_mode) v = (v == 255u) ? 255u : 0u;
+        outw |= v << (8 * j);
+    }
+    *reinterpret_cast<uint32_t *>(dst + (long long)f * dfs + (long long)y * dpitch + x4) = outw;
+}
+
+// a1.2 level 0 of the mask pyramid: mask != 0 -> 255
+__global__ void __launch_bounds__(256)
+k_mask_binarise(const uint8_t *__restrict__ src, long long sfs, long long sstep,
+                uint8_t *__restrict__ dst, long long dfs, int dpitch, int w, int h)
+{
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 8 + threadIdx.y;
+    const int f = blockIdx.z;
+    if (x4 >= w || y >= h) return;
+    const uint8_t *s = src + (long long)f * sfs + (long long)y * sstep;
+    uint32_t outw = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int x = min(x4 + j, w - 1);
+        outw |= (__ldg(s + x) ? 255u : 0u) << (8 * j);
+    }
+    *reinterpret_cast<uint32_t *>(dst + (long long)f * dfs + (long long)y * dpitch + x4) = outw;
+}
+
+// ======================================================================================================
+// a1.3 / a1.4  FAST-9/16 score + 3x3 NMS + border / mask filter -> per-(frame, level) corner list
+// ======================================================================================================
+// One CTA = one 64x32 tile of the keepable region [31, W-31) x [31, H-31) of one level of one frame.
+//   source tile 80 x 40 bytes, origin (tx0-8, ty0-4), 16-byte aligned rows -> uint4 loads
+//   score  tile 72 x 34 bytes, origin (tx0-4, ty0-1)
+// phase 1: necessary-condition test on 4 pixels per thread (u16x2 SIMD, two pixels per op); survivors are
+//          compacted into a shared-memory queue by warp ballot + popc prefix
+// phase 2: exact score of the queued pixels (both polarities in one u16x2 word, VIMNMX3 trees)
+// phase 3: 3x3 NMS on the score tile, border/mask predicate, block-aggregated append to the global list
+constexpr int FT_W = 64, FT_H = 32;
+constexpr int FS_W = 80, FS_H = FT_H + 8;
+constexpr int SC_W = 72, SC_H = FT_H + 2;
+constexpr int FQ_PER_ROW = SC_W / 4;
+constexpr int NQUAD = FQ_PER_ROW * SC_H;
+constexpr int FAST_X0 = 24; // interior x origin of tile column 0; source origin 16 keeps rows 16B-aligned
+constexpr int FAST_THREADS = 256;
+constexpr int FAST_EMIT_CAP = (FT_W / 2) * (FT_H / 2);
+
+__global__ void __launch_bounds__(FAST_THREADS)
+k_fast(const __grid_constant__ OrbDev g)
+{
+    __shared__ __align__(16) uint8_t s_src[FS_W * FS_H];
+    __shared__ __align__(16) uint8_t s_sc[SC_W * SC_H];
+    __shared__ uint16_t s_q[SC_W * SC_H];
+    __shared__ uint32_t s_emit[FAST_EMIT_CAP];
+    __shared__ int s_nq, s_nemit, s_gbase;
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int f = blockIdx.y;
+    int l = 0;
+    {
+        const int t = blockIdx.x;
+#pragma unroll 1
+        for (int i = 1; i < g.nlevels; i++)
+            if (t >= g.lv[i].tile_base && g.lv[i].tiles_x > 0) l = i;
+    }
+    const LevelDev &L = g.lv[l];
+    const int trel = blockIdx.x - L.tile_base;
+    const int tix = trel % L.tiles_x, tiy = trel / L.tiles_x;
+    const int W = L.w, H = L.h, pitch = L.pitch;
+    const int tx0 = FAST_X0 + FT_W * tix, ty0 = KFS_BORDER + FT_H * tiy;
+    const int sx0 = tx0 - 8, sy0 = ty0 - 4;
+    const uint8_t *img = L.img + (long long)f * L.img_fs;
+    const int thr = g.fast_thr;
+
+    // ---- load the source tile (uint4 per thread), clear the score tile
+    for (int i = tid; i < FS_H * (FS_W / 16); i += FAST_THREADS) {
+        const int r = i / (FS_W / 16), c = i % (FS_W / 16);
+        const int gy = min(max(sy0 + r, 0), H - 1), gx = sx0 + 16 * c;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
+        *reinterpret_cast<uint4 *>(s_src + r * FS_W + 16 * c) = v;
+    }
+    for (int i = tid; i < SC_W * SC_H / 4; i += FAST_THREADS) reinterpret_cast<uint32_t *>(s_sc)[i] = 0;
+    if (tid == 0) { s_nq = 0; s_nemit = 0; }
+    __syncthreads();
+
+    // ---- phase 1: quick reject, 4 pixels per thread per iteration
+    // x range whose score this tile needs: [tx0-1, tx0+64] clipped to [30, W-31]; y likewise
+    const int xlo = max(tx0 - 1, KFS_BORDER - 1), xhi = min(tx0 + FT_W, W - KFS_BORDER);
+    const int ylo = max(ty0 - 1, KFS_BORDER - 1), yhi = min(ty0 + FT_H, H - KFS_BORDER);
+#pragma unroll 1
+    for (int it = 0; it < (NQUAD + FAST_THREADS - 1) / FAST_THREADS; it++) {
+        const int qi = it * FAST_THREADS + tid;
+        uint32_t pass4 = 0;
+        int qr = 0, qc = 0;
+        if (qi < NQUAD) {
+            qr = qi / FQ_PER_ROW;
+            qc = qi - qr * FQ_PER_ROW;
+            const int x = tx0 - 4 + 4 * qc, y = ty0 - 1 + qr;
+            uint32_t vm = 0;
+            if (y >= ylo && y <= yhi) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) vm |= (uint32_t)(x + j >= xlo && x + j <= xhi) << j;
+            }
+            if (vm) {
+                const uint8_t *rowc = s_src + (qr + 3) * FS_W + 4 + 4 * qc;
+                const uint32_t B = *reinterpret_cast<const uint32_t *>(rowc);
+                const uint32_t A = *reinterpret_cast<const uint32_t *>(rowc - 4);
+                const uint32_t C = *reinterpret_cast<const uint32_t *>(rowc + 4);
+                const uint32_t U = *reinterpret_cast<const uint32_t *>(rowc - 3 * FS_W);
+                const uint32_t D = *reinterpret_cast<const uint32_t *>(rowc + 3 * FS_W);
+                const uint32_t Rw = __funnelshift_r(B, C, 24); // pixels x+3 .. x+6
+                const uint32_t Lw = __funnelshift_r(A, B, 8);  // pixels x-3 .. x
+                const uint32_t M = 0x00ff00ffu;
+                const uint32_t me = kfs_fast_quick2(B & M, U & M, D & M, Rw & M, Lw & M, thr);
+                const uint32_t mo = kfs_fast_quick2((B >> 8) & M, (U >> 8) & M, (D >> 8) & M, (Rw >> 8) & M, (Lw >> 8) & M, thr);
+                pass4 = ((me >> 15) & 1u) | (((mo >> 15) & 1u) << 1) | (((me >> 31) & 1u) << 2) | (((mo >> 31) & 1u) << 3);
+                pass4 &= vm;
+            }
+        }
+        const uint32_t b0 = __ballot_sync(0xffffffffu, pass4 & 1u), b1 = __ballot_sync(0xffffffffu, pass4 & 2u);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, pass4 & 4u), b3 = __ballot_sync(0xffffffffu, pass4 & 8u);
+        const int c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
+        const int tot = c0 + c1 + c2 + c3;
+        if (tot) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&s_nq, tot);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            const uint32_t lt = (1u << lane) - 1u;
+            const int pi = qr * SC_W + 4 * qc;
+            if (pass4 & 1u) s_q[base + __popc(b0 & lt)] = (uint16_t)(pi);
+            if (pass4 & 2u) s_q[base + c0 + __popc(b1 & lt)] = (uint16_t)(pi + 1);
+            if (pass4 & 4u) s_q[base + c0 + c1 + __popc(b2 & lt)] = (uint16_t)(pi + 2);
+            if (pass4 & 8u) s_q[base + c0 + c1 + c2 + __popc(b3 & lt)] = (uint16_t)(pi + 3);
+        }
+    }
+    __syncthreads();
+    const int nq = s_nq;
+
+    // ---- phase 2: exact score of queued pixels
+    for (int e = tid; e < nq; e += FAST_THREADS) {
+        const int pi = s_q[e];
+        const int sy = pi / SC_W, sx = pi - sy * SC_W;
+        const uint8_t *c = s_src + (sy + 3) * FS_W + sx + 4;
+        const uint32_t cv = kfs_fast_cv(c[0]);
+        uint32_t ek[16];
+        ek[0] = kfs_fast_e(cv, c[3 * FS_W + 0]);   ek[1] = kfs_fast_e(cv, c[3 * FS_W + 1]);
+        ek[2] = kfs_fast_e(cv, c[2 * FS_W + 2]);   ek[3] = kfs_fast_e(cv, c[1 * FS_W + 3]);
+        ek[4] = kfs_fast_e(cv, c[3]);              ek[5] = kfs_fast_e(cv, c[-1 * FS_W + 3]);
+        ek[6] = kfs_fast_e(cv, c[-2 * FS_W + 2]);  ek[7] = kfs_fast_e(cv, c[-3 * FS_W + 1]);
+        ek[8] = kfs_fast_e(cv, c[-3 * FS_W + 0]);  ek[9] = kfs_fast_e(cv, c[-3 * FS_W - 1]);
+        ek[10] = kfs_fast_e(cv, c[-2 * FS_W - 2]); ek[11] = kfs_fast_e(cv, c[-1 * FS_W - 3]);
+        ek[12] = kfs_fast_e(cv, c[-3]);            ek[13] = kfs_fast_e(cv, c[1 * FS_W - 3]);
+        ek[14] = kfs_fast_e(cv, c[2 * FS_W - 2]);  ek[15] = kfs_fast_e(cv, c[3 * FS_W - 1]);
+        const int m = kfs_fast9_m(ek);
+        if (m > thr) s_sc[pi] = (uint8_t)(m - 1);
+    }
+    __syncthreads();
+
+    // ---- phase 3: NMS + border/mask filter + emit
+    const uint8_t *mask = L.mask ? L.mask + (long long)f * L.mask_fs : nullptr;
+    for (int e0 = 0; e0 < nq; e0 += FAST_THREADS) {
+        const int e = e0 + tid;
+        uint32_t packed = 0;
+        bool keep = false;
+        if (e < nq) {
+            const int pi = s_q[e];
+            const int s = s_sc[pi];
+            const int sy = pi / SC_W, sx = pi - sy * SC_W;
+            const int x = tx0 - 4 + sx, y = ty0 - 1 + sy;
+            if (s > 0 && sx >= 4 && sx < 4 + FT_W && sy >= 1 && sy <= FT_H &&
+                x >= KFS_BORDER && x < W - KFS_BORDER && y >= KFS_BORDER && y < H - KFS_BORDER) {
+                const uint8_t *p = s_sc + pi;
+                keep = s > p[-1] && s > p[1] && s > p[-SC_W - 1] && s > p[-SC_W] && s > p[-SC_W + 1] &&
+                       s > p[SC_W - 1] && s > p[SC_W] && s > p[SC_W + 1];
+                if (keep && mask) keep = __ldg(mask + (long long)y * L.mask_pitch + x) != 0;
+                packed = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+            }
+        }
+        const uint32_t bk = __ballot_sync(0xffffffffu, keep);
+        if (bk) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&s_nemit, __popc(bk));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (keep) s_emit[base + __popc(bk & ((1u << lane) - 1u))] = packed;
+        }
+    }
+    __syncthreads();
+    const int ne = s_nemit;
+    if (ne == 0) return;
+    if (tid == 0) s_gbase = atomicAdd(g.raw_count + f * KFS_MAX_LEVELS + l, ne);
+    __syncthreads();
+    const int gbase = s_gbase;
+    uint32_t *out = g.raw + (long long)f * g.list_fs + L.list_off;
+    for (int i = tid; i < ne; i += FAST_THREADS)
+        if (gbase + i < L.list_cap) out[gbase + i] = s_emit[i];
+}
+
+// ======================================================================================================
+// a1.4  retainBest(2*quota) on the FAST score: keep every corner whose score >= the (2*quota)-th largest
+// ======================================================================================================
+// grid (level, frame); scores are integers in [thr, 254] so a 256-bin histogram select is exact.
+constexpr int SEL_THREADS = 1024;
+__global__ void __launch_bounds__(SEL_THREADS)
+k_select_fast(const __grid_constant__ OrbDev g)
+{
+    __shared__ int s_hist[256];
+    __shared__ int s_thr;
+    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+    const LevelDev &L = g.lv[l];
+    if (L.list_cap == 0) return;
+    const int n = min(g.raw_count[f * KFS_MAX_LEVELS + l], L.list_cap);
+    const int target = 2 * L.quota;
+    const uint32_t *raw = g.raw + (long long)f * g.list_fs + L.list_off;
+    int thr = 0;
+    if (n > target) {
+        if (tid < 256) s_hist[tid] = 0;
+        __syncthreads();
+        for (int i = tid; i < n; i += SEL_THREADS) atomicAdd(&s_hist[raw[i] >> 24], 1);
+        __syncthreads();
+        if (tid < 32) {
+            // warp scan from the top bin down, 8 bins per lane
+            int loc[8], sum = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) { loc[k] = s_hist[255 - (lane * 8 + k)]; sum += loc[k]; }
+            int incl = sum;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += v;
+            }
+            int cum = incl - sum, found = -1;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                cum += loc[k];
+                if (found < 0 && cum >= target) found = 255 - (lane * 8 + k);
+            }
+            const uint32_t b = __ballot_sync(0xffffffffu, found >= 0);
+            const int src = __ffs(b) - 1;
+            const int t = __shfl_sync(0xffffffffu, found, src < 0 ? 0 : src);
+            if (lane == 0) s_thr = (b ? t : 0);
+        }
+        __syncthreads();
+        thr = s_thr;
+    }
+    if (target <= 0) thr = 256; // nothing is kept for a zero quota
+    uint32_t *cand = g.cand_xy + (long long)f * g.list_fs + L.list_off;
+    int *ccount = g.cand_count + f * KFS_MAX_LEVELS + l;
+    for (int i0 = 0; i0 < n; i0 += SEL_THREADS) {
+        const int i = i0 + tid;
+        uint32_t v = 0;
+        bool keep = false;
+        if (i < n) { v = raw[i]; keep = (int)(v >> 24) >= thr; }
+        const uint32_t b = __ballot_sync(0xffffffffu, keep);
+        if (b) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(ccount, __popc(b));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (keep) cand[base + __popc(b & ((1u << lane) - 1u))] = v;
+        }
+    }
+}
+
+// ======================================================================================================
+// a1.5  Harris response (block 7, k 0.04) on the un-blurred level, one thread per candidate
+// ======================================================================================================
+__global__ void __launch_bounds__(256)
+k_harris(const __grid_constant__ OrbDev g)
+{
+    const int l = blockIdx.y, f = blockIdx.z;
+    const LevelDev &L = g.lv[l];
+    if (L.list_cap == 0) return;
+    const int n = min(g.cand_count[f * KFS_MAX_LEVELS + l], L.list_cap);
+    const uint32_t *cand = g.cand_xy + (long long)f * g.list_fs + L.list_off;
+    float *resp = g.cand_resp + (long long)f * g.list_fs + L.list_off;
+    const uint8_t *img = L.img + (long long)f * L.img_fs;
+    const int pitch = L.pitch;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t v = cand[i];
+        const int x = v & 0xfff, y = (v >> 12) & 0xfff;
+        const uint8_t *p = img + (long long)(y - 4) * pitch + (x - 4);
+        int r0[9], r1[9], r2[9];
+#pragma unroll
+        for (int j = 0; j < 9; j++) { r0[j] = __ldg(p + j); r1[j] = __ldg(p + pitch + j); }
+        int a = 0, b = 0, c = 0;
+#pragma unroll
+        for (int i7 = 0; i7 < 7; i7++) {
+            const uint8_t *q = p + (long long)(i7 + 2) * pitch;
+#pragma unroll
+            for (int j = 0; j < 9; j++) r2[j] = __ldg(q + j);
+#pragma unroll
+            for (int j = 0; j < 7; j++) {
+                const int Ix = (r1[j + 2] - r1[j]) * 2 + (r0[j + 2] - r0[j]) + (r2[j + 2] - r2[j]);
+                const int Iy = (r2[j + 1] - r0[j + 1]) * 2 + (r2[j] - r0[j]) + (r2[j + 2] - r0[j + 2]);
+                a += Ix * Ix; b += Iy * Iy; c += Ix * Iy;
+            }
+#pragma unroll
+            for (int j = 0; j < 9; j++) { r0[j] = r1[j]; r1[j] = r2[j]; }
+        }
+        resp[i] = kfs_harris_response(a, b, c);
+    }
+}
+
+// ======================================================================================================
+// a1.6  retainBest(quota) on the Harris response (ties kept) + deterministic (y,x) order
+// ======================================================================================================
+// grid (level, frame).  4-pass radix select on the order-preserving u32 key of the fp32 response gives the
+// exact quota-th largest; everything >= it is kept; the rank of a kept entry among kept entries by
+// (y<<12|x) is its output position.
+constexpr int SORT_THREADS = 512;
+constexpr int SORT_SMEM_N = 4096;
+__global__ void __launch_bounds__(SORT_THREADS)
+k_select_sort(const __grid_constant__ OrbDev g)
+{
+    __shared__ uint32_t s_key[SORT_SMEM_N];
+    __shared__ uint32_t s_pos[SORT_SMEM_N];
+    __shared__ int s_hist[256];
+    __shared__ uint32_t s_prefix;
+    __shared__ int s_need, s_nkept;
+    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    const LevelDev &L = g.lv[l];
+    if (L.list_cap == 0) return;
+    const int n = min(g.cand_count[f * KFS_MAX_LEVELS + l], L.list_cap);
+    const uint32_t *cand = g.cand_xy + (long long)f * g.list_fs + L.list_off;
+    const float *resp = g.cand_resp + (long long)f * g.list_fs + L.list_off;
+    const bool in_smem = n <= SORT_SMEM_N;
+    if (in_smem)
+        for (int i = tid; i < n; i += SORT_THREADS) { s_key[i] = kfs_float_key(resp[i]); s_pos[i] = cand[i] & 0xffffffu; }
+    if (tid == 0) { s_prefix = 0; s_need = L.quota; s_nkept = 0; }
+    __syncthreads();
+    uint32_t thr_key = 0;
+    if (L.quota <= 0) thr_key = 0xffffffffu;
+    else if (n > L.quota) {
+        for (int pass = 0; pass < 4; pass++) {
+            const int shift = 24 - 8 * pass;
+            const uint32_t hi_mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+            if (tid < 256) s_hist[tid] = 0;
+            __syncthreads();
+            const uint32_t prefix = s_prefix;
+            for (int i = tid; i < n; i += SORT_THREADS) {
+                const uint32_t k = in_smem ? s_key[i] : kfs_float_key(resp[i]);
+                if ((k & hi_mask) == prefix) atomicAdd(&s_hist[(k >> shift) & 255u], 1);
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int need = s_need, cum = 0;
+                for (int d = 255; d >= 0; d--) {
+                    const int c = s_hist[d];
+                    if (cum + c >= need) { s_prefix = prefix | ((uint32_t)d << shift); s_need = need - cum; break; }
+                    cum += c;
+                }
+            }
+            __syncthreads();
+        }
+        thr_key = s_prefix;
+    }
+    uint32_t *kxy = g.kept_xy + (long long)f * g.list_fs + L.list_off;
+    float *kresp = g.kept_resp + (long long)f * g.list_fs + L.list_off;
+    int mine = 0;
+    for (int i = tid; i < n; i += SORT_THREADS) {
+        const uint32_t ki = in_smem ? s_key[i] : kfs_float_key(resp[i]);
+        if (ki < thr_key) continue;
+        const uint32_t pi = in_smem ? s_pos[i] : (cand[i] & 0xffffffu);
+        int rank = 0;
+        if (in_smem) {
+            for (int j = 0; j < n; j++) rank += (s_key[j] >= thr_key && s_pos[j] < pi) ? 1 : 0;
+        } else {
+            for (int j = 0; j < n; j++) rank += (kfs_float_key(resp[j]) >= thr_key && (cand[j] & 0xffffffu) < pi) ? 1 : 0;
+        }
+        kxy[rank] = pi;
+        kresp[rank] = resp[i];
+        mine++;
+    }
+    if (mine) atomicAdd(&s_nkept, mine);
+    __syncthreads();
+    if (tid == 0) g.kept_count[f * KFS_MAX_LEVELS + l] = s_nkept;
+}
+
+// ======================================================================================================
+// a1.7 / a1.8  intensity-centroid orientation + keypoint record
+// ======================================================================================================
+// grid (ceil(cap_out/8), frame); one warp per output slot.  Lane = column u of the radius-15 disc; the
+// disc is symmetric so column u spans rows |v| <= umax[|u|].  fp64 sincos for the descriptor rotation is
+// done once per keypoint by lanes 0..7 of warp 0 (dense) instead of once per warp.
+constexpr int ORI_KP_PER_CTA = 8;
+__global__ void __launch_bounds__(32 * ORI_KP_PER_CTA)
+k_orient(const __grid_constant__ OrbDev g)
+{
+    __shared__ float s_angle[ORI_KP_PER_CTA], s_resp[ORI_KP_PER_CTA];
+    __shared__ uint32_t s_meta[ORI_KP_PER_CTA];
+    const int f = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * ORI_KP_PER_CTA + warp;
+    // per-level kept counts -> prefix
+    int cnt = 0;
+    if (lane < g.nlevels) cnt = min(g.kept_count[f * KFS_MAX_LEVELS + lane], g.lv[lane].list_cap);
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += v;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (blockIdx.x == 0 && threadIdx.x == 0) g.n_out[f] = total;
+    const bool valid = slot < min(total, g.cap_out);
+    uint32_t meta = 0xffffffffu;
+    if (valid) {
+        const int level = __popc(__ballot_sync(0xffffffffu, incl <= slot));
+        const int excl = __shfl_sync(0xffffffffu, incl - cnt, level);
+        const int rank = slot - excl;
+        const LevelDev &L = g.lv[level];
+        const long long li = (long long)f * g.list_fs + L.list_off + rank;
+        const uint32_t xy = g.kept_xy[li];
+        const int x = xy & 0xfff, y = (xy >> 12) & 0xfff;
+        int m10 = 0, m01 = 0;
+        if (lane < 31) {
+            const int u = lane - 15, au = u < 0 ? -u : u;
+            const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * au)) & 15ull);
+            const uint8_t *c = L.img + (long long)f * L.img_fs + (long long)y * L.pitch + x + u;
+            int colsum = 0;
+            for (int v = -d; v <= d; v++) {
+                const int I = __ldg(c + (long long)v * L.pitch);
+                colsum += I;
+                m01 += v * I;
+            }
+            m10 = u * colsum;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, d);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, d);
+        }
+        if (lane == 0) {
+            s_angle[warp] = kfs_fast_atan2((float)m01, (float)m10);
+            s_resp[warp] = g.kept_resp[li];
+        }
+        meta = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)level << 24);
+    }
+    if (lane == 0) s_meta[warp] = meta;
+    __syncthreads();
+    if (threadIdx.x < ORI_KP_PER_CTA) {
+        const uint32_t m = s_meta[threadIdx.x];
+        if (m != 0xffffffffu) {
+            const int k = blockIdx.x * ORI_KP_PER_CTA + threadIdx.x;
+            const int x = m & 0xfff, y = (m >> 12) & 0xfff, level = m >> 24;
+            const float sc = g.lv[level].scale, ang = s_angle[threadIdx.x];
+            kfs_keypoint kp;
+            kp.x = kfs_mul((float)x, sc);
+            kp.y = kfs_mul((float)y, sc);
+            kp.size = kfs_mul(31.f, sc);
+            kp.angle = ang;
+            kp.response = s_resp[threadIdx.x];
+            kp.octave = level;
+            kp.class_id = -1;
+            const long long o = (long long)f * g.cap_out + k;
+            g.kp[o] = kp;
+            const float rad = kfs_mul(ang, (float)(3.1415926535897932384626433832795 / 180.f));
+            double sn, cs;
+            sincos((double)rad, &sn, &cs);
+            g.rot[o] = make_float2((float)cs, (float)sn);
+            g.slot_meta[o] = m;
+        }
+    }
+}
+
+// ======================================================================================================
+// a1.9 / a1.10  on-demand 7x7 blur of the 43x43 patch + rotated BRIEF-256, one CTA per keypoint
+// ======================================================================================================
+// The reference blurs every level in full (Σpx read + Σpx write per frame).  Keypoints sit >= 31 px inside
+// the level and the rotated pattern reaches at most 18 px, so only the 37x37 blurred patch around each
+// keypoint is ever sampled; it is produced here in shared memory with the exact sepFilter2D operation
+// order (kfs_blur_row / kfs_blur_col) and never written to HBM.
+constexpr int DESC_THREADS = 128;
+constexpr int WIN = 43, WIN_P = 45;   // raw window as float, pitch 45 (odd: conflict-free row items)
+constexpr int ROW_C = 37, ROW_P = 37; // row-pass output 43 rows x 37 cols
+constexpr int BL_P = 40;              // blurred patch 37 x 37, u8, pitch 40
+__global__ void __launch_bounds__(DESC_THREADS)
+k_describe(const __grid_constant__ OrbDev g)
+{
+    __shared__ float s_win[WIN * WIN_P];
+    __shared__ float s_row[WIN * ROW_P];
+    __shared__ __align__(4) uint8_t s_bl[ROW_C * BL_P];
+    const int f = blockIdx.y, slot = blockIdx.x, tid = threadIdx.x;
+    const int n = min(g.n_out[f], g.cap_out);
+    if (slot >= n) return;
+    const long long o = (long long)f * g.cap_out + slot;
+    const uint32_t meta = g.slot_meta[o];
+    const int level = meta >> 24;
+    const LevelDev &L = g.lv[level];
+    const kfs_keypoint kp = g.kp[o];
+    const float inv = kfs_div(1.f, L.scale);
+    const int cx = kfs_rint(kfs_mul(kp.x, inv)), cy = kfs_rint(kfs_mul(kp.y, inv));
+    const uint8_t *img = L.img + (long long)f * L.img_fs + (long long)(cy - 21) * L.pitch + (cx - 21);
+    for (int i = tid; i < WIN * WIN; i += DESC_THREADS) {
+        const int r = i / WIN, c = i - r * WIN;
+        s_win[r * WIN_P + c] = (float)__ldg(img + (long long)r * L.pitch + c);
+    }
+    __syncthreads();
+    // row pass: 86 items = (segment, row); segment 0 -> cols 0..18, segment 1 -> cols 19..36
+    if (tid < 2 * WIN) {
+        const int seg = tid / WIN, r = tid - seg * WIN;
+        const int c0 = seg * 19, cnt = seg ? 18 : 19;
+        const float *w = s_win + r * WIN_P + c0;
+        float *out = s_row + r * ROW_P + c0;
+        float p0 = w[0], p1 = w[1], p2 = w[2], p3 = w[3], p4 = w[4], p5 = w[5], p6;
+#pragma unroll
+        for (int k = 0; k < 19; k++) {
+            if (k < cnt) {
+                p6 = w[k + 6];
+                out[k] = kfs_blur_row(p0, p1, p2, p3, p4, p5, p6);
+                p0 = p1; p1 = p2; p2 = p3; p3 = p4; p4 = p5; p5 = p6;
+            }
+        }
+    }
+    __syncthreads();
+    // column pass: 111 items = (vertical segment, column); rows [0,13) [13,25) [25,37)
+    if (tid < 3 * ROW_C) {
+        const int vs = tid / ROW_C, c = tid - vs * ROW_C;
+        const int o0 = vs == 0 ? 0 : (vs == 1 ? 13 : 25), cnt = vs == 0 ? 13 : 12;
+        const float *r = s_row + o0 * ROW_P + c;
+        float q0 = r[0], q1 = r[ROW_P], q2 = r[2 * ROW_P], q3 = r[3 * ROW_P], q4 = r[4 * ROW_P], q5 = r[5 * ROW_P], q6;
+#pragma unroll
+        for (int k = 0; k < 13; k++) {
+            if (k < cnt) {
+                q6 = r[(k + 6) * ROW_P];
+                s_bl[(o0 + k) * BL_P + c] = (uint8_t)kfs_blur_col(q0, q1, q2, q3, q4, q5, q6);
+                q0 = q1; q1 = q2; q2 = q3; q3 = q4; q4 = q5; q5 = q6;
+            }
+        }
+    }
+    __syncthreads();
+    // rBRIEF: warp w, lane i -> pairs 64w+i and 64w+32+i; ballots give descriptor words 2w and 2w+1
+    const float2 ab = g.rot[o];
+    const int warp = tid >> 5, lane = tid & 31;
+    uint32_t words[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int pair = 64 * warp + 32 * h + lane;
+        const char4 pt = *reinterpret_cast<const char4 *>(d_pattern + 4 * pair);
+        int ix0, iy0, ix1, iy1;
+        kfs_brief_rot(pt.x, pt.y, ab.x, ab.y, &ix0, &iy0);
+        kfs_brief_rot(pt.z, pt.w, ab.x, ab.y, &ix1, &iy1);
+        const int v0 = s_bl[(18 + iy0) * BL_P + 18 + ix0], v1 = s_bl[(18 + iy1) * BL_P + 18 + ix1];
+        words[h] = __ballot_sync(0xffffffffu, v0 < v1);
+    }
+    if (lane == 0) {
+        uint32_t *d = reinterpret_cast<uint32_t *>(g.desc + o * 32);
+        d[2 * warp] = words[0];
+        d[2 * warp + 1] = words[1];
+    }
+}
+
+// ======================================================================================================
+// host side
+// ======================================================================================================
+struct kfs_orb {
+    kfs_orb_params p;
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    // geometry currently allocated for
+    int W = 0, H = 0, B = 0;
+    bool has_mask_alloc = false;
+    int cap_out = 0;
+    int nlevels_active = 0;
+    int lw[KFS_MAX_LEVELS], lh[KFS_MAX_LEVELS], lpitch[KFS_MAX_LEVELS], quota[KFS_MAX_LEVELS];
+    float lscale[KFS_MAX_LEVELS];
+    long long lfs[KFS_MAX_LEVELS];
+    uint8_t *pyr[KFS_MAX_LEVELS];   // internal level buffers (level 0 included)
+    uint8_t *mpyr[KFS_MAX_LEVELS];  // mask pyramid
+    uint32_t *xtab[KFS_MAX_LEVELS], *ytab[KFS_MAX_LEVELS];
+    void *arena = nullptr;          // one cudaMalloc for everything above and below
+    size_t arena_bytes = 0;
+    int *counters = nullptr;        // raw_count | cand_count | kept_count | n_out
+    size_t counters_bytes = 0;
+    OrbDev g;
+    int last_batch = 0;
+    int launches = 0;
+    bool profiling = false;
+    cudaEvent_t ev[KFS_STAGE_COUNT + 1];
+    bool ev_made = false;
+    float stage_ms[KFS_STAGE_COUNT];
+    int *h_counts = nullptr; // pinned staging for n_out
+};
+
+static int kfs_cvround(double v) { return (int)lrint(v); }
+
+static void kfs_axis_table(int src, int dst, int padded, std::vector<uint32_t> &tab)
+{
+    tab.assign((size_t)padded, (uint32_t)(src - 1));
+    const double scale = 1.0 / ((double)dst / (double)src);
+    for (int d = 0; d < dst; d++) {
+        const double fv = scale * ((double)d + 0.5) - 0.5;
+        const int i = (int)floor(fv);
+        uint32_t ofs, m1;
+        if (i < 0 || src <= 1) { ofs = 0; m1 = 0; }
+        else if (i >= src - 1) { ofs = (uint32_t)(src - 1); m1 = 0; }
+        else { ofs = (uint32_t)i; m1 = (uint32_t)lrint((fv - (double)i) * 256.0); }
+        tab[(size_t)d] = ofs | (m1 << 16);
+    }
+}
+
+static void kfs_orb_free_arena(kfs_orb *o)
+{
+    if (o->arena) { cudaFree(o->arena); o->arena = nullptr; }
+    o->W = o->H = o->B = 0;
+}
+
+static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_mask)
+{
+    if (o->arena && o->W == w && o->H == h && o->B >= batch && (o->has_mask_alloc || !need_mask)) return KFS_OK;
+    if (o->arena) { KFS_CUDA_TRY(cudaStreamSynchronize(o->stream)); kfs_orb_free_arena(o); }
+    const kfs_orb_params &P = o->p;
+    // geometry (SURVEY §8 header, a1.1): scale_l = (float)pow((double)sf, l); size_l = cvRound(W * (1.f/scale_l))
+    int L = P.nlevels;
+    {
+        const float factor = (float)(1.0 / P.scale_factor);
+        float ndes = P.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)P.nlevels));
+        int sum = 0;
+        for (int l = 0; l < P.nlevels - 1; l++) {
+            o->quota[l] = kfs_cvround((double)ndes);
+            sum += o->quota[l];
+            ndes *= factor;
+        }
+        o->quota[P.nlevels - 1] = P.nfeatures - sum > 0 ? P.nfeatures - sum : 0;
+    }
+    for (int l = 0; l < P.nlevels; l++) {
+        o->lscale[l] = (float)pow((double)P.scale_factor, (double)l);
+        const float inv = 1.f / o->lscale[l];
+        o->lw[l] = kfs_cvround((double)((float)w * inv));
+        o->lh[l] = kfs_cvround((double)((float)h * inv));
+        if (o->lw[l] < 1 || o->lh[l] < 1) { L = l; break; }
+        o->lpitch[l] = (int)kfs_align_up((size_t)o->lw[l], 128);
+        o->lfs[l] = (long long)o->lpitch[l] * o->lh[l];
+    }
+    o->nlevels_active = L;
+    // arena layout
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t r = off; off = kfs_align_up(off + bytes, 256); return r; };
+    size_t o_pyr[KFS_MAX_LEVELS], o_mpyr[KFS_MAX_LEVELS], o_xt[KFS_MAX_LEVELS], o_yt[KFS_MAX_LEVELS];
+    int list_off[KFS_MAX_LEVELS], list_cap[KFS_MAX_LEVELS], list_fs = 0;
+    for (int l = 0; l < L; l++) {
+        o_pyr[l] = take((size_t)o->lfs[l] * batch + 256);
+        o_mpyr[l] = need_mask ? take((size_t)o->lfs[l] * batch + 256) : 0;
+        o_xt[l] = take(kfs_align_up((size_t)o->lw[l], 4) * 4);
+        o_yt[l] = take((size_t)o->lh[l] * 4);
+        const int W = o->lw[l], H = o->lh[l];
+        list_cap[l] = (W > 2 * KFS_BORDER && H > 2 * KFS_BORDER) ? ((W - 62) / 2 + 2) * ((H - 62) / 2 + 2) : 0;
+        list_off[l] = list_fs;
+        list_fs += (list_cap[l] + 63) / 64 * 64;
+    }
+    const size_t lists = (size_t)list_fs * batch;
+    const size_t o_raw = take(lists * 4), o_cxy = take(lists * 4), o_cr = take(lists * 4), o_kxy = take(lists * 4), o_kr = take(lists * 4);
+    const size_t cnt_bytes = ((size_t)batch * KFS_MAX_LEVELS * 3 + (size_t)batch) * sizeof(int);
+    const size_t o_cnt = take(cnt_bytes);
+    const size_t outs = (size_t)batch * o->cap_out;
+    const size_t o_kp = take(outs * sizeof(kfs_keypoint)), o_desc = take(outs * 32), o_rot = take(outs * sizeof(float2)), o_meta = take(outs * 4);
+    KFS_CUDA_TRY(cudaMalloc(&o->arena, off));
+    o->arena_bytes = off;
+    uint8_t *base = (uint8_t *)o->arena;
+    KFS_CUDA_TRY(cudaMemsetAsync(base, 0, off, o->stream));
+    OrbDev &g = o->g;
+    memset(&g, 0, sizeof(g));
+    g.nlevels = L; g.batch = batch; g.fast_thr = P.fast_threshold; g.cap_out = o->cap_out; g.list_fs = list_fs;
+    g.raw = (uint32_t *)(base + o_raw); g.cand_xy = (uint32_t *)(base + o_cxy); g.cand_resp = (float *)(base + o_cr);
+    g.kept_xy = (uint32_t *)(base + o_kxy); g.kept_resp = (float *)(base + o_kr);
+    o->counters = (int *)(base + o_cnt); o->counters_bytes = cnt_bytes;
+    g.raw_count = o->counters; g.cand_count = g.raw_count + (size_t)batch * KFS_MAX_LEVELS;
+    g.kept_count = g.cand_count + (size_t)batch * KFS_MAX_LEVELS; g.n_out = g.kept_count + (size_t)batch * KFS_MAX_LEVELS;
+    g.kp = (kfs_keypoint *)(base + o_kp); g.desc = base + o_desc; g.rot = (float2 *)(base + o_rot); g.slot_meta = (uint32_t *)(base + o_meta);
+    int tile_base = 0;
+    std::vector<uint32_t> tab;
+    for (int l = 0; l < L; l++) {
+        o->pyr[l] = base + o_pyr[l];
+        o->mpyr[l] = need_mask ? base + o_mpyr[l] : nullptr;
+        o->xtab[l] = (uint32_t *)(base + o_xt[l]);
+        o->ytab[l] = (uint32_t *)(base + o_yt[l]);
+        LevelDev &D = g.lv[l];
+        D.img = o->pyr[l]; D.img_fs = o->lfs[l]; D.pitch = o->lpitch[l];
+        D.mask = nullptr; D.mask_fs = o->lfs[l]; D.mask_pitch = o->lpitch[l];
+        D.w = o->lw[l]; D.h = o->lh[l]; D.quota = o->quota[l]; D.scale = o->lscale[l];
+        D.list_off = list_off[l]; D.list_cap = list_cap[l];
+        if (list_cap[l] > 0) {
+            D.tiles_x = kfs_div_up(D.w - KFS_BORDER - FAST_X0, FT_W);
+            D.tiles_y = kfs_div_up(D.h - 2 * KFS_BORDER, FT_H);
+        } else { D.tiles_x = 0; D.tiles_y = 0; }
+        D.tile_base = tile_base;
+        tile_base += D.tiles_x * D.tiles_y;
+        if (l > 0) {
+            kfs_axis_table(o->lw[l - 1], o->lw[l], (int)kfs_align_up((size_t)o->lw[l], 4), tab);
+            KFS_CUDA_TRY(cudaMemcpyAsync(o->xtab[l], tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, o->stream));
+            KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+            kfs_axis_table(o->lh[l - 1], o->lh[l], o->lh[l], tab);
+            KFS_CUDA_TRY(cudaMemcpyAsync(o->ytab[l], tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, o->stream));
+            KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+        }
+    }
+    g.total_tiles = tile_base;
+    if (o->h_counts) { cudaFreeHost(o->h_counts); o->h_counts = nullptr; }
+    KFS_CUDA_TRY(cudaMallocHost(&o->h_counts, sizeof(int) * (size_t)batch));
+    o->W = w; o->H = h; o->B = batch; o->has_mask_alloc = need_mask;
+    return KFS_OK;
+}
+
+#define KFS_LAUNCH_CHECK(o)                                                                     \
+    do {                                                                                        \
+        cudaError_t e__ = cudaGetLastError();                                                   \
+        if (e__ != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "kernel launch failed at %s:%d: %s", __FILE__, __LINE__, cudaGetErrorString(e__)); \
+        (o)->launches++;                                                                        \
+    } while (0)
+
+static kfs_status kfs_stage_mark(kfs_orb *o, int idx)
+{
+    if (!o->profiling) return KFS_OK;
+    if (!o->ev_made) {
+        for (int i = 0; i <= KFS_STAGE_COUNT; i++) KFS_CUDA_TRY(cudaEventCreate(&o->ev[i]));
+        o->ev_made = true;
+    }
+    KFS_CUDA_TRY(cudaEventRecord(o->ev[idx], o->stream));
+    return KFS_OK;
+}
+
+// Runs the kernel chain on `batch` frames whose level 0 is already described by g.lv[0].img / .mask.
+static kfs_status kfs_orb_run(kfs_orb *o, int batch, const uint8_t *d_mask_in, size_t mask_step, size_t mask_fs)
+{
+    OrbDev &g = o->g;
+    const int L = g.nlevels;
+    cudaStream_t st = o->stream;
+    g.batch = batch;
+    KFS_CUDA_TRY(cudaMemsetAsync(o->counters, 0, o->counters_bytes, st));
+    const dim3 rb(32, 8);
+    const bool has_mask = d_mask_in != nullptr;
+    for (int l = 0; l < L; l++) g.lv[l].mask = has_mask ? o->mpyr[l] : nullptr;
+    if (has_mask) {
+        k_mask_binarise<<<dim3(kfs_div_up(o->lw[0], 128), kfs_div_up(o->lh[0], 8), batch), rb, 0, st>>>(
+            d_mask_in, (long long)mask_fs, (long long)mask_step, o->mpyr[0], o->lfs[0], o->lpitch[0], o->lw[0], o->lh[0]);
+        KFS_LAUNCH_CHECK(o);
+    }
+    for (int l = 1; l < L; l++) {
+        const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8), batch);
+        k_resize<<<grid, rb, 0, st>>>(g.lv[l - 1].img, g.lv[l - 1].img_fs, g.lv[l - 1].pitch, o->lw[l - 1], o->lh[l - 1],
+                                      o->pyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 0);
+        KFS_LAUNCH_CHECK(o);
+        if (has_mask) {
+            k_resize<<<grid, rb, 0, st>>>(o->mpyr[l - 1], o->lfs[l - 1], o->lpitch[l - 1], o->lw[l - 1], o->lh[l - 1],
+                                          o->mpyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 1);
+            KFS_LAUNCH_CHECK(o);
+        }
+    }
+    if (kfs_stage_mark(o, KFS_STAGE_FAST)) return KFS_ERR_CUDA;
+    if (g.total_tiles > 0) {
+        k_fast<<<dim3(g.total_tiles, batch), FAST_THREADS, 0, st>>>(g);
+        KFS_LAUNCH_CHECK(o);
+    }
+    if (kfs_stage_mark(o, KFS_STAGE_SELECT_HARRIS)) return KFS_ERR_CUDA;
+    if (g.total_tiles > 0) {
+        k_select_fast<<<dim3(L, batch), SEL_THREADS, 0, st>>>(g);
+        KFS_LAUNCH_CHECK(o);
+        int maxq = 1;
+        for (int l = 0; l < L; l++) maxq = o->quota[l] > maxq ? o->quota[l] : maxq;
+        k_harris<<<dim3(kfs_div_up(2 * maxq + 256, 256), L, batch), 256, 0, st>>>(g);
+        KFS_LAUNCH_CHECK(o);
+    }
+    if (kfs_stage_mark(o, KFS_STAGE_SELECT_SORT)) return KFS_ERR_CUDA;
+    if (g.total_tiles > 0) {
+        k_select_sort<<<dim3(L, batch), SORT_THREADS, 0, st>>>(g);
+        KFS_LAUNCH_CHECK(o);
+    }
+    if (kfs_stage_mark(o, KFS_STAGE_ORIENT)) return KFS_ERR_CUDA;
+    k_orient<<<dim3(kfs_div_up(g.cap_out, ORI_KP_PER_CTA), batch), 32 * ORI_KP_PER_CTA, 0, st>>>(g);
+    KFS_LAUNCH_CHECK(o);
+    if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
+    k_describe<<<dim3(g.cap_out, batch), DESC_THREADS, 0, st>>>(g);
+    KFS_LAUNCH_CHECK(o);
+    if (kfs_stage_mark(o, KFS_STAGE_COUNT)) return KFS_ERR_CUDA;
+    o->last_batch = batch;
+    return KFS_OK;
+}
+
+static kfs_status kfs_orb_check_frame_args(const kfs_orb *o, const void *gray, size_t step, int w, int h, int batch)
+{
+    if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
+    if (w < 0 || h < 0 || batch < 1) KFS_FAIL(KFS_ERR_INVALID_ARG, "negative image size or batch < 1");
+    if (w == 0 || h == 0) return KFS_OK;
+    if (!gray) KFS_FAIL(KFS_ERR_INVALID_ARG, "image pointer is NULL");
+    if (step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "step %zu < width %d", step, w);
+    if (w > 4096 || h > 4096) KFS_FAIL(KFS_ERR_UNSUPPORTED, "image larger than 4096 px on a side (%dx%d)", w, h);
+    if (batch > 65535) KFS_FAIL(KFS_ERR_UNSUPPORTED, "batch > 65535");
+    return KFS_OK;
+}
+
+extern "C" {
+
+void kfs_orb_default_params(kfs_orb_params *p)
+{
+    if (!p) return;
+    p->nfeatures = 500; p->scale_factor = 1.2f; p->nlevels = 8; p->edge_threshold = 31; p->first_level = 0;
+    p->wta_k = 2; p->score_type = KFS_ORB_HARRIS_SCORE; p->patch_size = 31; p->fast_threshold = 20;
+}
+
+kfs_status kfs_orb_create(const kfs_orb_params *params, int device, kfs_orb **out)
+{
+    if (!params || !out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_create: NULL argument");
+    *out = nullptr;
+    const kfs_orb_params &P = *params;
+    if (P.nfeatures < 1 || !(P.scale_factor > 1.f) || P.nlevels < 1 || P.fast_threshold < 1 || P.fast_threshold > 254)
+        KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_create: nfeatures>=1, scale_factor>1, nlevels>=1, 1<=fast_threshold<=254 required");
+    if (P.nlevels > KFS_MAX_LEVELS) KFS_FAIL(KFS_ERR_UNSUPPORTED, "nlevels > %d", KFS_MAX_LEVELS);
+    if (P.edge_threshold != 31 || P.first_level != 0 || P.wta_k != 2 || P.score_type != KFS_ORB_HARRIS_SCORE || P.patch_size != 31)
+        KFS_FAIL(KFS_ERR_UNSUPPORTED, "only edgeThreshold=31, firstLevel=0, WTA_K=2, HARRIS_SCORE, patchSize=31 (the reference's values) are built");
+    const int ndev = kfs_device_count();
+    if (ndev == 0) KFS_FAIL(KFS_ERR_NO_DEVICE, "no CUDA device visible; this library has no CPU path");
+    if (device < 0 || device >= ndev) KFS_FAIL(KFS_ERR_INVALID_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    kfs_orb *o = new (std::nothrow) kfs_orb();
+    if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "out of host memory");
+    o->p = P;
+    o->device = device;
+    o->cap_out = (int)kfs_align_up((size_t)(P.nfeatures + P.nfeatures / 4 + 64), 8);
+    memset(&o->g, 0, sizeof(o->g));
+    memset(o->stage_ms, 0, sizeof(o->stage_ms));
+    KfsDeviceGuard guard(device);
+    cudaError_t e = cudaStreamCreateWithFlags(&o->own_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete o;
+        KFS_FAIL(KFS_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
+    }
+    o->stream = o->own_stream;
+    *out = o;
+    return KFS_OK;
+}
+
+void kfs_orb_destroy(kfs_orb *o)
+{
+    if (!o) return;
+    KfsDeviceGuard guard(o->device);
+    cudaStreamSynchronize(o->stream);
+    kfs_orb_free_arena(o);
+    if (o->h_counts) cudaFreeHost(o->h_counts);
+    if (o->ev_made) for (int i = 0; i <= KFS_STAGE_COUNT; i++) cudaEventDestroy(o->ev[i]);
+    if (o->own_stream) cudaStreamDestroy(o->own_stream);
+    delete o;
+}
+
+int kfs_orb_capacity(const kfs_orb *o) { return o ? o->cap_out : 0; }
+
+kfs_status kfs_orb_set_capacity(kfs_orb *o, int capacity)
+{
+    if (!o || capacity < 1) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_set_capacity: bad arguments");
+    KfsDeviceGuard guard(o->device);
+    const int c = (int)kfs_align_up((size_t)capacity, 8);
+    if (c != o->cap_out) {
+        if (o->arena) { KFS_CUDA_TRY(cudaStreamSynchronize(o->stream)); kfs_orb_free_arena(o); }
+        o->cap_out = c;
+    }
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_set_stream(kfs_orb *o, void *s)
+{
+    if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
+    KfsDeviceGuard guard(o->device);
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    o->stream = s ? (cudaStream_t)s : o->own_stream;
+    return KFS_OK;
+}
+
+void *kfs_orb_get_stream(kfs_orb *o) { return o ? (void *)o->stream : nullptr; }
+
+kfs_status kfs_orb_sync(kfs_orb *o)
+{
+    if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
+    KfsDeviceGuard guard(o->device);
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_extract_device(kfs_orb *o, const uint8_t *d_gray, size_t step, size_t frame_stride, int w, int h, int batch,
+                                  const uint8_t *d_mask, size_t mask_step, size_t mask_frame_stride)
+{
+    kfs_status s = kfs_orb_check_frame_args(o, d_gray, step, w, h, batch);
+    if (s) return s;
+    KfsDeviceGuard guard(o->device);
+    o->launches = 0;
+    if (w == 0 || h == 0) { o->last_batch = 0; return KFS_OK; }
+    if (d_mask && mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < width");
+    s = kfs_orb_ensure(o, w, h, batch, d_mask != nullptr);
+    if (s) return s;
+    if (kfs_stage_mark(o, KFS_STAGE_INGEST)) return KFS_ERR_CUDA;
+    LevelDev &L0 = o->g.lv[0];
+    const bool alias = ((uintptr_t)d_gray % 16 == 0) && (step % 16 == 0) && (frame_stride % 16 == 0);
+    if (alias) {
+        L0.img = d_gray; L0.pitch = (int)step; L0.img_fs = (long long)frame_stride;
+    } else {
+        L0.img = o->pyr[0]; L0.pitch = o->lpitch[0]; L0.img_fs = o->lfs[0];
+        if (frame_stride == step * (size_t)h) {
+            KFS_CUDA_TRY(cudaMemcpy2DAsync(o->pyr[0], (size_t)o->lpitch[0], d_gray, step, (size_t)w, (size_t)h * batch, cudaMemcpyDeviceToDevice, o->stream));
+        } else {
+            for (int f = 0; f < batch; f++)
+                KFS_CUDA_TRY(cudaMemcpy2DAsync(o->pyr[0] + (size_t)f * o->lfs[0], (size_t)o->lpitch[0], d_gray + (size_t)f * frame_stride, step,
+                                               (size_t)w, (size_t)h, cudaMemcpyDeviceToDevice, o->stream));
+        }
+    }
+    if (kfs_stage_mark(o, KFS_STAGE_PYRAMID)) return KFS_ERR_CUDA;
+    return kfs_orb_run(o, batch, d_mask, mask_step, mask_frame_stride);
+}
+
+kfs_status kfs_orb_device_results(kfs_orb *o, const kfs_keypoint **d_kp, const uint8_t **d_desc, const int **d_counts, int *capacity, int *batch)
+{
+    if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
+    if (!o->arena) KFS_FAIL(KFS_ERR_INVALID_ARG, "no extraction has run on this handle yet");
+    if (d_kp) *d_kp = o->g.kp;
+    if (d_desc) *d_desc = o->g.desc;
+    if (d_counts) *d_counts = o->g.n_out;
+    if (capacity) *capacity = o->cap_out;
+    if (batch) *batch = o->last_batch;
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_fetch_results(kfs_orb *o, kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out)
+{
+    if (!o || !n_out || capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_fetch_results: bad arguments");
+    const int B = o->last_batch;
+    if (B == 0) return KFS_OK;
+    if ((!kp_out || !desc_out) && capacity > 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
+    KfsDeviceGuard guard(o->device);
+    const int cp = capacity < o->cap_out ? capacity : o->cap_out;
+    KFS_CUDA_TRY(cudaMemcpyAsync(o->h_counts, o->g.n_out, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, o->stream));
+    if (cp > 0) {
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(kp_out, (size_t)capacity * sizeof(kfs_keypoint), o->g.kp, (size_t)o->cap_out * sizeof(kfs_keypoint),
+                                       (size_t)cp * sizeof(kfs_keypoint), (size_t)B, cudaMemcpyDeviceToHost, o->stream));
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(desc_out, (size_t)capacity * 32, o->g.desc, (size_t)o->cap_out * 32,
+                                       (size_t)cp * 32, (size_t)B, cudaMemcpyDeviceToHost, o->stream));
+    }
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    kfs_status rc = KFS_OK;
+    for (int f = 0; f < B; f++) {
+        n_out[f] = o->h_counts[f];
+        if (n_out[f] > cp) rc = KFS_ERR_CAPACITY;
+    }
+    if (rc == KFS_ERR_CAPACITY) kfs_set_error("output capacity %d too small (handle capacity %d); n_out holds the required counts", capacity, o->cap_out);
+    if (o->profiling && o->ev_made) {
+        for (int i = 0; i < KFS_STAGE_COUNT; i++) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, o->ev[i], o->ev[i + 1]) == cudaSuccess) o->stage_ms[i] = ms;
+            else cudaGetLastError();
+        }
+    }
+    return rc;
+}
+
+kfs_status kfs_orb_detect_and_compute_batch(kfs_orb *o, const uint8_t *gray, size_t step, size_t frame_stride, int w, int h, int batch,
+                                            const uint8_t *mask, size_t mask_step, size_t mask_frame_stride,
+                                            kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out)
+{
+    kfs_status s = kfs_orb_check_frame_args(o, gray, step, w, h, batch);
+    if (s) return s;
+    if (!n_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "n_out is NULL");
+    for (int f = 0; f < batch; f++) n_out[f] = 0;
+    if (w == 0 || h == 0) return KFS_OK; // OpenCV returns early on an empty image
+    if (mask && mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < width");
+    KfsDeviceGuard guard(o->device);
+    o->launches = 0;
+    s = kfs_orb_ensure(o, w, h, batch, mask != nullptr);
+    if (s) return s;
+    if (kfs_stage_mark(o, KFS_STAGE_INGEST)) return KFS_ERR_CUDA;
+    LevelDev &L0 = o->g.lv[0];
+    L0.img = o->pyr[0]; L0.pitch = o->lpitch[0]; L0.img_fs = o->lfs[0];
+    // host -> device straight into level 0 (and into the scratch half of the mask pyramid's level-0 slot)
+    if (frame_stride == step * (size_t)h) {
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(o->pyr[0], (size_t)o->lpitch[0], gray, step, (size_t)w, (size_t)h * batch, cudaMemcpyHostToDevice, o->stream));
+    } else {
+        for (int f = 0; f < batch; f++)
+            KFS_CUDA_TRY(cudaMemcpy2DAsync(o->pyr[0] + (size_t)f * o->lfs[0], (size_t)o->lpitch[0], gray + (size_t)f * frame_stride, step,
+                                           (size_t)w, (size_t)h, cudaMemcpyHostToDevice, o->stream));
+    }
+    const uint8_t *d_mask = nullptr;
+    if (mask) {
+        // stage the raw mask in the LAST level-0-sized region we own that is not read before it is
+        // overwritten: the kept_xy list area is free until k_select_sort, but may be smaller than a frame;
+        // simplest robust choice: a temporary device buffer.
+        uint8_t *tmp = nullptr;
+        KFS_CUDA_TRY(cudaMallocAsync((void **)&tmp, (size_t)o->lfs[0] * batch, o->stream));
+        if (mask_frame_stride == mask_step * (size_t)h) {
+            KFS_CUDA_TRY(cudaMemcpy2DAsync(tmp, (size_t)o->lpitch[0], mask, mask_step, (size_t)w, (size_t)h * batch, cudaMemcpyHostToDevice, o->stream));
+        } else {
+            for (int f = 0; f < batch; f++)
+                KFS_CUDA_TRY(cudaMemcpy2DAsync(tmp + (size_t)f * o->lfs[0], (size_t)o->lpitch[0], mask + (size_t)f * mask_frame_stride, mask_step,
+                                               (size_t)w, (size_t)h, cudaMemcpyHostToDevice, o->stream));
+        }
+        d_mask = tmp;
+        if (kfs_stage_mark(o, KFS_STAGE_PYRAMID)) return KFS_ERR_CUDA;
+        s = kfs_orb_run(o, batch, d_mask, (size_t)o->lpitch[0], (size_t)o->lfs[0]);
+        cudaFreeAsync(tmp, o->stream);
+    } else {
+        if (kfs_stage_mark(o, KFS_STAGE_PYRAMID)) return KFS_ERR_CUDA;
+        s = kfs_orb_run(o, batch, nullptr, 0, 0);
+    }
+    if (s) return s;
+    return kfs_orb_fetch_results(o, kp_out, desc_out, capacity, n_out);
+}
+
+kfs_status kfs_orb_detect_and_compute(kfs_orb *o, const uint8_t *gray, size_t step, int w, int h,
+                                      const uint8_t *mask, size_t mask_step,
+                                      kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out)
+{
+    return kfs_orb_detect_and_compute_batch(o, gray, step, step * (size_t)(h > 0 ? h : 0), w, h, 1, mask, mask_step,
+                                            mask_step * (size_t)(h > 0 ? h : 0), kp_out, desc_out, capacity, n_out);
+}
+
+kfs_status kfs_orb_level_info(kfs_orb *o, int level, int *w, int *h, int *quota, float *scale)
+{
+    if (!o || !o->arena) KFS_FAIL(KFS_ERR_INVALID_ARG, "no extraction has run on this handle yet");
+    if (level < 0 || level >= o->nlevels_active) KFS_FAIL(KFS_ERR_INVALID_ARG, "level out of range");
+    if (w) *w = o->lw[level];
+    if (h) *h = o->lh[level];
+    if (quota) *quota = o->quota[level];
+    if (scale) *scale = o->lscale[level];
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_download_level(kfs_orb *o, int frame, int level, uint8_t *out, size_t out_step)
+{
+    if (!o || !o->arena || !out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_download_level: bad arguments");
+    if (level < 0 || level >= o->nlevels_active || frame < 0 || frame >= o->last_batch) KFS_FAIL(KFS_ERR_INVALID_ARG, "frame/level out of range");
+    KfsDeviceGuard guard(o->device);
+    const LevelDev &L = o->g.lv[level];
+    KFS_CUDA_TRY(cudaMemcpy2DAsync(out, out_step, L.img + (size_t)frame * L.img_fs, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost, o->stream));
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_download_fast_corners(kfs_orb *o, int frame, int level, uint32_t *out, int capacity, int *n_out)
+{
+    if (!o || !o->arena || !n_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_download_fast_corners: bad arguments");
+    if (level < 0 || level >= o->nlevels_active || frame < 0 || frame >= o->last_batch) KFS_FAIL(KFS_ERR_INVALID_ARG, "frame/level out of range");
+    KfsDeviceGuard guard(o->device);
+    const LevelDev &L = o->g.lv[level];
+    int n = 0;
+    KFS_CUDA_TRY(cudaMemcpyAsync(&n, o->g.raw_count + frame * KFS_MAX_LEVELS + level, sizeof(int), cudaMemcpyDeviceToHost, o->stream));
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    if (n > L.list_cap) n = L.list_cap;
+    *n_out = n;
+    const int c = n < capacity ? n : capacity;
+    if (c > 0 && out) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(out, o->g.raw + (size_t)frame * o->g.list_fs + L.list_off, sizeof(uint32_t) * (size_t)c, cudaMemcpyDeviceToHost, o->stream));
+        KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    }
+    return n > capacity ? KFS_ERR_CAPACITY : KFS_OK;
+}
+
+kfs_status kfs_orb_set_profiling(kfs_orb *o, int on)
+{
+    if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
+    o->profiling = on != 0;
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_stage_times(kfs_orb *o, float *ms)
+{
+    if (!o || !ms) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_stage_times: bad arguments");
+    KfsDeviceGuard guard(o->device);
+    if (o->profiling && o->ev_made) {
+        KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+        for (int i = 0; i < KFS_STAGE_COUNT; i++) {
+            float t = 0;
+            if (cudaEventElapsedTime(&t, o->ev[i], o->ev[i + 1]) == cudaSuccess) o->stage_ms[i] = t;
+            else cudaGetLastError();
+        }
+    }
+    for (int i = 0; i < KFS_STAGE_COUNT; i++) ms[i] = o->stage_ms[i];
+    return KFS_OK;
+}
+
+int kfs_orb_last_launches(const kfs_orb *o) { return o ? o->launches : 0; }
+
+} // extern "C"

@@ -1,0 +1,237 @@
+"""Host-side mirror of the reference's operator interface for the hot path, over the C ABI.
+
+The reference tracker (C++) calls, per frame (/root/reference/src/lib/VisualOdometry.cpp):
+    ptrExtractor = cv::ORB::create(3000, 1.2f, 8, 31, 0, 2, cv::ORB::HARRIS_SCORE, 31, 20)      :10-16
+    ptrExtractor->detectAndCompute(gray, mask, kp, desc)                                         :30
+    ptrMatcher   = cv::BFMatcher::create(cv::NORM_HAMMING)                                       :18
+    ptrMatcher->knnMatch(keyframe->matDescriptors, dpCurrImg, knnMatches, 2)                     :39
+The C++ drop-in for those is include/kfslam_frontend_cv.hpp.  This module is the same surface for
+Python callers and for the parity tests (names and argument meaning follow cv2's: ORB_create,
+detectAndCompute, BFMatcher_create, knnMatch), so a test written against cv2 reads the same here.
+Keypoints come back as a structured array with cv::KeyPoint's fields; matches as cv::DMatch's.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from ._native import KP_DTYPE, DM_DTYPE, NORM_HAMMING, ORB_HARRIS_SCORE, KfsError  # noqa: F401
+
+
+def _ptr(a):
+    return a.ctypes.data if a is not None else None
+
+
+class ORB:
+    """cv::ORB stand-in.  One instance per host thread / GPU (not thread-safe, like the reference's use)."""
+
+    def __init__(self, nfeatures=500, scaleFactor=1.2, nlevels=8, edgeThreshold=31, firstLevel=0, WTA_K=2,
+                 scoreType=ORB_HARRIS_SCORE, patchSize=31, fastThreshold=20, device=0):
+        self._h = C.c_void_p()
+        self.params = N.OrbParams(nfeatures, scaleFactor, nlevels, edgeThreshold, firstLevel, WTA_K, scoreType,
+                                  patchSize, fastThreshold)
+        N.check(N.lib().kfs_orb_create(C.byref(self.params), device, C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            N.lib().kfs_orb_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    # -- cv2-shaped calls ---------------------------------------------------------------------------
+    def detectAndCompute(self, image, mask=None, capacity=None):
+        """-> (keypoints[KP_DTYPE], descriptors uint8[n,32]); descriptors is None when n == 0 (as cv2)."""
+        kps, descs = self.detectAndComputeBatch(np.asarray(image)[None], None if mask is None else np.asarray(mask)[None], capacity)
+        return kps[0], (descs[0] if len(kps[0]) else None)
+
+    def detectAndComputeBatch(self, images, masks=None, capacity=None):
+        """images uint8 [B,H,W] (host) -> lists of per-frame (keypoints, descriptors)."""
+        images = np.ascontiguousarray(images, dtype=np.uint8)
+        if images.ndim != 3:
+            raise ValueError("images must be [B,H,W] uint8 (gray)")
+        B, H, W = images.shape
+        if masks is not None:
+            masks = np.ascontiguousarray(masks, dtype=np.uint8)
+            if masks.shape != images.shape:
+                raise ValueError("mask shape must equal image shape")
+        cap = capacity or self.capacity
+        while True:
+            kp = np.zeros((B, cap), KP_DTYPE)
+            desc = np.zeros((B, cap, 32), np.uint8)
+            n = (C.c_int * B)()
+            st = N.lib().kfs_orb_detect_and_compute_batch(
+                self._h, _ptr(images), W, H * W, W, H, B,
+                _ptr(masks), W if masks is not None else 0, H * W if masks is not None else 0,
+                _ptr(kp), _ptr(desc), cap, n)
+            N.check(st, allow=(N.KFS_ERR_CAPACITY,))
+            if st == N.KFS_ERR_CAPACITY and capacity is None:
+                need = max(n)
+                if need > self.capacity:
+                    N.check(N.lib().kfs_orb_set_capacity(self._h, need + 64))
+                cap = self.capacity
+                continue
+            break
+        counts = [min(int(c), cap) for c in n]
+        return [kp[f, :counts[f]].copy() for f in range(B)], [desc[f, :counts[f]].copy() for f in range(B)]
+
+    # -- device-resident path -----------------------------------------------------------------------
+    def extract_device(self, d_ptr, step, frame_stride, w, h, batch, d_mask=None, mask_step=0, mask_frame_stride=0):
+        N.check(N.lib().kfs_orb_extract_device(self._h, d_ptr, step, frame_stride, w, h, batch, d_mask, mask_step, mask_frame_stride))
+
+    def device_results(self):
+        kp, desc, cnt = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        cap, batch = C.c_int(), C.c_int()
+        N.check(N.lib().kfs_orb_device_results(self._h, C.byref(kp), C.byref(desc), C.byref(cnt), C.byref(cap), C.byref(batch)))
+        return kp.value, desc.value, cnt.value, cap.value, batch.value
+
+    def fetch_results(self, batch, capacity=None):
+        cap = capacity or self.capacity
+        kp = np.zeros((batch, cap), KP_DTYPE)
+        desc = np.zeros((batch, cap, 32), np.uint8)
+        n = (C.c_int * batch)()
+        N.check(N.lib().kfs_orb_fetch_results(self._h, _ptr(kp), _ptr(desc), cap, n), allow=(N.KFS_ERR_CAPACITY,))
+        counts = [min(int(c), cap) for c in n]
+        return [kp[f, :counts[f]].copy() for f in range(batch)], [desc[f, :counts[f]].copy() for f in range(batch)]
+
+    def sync(self):
+        N.check(N.lib().kfs_orb_sync(self._h))
+
+    def set_stream(self, cuda_stream):
+        N.check(N.lib().kfs_orb_set_stream(self._h, cuda_stream))
+
+    @property
+    def capacity(self):
+        return N.lib().kfs_orb_capacity(self._h)
+
+    def set_capacity(self, cap):
+        N.check(N.lib().kfs_orb_set_capacity(self._h, cap))
+
+    # -- stage taps ---------------------------------------------------------------------------------
+    def level_info(self, level):
+        w, h, q, s = C.c_int(), C.c_int(), C.c_int(), C.c_float()
+        N.check(N.lib().kfs_orb_level_info(self._h, level, C.byref(w), C.byref(h), C.byref(q), C.byref(s)))
+        return w.value, h.value, q.value, s.value
+
+    def download_level(self, frame, level):
+        w, h, _, _ = self.level_info(level)
+        out = np.empty((h, w), np.uint8)
+        N.check(N.lib().kfs_orb_download_level(self._h, frame, level, _ptr(out), w))
+        return out
+
+    def download_fast_corners(self, frame, level):
+        """-> int32 [n,3] rows (x, y, score), sorted by (y, x)."""
+        w, h, _, _ = self.level_info(level)
+        cap = max(16, (w // 2 + 2) * (h // 2 + 2))
+        out = np.zeros(cap, np.uint32)
+        n = C.c_int()
+        N.check(N.lib().kfs_orb_download_fast_corners(self._h, frame, level, _ptr(out), cap, C.byref(n)))
+        v = out[:n.value]
+        arr = np.stack([(v & 0xfff).astype(np.int32), ((v >> 12) & 0xfff).astype(np.int32), (v >> 24).astype(np.int32)], 1)
+        return arr[np.lexsort((arr[:, 0], arr[:, 1]))]
+
+    def set_profiling(self, on=True):
+        N.check(N.lib().kfs_orb_set_profiling(self._h, int(on)))
+
+    def stage_times(self):
+        ms = (C.c_float * len(N.STAGE_NAMES))()
+        N.check(N.lib().kfs_orb_stage_times(self._h, ms))
+        return dict(zip(N.STAGE_NAMES, [float(x) for x in ms]))
+
+    @property
+    def last_launches(self):
+        return N.lib().kfs_orb_last_launches(self._h)
+
+
+def ORB_create(nfeatures=500, scaleFactor=1.2, nlevels=8, edgeThreshold=31, firstLevel=0, WTA_K=2,
+               scoreType=ORB_HARRIS_SCORE, patchSize=31, fastThreshold=20, device=0):
+    """cv2.ORB_create / cv::ORB::create with the same positional arguments."""
+    return ORB(nfeatures, scaleFactor, nlevels, edgeThreshold, firstLevel, WTA_K, scoreType, patchSize, fastThreshold, device)
+
+
+class BFMatcher:
+    """cv::BFMatcher stand-in (NORM_HAMMING, crossCheck=false, k <= 2)."""
+
+    def __init__(self, normType=NORM_HAMMING, crossCheck=False, device=0):
+        self._h = C.c_void_p()
+        N.check(N.lib().kfs_bf_create(normType, int(crossCheck), device, C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            N.lib().kfs_bf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    @staticmethod
+    def _desc(a):
+        a = np.ascontiguousarray(a, dtype=np.uint8)
+        if a.size == 0:
+            return np.zeros((0, 32), np.uint8)
+        if a.ndim != 2 or a.shape[1] != 32:
+            raise ValueError("descriptors must be [n,32] uint8")
+        return a
+
+    def knnMatch(self, queryDescriptors, trainDescriptors, k=2):
+        """-> (matches[DM_DTYPE] shape [nq,k], counts int32[nq]); row q holds counts[q] = min(k, nt) entries."""
+        q, t = self._desc(queryDescriptors), self._desc(trainDescriptors)
+        out = np.zeros((len(q), k), DM_DTYPE)
+        counts = np.zeros(len(q), np.int32)
+        N.check(N.lib().kfs_bf_knn_match(self._h, _ptr(q), len(q), _ptr(t), len(t), k, _ptr(out), _ptr(counts)))
+        return out, counts
+
+    def knnMatchPairs(self, pairs, k=2):
+        """pairs: list of (query, train) host arrays -> list of (matches, counts); one launch for all pairs."""
+        qs = [self._desc(p[0]) for p in pairs]
+        ts = [self._desc(p[1]) for p in pairs]
+        # identical input arrays share one upload (window matching: one query set vs many train sets)
+        outs = [np.zeros((len(q), k), DM_DTYPE) for q in qs]
+        cnts = [np.zeros(len(q), np.int32) for q in qs]
+        arr = (N.BfPair * len(pairs))()
+        ids = {}
+        for i, (p, q, t) in enumerate(zip(pairs, qs, ts)):
+            kq, kt = id(p[0]), id(p[1])
+            q = ids.setdefault(("q", kq), q)
+            t = ids.setdefault(("t", kt), t)
+            arr[i] = N.BfPair(_ptr(q), len(q), None, _ptr(t), len(t), None, _ptr(outs[i]), _ptr(cnts[i]))
+        N.check(N.lib().kfs_bf_knn_match_pairs(self._h, arr, len(pairs), k))
+        return list(zip(outs, cnts))
+
+    def knnMatchPairsDevice(self, pairs, k=2):
+        """pairs: list of dict(query=ptr, nq=int, train=ptr, nt=int, out=ptr, counts=ptr|None, d_nq=ptr|None, d_nt=ptr|None)."""
+        arr = (N.BfPair * len(pairs))()
+        for i, p in enumerate(pairs):
+            arr[i] = N.BfPair(p["query"], p["nq"], p.get("d_nq"), p["train"], p["nt"], p.get("d_nt"), p["out"], p.get("counts"))
+        N.check(N.lib().kfs_bf_knn_match_pairs_device(self._h, arr, len(pairs), k))
+
+    def knnMatchRatio(self, queryDescriptors, trainDescriptors, ratio=0.6):
+        """knnMatch(k=2) + the reference's ratio test (VisualOdometry.cpp:46) fused on the device."""
+        q, t = self._desc(queryDescriptors), self._desc(trainDescriptors)
+        good = np.zeros(max(len(q), 1), DM_DTYPE)
+        n = C.c_int()
+        N.check(N.lib().kfs_bf_knn_match_ratio(self._h, _ptr(q), len(q), _ptr(t), len(t), ratio, _ptr(good), C.byref(n)))
+        return good[:n.value].copy()
+
+    def set_stream(self, cuda_stream):
+        N.check(N.lib().kfs_bf_set_stream(self._h, cuda_stream))
+
+    def sync(self):
+        N.check(N.lib().kfs_bf_sync(self._h))
+
+    @property
+    def last_launches(self):
+        return N.lib().kfs_bf_last_launches(self._h)
+
+
+def BFMatcher_create(normType=NORM_HAMMING, crossCheck=False, device=0):
+    """cv2.BFMatcher_create / cv::BFMatcher::create."""
+    return BFMatcher(normType, crossCheck, device)
+
+
+def pipe_peak(device=0, what="popc"):
+    """Measured integer-pipe issue rate in 1e9 ops/s (what = 'popc' | 'lop3'); matcher roofline denominator."""
+    g = C.c_double()
+    N.check(N.lib().kfs_pipe_peak(device, 0 if what == "popc" else 1, C.byref(g)))
+    return g.value

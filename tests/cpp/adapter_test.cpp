@@ -1,0 +1,72 @@
+// tests/cpp/adapter_test.cpp — drives the C++ drop-in exactly the way the reference tracker drives OpenCV
+// (VisualOdometry.cpp:10-18 construction, :30 detectAndCompute, :39 knnMatch, :46 ratio test) and dumps the
+// results for the Python test to compare with the golden vectors.  Usage:
+//   adapter_test <w> <h> <nfeatures> <frameA.raw> <frameB.raw> <out.bin>     (needs a GPU)
+//   adapter_test --abi-only                                                  (no GPU: construction must fail loudly)
+#include "kfslam_frontend_cv.hpp"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+
+static std::vector<uint8_t> slurp(const char *path)
+{
+    std::ifstream f(path, std::ios::binary);
+    return std::vector<uint8_t>((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+}
+
+int main(int argc, char **argv)
+{
+    if (argc == 2 && !std::strcmp(argv[1], "--abi-only")) {
+        std::printf("kfs_version=%d devices=%d\n", kfs_version(), kfs_device_count());
+        if (kfs_device_count() == 0) {
+            try { kfs::ORB::create(3000, 1.2f, 8, 31, 0, 2, kfs::ORB::HARRIS_SCORE, 31, 20); }
+            catch (const cv::Exception &e) { std::printf("no device -> cv::Exception: %s\n", e.what()); return 0; }
+            return 2; // must not silently fall back to a CPU path
+        }
+        return 0;
+    }
+    if (argc != 7) { std::fprintf(stderr, "usage\n"); return 64; }
+    const int w = std::atoi(argv[1]), h = std::atoi(argv[2]), nf = std::atoi(argv[3]);
+    auto a = slurp(argv[4]), b = slurp(argv[5]);
+    if ((int)a.size() != w * h || (int)b.size() != w * h) { std::fprintf(stderr, "bad frame size\n"); return 65; }
+
+    // --- the reference's constructor body (VisualOdometry.cpp:10-18), types swapped for the drop-in
+    cv::Ptr<kfs::ORB> ptrExtractor = kfs::ORB::create(nf, 1.2f, 8, 31, 0, 2, kfs::ORB::HARRIS_SCORE, 31, 20);
+    cv::Ptr<kfs::BFMatcher> ptrMatcher = kfs::BFMatcher::create(cv::NORM_HAMMING);
+
+    // --- ExtractFeatures (VisualOdometry.cpp:21-33) on the keyframe and on the current frame
+    cv::Mat grayA(h, w, cv::CV_8UC1, a.data()), grayB(h, w, cv::CV_8UC1, b.data()), mask;
+    std::vector<cv::KeyPoint> kpA, kpB;
+    cv::Mat dpA, dpB;
+    ptrExtractor->detectAndCompute(grayA, mask, kpA, dpA);
+    ptrExtractor->detectAndCompute(grayB, mask, kpB, dpB);
+
+    // --- MatchFeatures (VisualOdometry.cpp:35-62): query = keyframe, train = current; ratio 0.6
+    std::vector<std::vector<cv::DMatch>> knnMatches;
+    ptrMatcher->knnMatch(dpA, dpB, knnMatches, 2);
+    std::vector<cv::DMatch> matches;
+    for (size_t i = 0; i < knnMatches.size(); i++)
+        if (knnMatches[i].size() >= 2 && knnMatches[i][0].distance < 0.6f * knnMatches[i][1].distance) matches.push_back(knnMatches[i][0]);
+
+    // --- error behaviour: unsupported options throw like OpenCV
+    int threw = 0;
+    try { kfs::ORB::create(500, 1.2f, 8, 31, 0, 4); } catch (const cv::Exception &) { threw++; }
+    try { kfs::BFMatcher::create(cv::NORM_L2); } catch (const cv::Exception &) { threw++; }
+    cv::Mat empty; std::vector<cv::KeyPoint> kpE; cv::Mat dpE;
+    ptrExtractor->detectAndCompute(empty, mask, kpE, dpE);
+    if (!kpE.empty() || !dpE.empty()) threw = -100;
+
+    std::ofstream out(argv[6], std::ios::binary);
+    auto put32 = [&](int v) { out.write((const char *)&v, 4); };
+    put32((int)kpA.size()); put32((int)kpB.size()); put32((int)knnMatches.size()); put32((int)matches.size()); put32(threw);
+    out.write((const char *)kpA.data(), (std::streamsize)(kpA.size() * sizeof(cv::KeyPoint)));
+    for (int r = 0; r < dpA.rows; r++) out.write((const char *)dpA.ptr(r), 32);
+    out.write((const char *)kpB.data(), (std::streamsize)(kpB.size() * sizeof(cv::KeyPoint)));
+    for (int r = 0; r < dpB.rows; r++) out.write((const char *)dpB.ptr(r), 32);
+    for (auto &row : knnMatches) { put32((int)row.size()); out.write((const char *)row.data(), (std::streamsize)(row.size() * sizeof(cv::DMatch))); }
+    out.write((const char *)matches.data(), (std::streamsize)(matches.size() * sizeof(cv::DMatch)));
+    std::printf("kpA=%zu kpB=%zu knn=%zu good=%zu threw=%d\n", kpA.size(), kpB.size(), knnMatches.size(), matches.size(), threw);
+    return 0;
+}
