@@ -6,6 +6,6 @@ and the synthetic frame source (synth).  Import as
     kfs = importlib.import_module("keyframe-based-slam_b200")
 (the directory name is not a Python identifier; `kfslam_b200.py` at the repo root re-exports it).
 """
-from . import _native, synth  # noqa: F401
+from . import _native, replay, synth  # noqa: F401
 from ._native import KP_DTYPE, DM_DTYPE, NORM_HAMMING, ORB_HARRIS_SCORE, KfsError, build, lib  # noqa: F401
 from .frontend import ORB, ORB_create, BFMatcher, BFMatcher_create, pipe_peak  # noqa: F401
