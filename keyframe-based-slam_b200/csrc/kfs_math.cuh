@@ -86,11 +86,13 @@ KFS_HD int kfs_fast9_m(const uint32_t e[16])
 // (bit 31) is set iff pixel a (b) MAY be a corner.
 KFS_HD uint32_t kfs_fast_quick2(uint32_t V, uint32_t U, uint32_t D, uint32_t R, uint32_t L, int thr)
 {
-    uint32_t T = (uint32_t)(thr + 1) * 0x10001u;
+    // per half: q + (0x8000 - t - 1) - v  >= 0x8000  <=>  q > v + t ;  v + (0x8000 - t - 1) - r >= 0x8000  <=>  r < v - t
+    // (each half stays in [0x8000 - 511, 0x8000 + 254]: no borrow/carry crosses the halves)
+    const uint32_t K = 0x80008000u - (uint32_t)(thr + 1) * 0x10001u;
     uint32_t q = kfs_min2(kfs_max2(U, D), kfs_max2(R, L));   // bright side
     uint32_t r = kfs_max2(kfs_min2(U, D), kfs_min2(R, L));   // dark side
-    uint32_t X = (q | 0x80008000u) - (V + T);                // half >= 0x8000  <=>  q - v - t - 1 >= 0
-    uint32_t Y = ((V | 0x80008000u) - T) - r;                // half >= 0x8000  <=>  v - t - 1 - r >= 0
+    uint32_t X = q + K - V;
+    uint32_t Y = V + K - r;
     return (X | Y) & 0x80008000u;
 }
 

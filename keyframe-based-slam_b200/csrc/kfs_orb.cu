@@ -106,110 +106,94 @@ k_mask_binarise(const uint8_t *__restrict__ src, long long sfs, long long sstep,
 // ======================================================================================================
 // a1.3 / a1.4  FAST-9/16 score + 3x3 NMS + border / mask filter -> per-(frame, level) corner list
 // ======================================================================================================
-// One CTA = one 64x32 tile of the keepable region [31, W-31) x [31, H-31) of one level of one frame.
-//   source tile 80 x 40 bytes, origin (tx0-8, ty0-4), 16-byte aligned rows -> uint4 loads
-//   score  tile 72 x 34 bytes, origin (tx0-4, ty0-1)
-// phase 1: necessary-condition test on 4 pixels per thread (u16x2 SIMD, two pixels per op); survivors are
-//          compacted into a shared-memory queue by warp ballot + popc prefix
+// One CTA = one 120x62 tile of the keepable region [31, W-31) x [31, H-31) of one level of one frame
+// (tile -> (level, tix, tiy) through a table, so one launch covers every level of every frame).
+//   source tile 136 x 70 bytes (pitch 144), origin (tx0-8, ty0-4), 8-byte aligned rows -> uint2 loads
+//   score  tile 128 x 64 bytes,             origin (tx0-4, ty0-1)
+// phase 1: each warp owns score rows w, w+8, ...; a lane tests 4 horizontally adjacent pixels with the
+//          necessary condition kfs_fast_quick2 (u16x2 SIMD, two pixels per op, conflict-free LDS.32); rows
+//          where no lane passes cost one vote and nothing else; survivors are compacted into a shared queue
+//          by ballot + popc prefix with one shared atomic per warp-row
 // phase 2: exact score of the queued pixels (both polarities in one u16x2 word, VIMNMX3 trees)
-// phase 3: 3x3 NMS on the score tile, border/mask predicate, block-aggregated append to the global list
-constexpr int FT_W = 64, FT_H = 32;
-constexpr int FS_W = 80, FS_H = FT_H + 8;
-constexpr int SC_W = 72, SC_H = FT_H + 2;
-constexpr int FQ_PER_ROW = SC_W / 4;
-constexpr int NQUAD = FQ_PER_ROW * SC_H;
-constexpr int FAST_X0 = 24; // interior x origin of tile column 0; source origin 16 keeps rows 16B-aligned
+// phase 3: 3x3 NMS on the score tile, border/mask predicate, warp-aggregated append to the global list
+constexpr int FT_W = 120, FT_H = 62;
+constexpr int FS_W = 136, FS_P = 144, FS_H = FT_H + 8;
+constexpr int SC_W = 128, SC_H = FT_H + 2;
+constexpr int FAST_X0 = 24; // interior x origin of tile column 0; source origin 16 (+120k) keeps rows 8B-aligned
 constexpr int FAST_THREADS = 256;
-constexpr int FAST_EMIT_CAP = (FT_W / 2) * (FT_H / 2);
 
 __global__ void __launch_bounds__(FAST_THREADS)
-k_fast(const __grid_constant__ OrbDev g)
+k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
 {
-    __shared__ __align__(16) uint8_t s_src[FS_W * FS_H];
+    __shared__ __align__(16) uint8_t s_src[FS_P * FS_H];
     __shared__ __align__(16) uint8_t s_sc[SC_W * SC_H];
     __shared__ uint16_t s_q[SC_W * SC_H];
-    __shared__ uint32_t s_emit[FAST_EMIT_CAP];
-    __shared__ int s_nq, s_nemit, s_gbase;
+    __shared__ int s_nq;
 
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int f = blockIdx.y;
-    int l = 0;
-    {
-        const int t = blockIdx.x;
-#pragma unroll 1
-        for (int i = 1; i < g.nlevels; i++)
-            if (t >= g.lv[i].tile_base && g.lv[i].tiles_x > 0) l = i;
-    }
+    const uint32_t tt = __ldg(tile_tab + blockIdx.x);
+    const int l = tt >> 24, tiy = (tt >> 12) & 0xfff, tix = tt & 0xfff;
     const LevelDev &L = g.lv[l];
-    const int trel = blockIdx.x - L.tile_base;
-    const int tix = trel % L.tiles_x, tiy = trel / L.tiles_x;
     const int W = L.w, H = L.h, pitch = L.pitch;
     const int tx0 = FAST_X0 + FT_W * tix, ty0 = KFS_BORDER + FT_H * tiy;
     const int sx0 = tx0 - 8, sy0 = ty0 - 4;
     const uint8_t *img = L.img + (long long)f * L.img_fs;
     const int thr = g.fast_thr;
 
-    // ---- load the source tile (uint4 per thread), clear the score tile
-    for (int i = tid; i < FS_H * (FS_W / 16); i += FAST_THREADS) {
-        const int r = i / (FS_W / 16), c = i % (FS_W / 16);
-        const int gy = min(max(sy0 + r, 0), H - 1), gx = sx0 + 16 * c;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
-        *reinterpret_cast<uint4 *>(s_src + r * FS_W + 16 * c) = v;
+    // ---- load the source tile (uint2 per thread), clear the score tile
+    for (int i = tid; i < FS_H * (FS_W / 8); i += FAST_THREADS) {
+        const int r = i / (FS_W / 8), c = i - r * (FS_W / 8);
+        const int gy = min(max(sy0 + r, 0), H - 1), gx = sx0 + 8 * c;
+        uint2 v = make_uint2(0, 0);
+        if (gx + 8 <= pitch) v = __ldg(reinterpret_cast<const uint2 *>(img + (long long)gy * pitch + gx));
+        *reinterpret_cast<uint2 *>(s_src + r * FS_P + 8 * c) = v;
     }
-    for (int i = tid; i < SC_W * SC_H / 4; i += FAST_THREADS) reinterpret_cast<uint32_t *>(s_sc)[i] = 0;
-    if (tid == 0) { s_nq = 0; s_nemit = 0; }
+    for (int i = tid; i < SC_W * SC_H / 16; i += FAST_THREADS) reinterpret_cast<uint4 *>(s_sc)[i] = make_uint4(0, 0, 0, 0);
+    if (tid == 0) s_nq = 0;
     __syncthreads();
 
-    // ---- phase 1: quick reject, 4 pixels per thread per iteration
-    // x range whose score this tile needs: [tx0-1, tx0+64] clipped to [30, W-31]; y likewise
+    // ---- phase 1: quick reject, one score row per warp-iteration, 4 pixels per lane
+    // x range whose score this tile needs: [tx0-1, tx0+120] clipped to [30, W-31]; y likewise
     const int xlo = max(tx0 - 1, KFS_BORDER - 1), xhi = min(tx0 + FT_W, W - KFS_BORDER);
     const int ylo = max(ty0 - 1, KFS_BORDER - 1), yhi = min(ty0 + FT_H, H - KFS_BORDER);
-#pragma unroll 1
-    for (int it = 0; it < (NQUAD + FAST_THREADS - 1) / FAST_THREADS; it++) {
-        const int qi = it * FAST_THREADS + tid;
-        uint32_t pass4 = 0;
-        int qr = 0, qc = 0;
-        if (qi < NQUAD) {
-            qr = qi / FQ_PER_ROW;
-            qc = qi - qr * FQ_PER_ROW;
-            const int x = tx0 - 4 + 4 * qc, y = ty0 - 1 + qr;
-            uint32_t vm = 0;
-            if (y >= ylo && y <= yhi) {
-#pragma unroll
-                for (int j = 0; j < 4; j++) vm |= (uint32_t)(x + j >= xlo && x + j <= xhi) << j;
-            }
-            if (vm) {
-                const uint8_t *rowc = s_src + (qr + 3) * FS_W + 4 + 4 * qc;
-                const uint32_t B = *reinterpret_cast<const uint32_t *>(rowc);
-                const uint32_t A = *reinterpret_cast<const uint32_t *>(rowc - 4);
-                const uint32_t C = *reinterpret_cast<const uint32_t *>(rowc + 4);
-                const uint32_t U = *reinterpret_cast<const uint32_t *>(rowc - 3 * FS_W);
-                const uint32_t D = *reinterpret_cast<const uint32_t *>(rowc + 3 * FS_W);
-                const uint32_t Rw = __funnelshift_r(B, C, 24); // pixels x+3 .. x+6
-                const uint32_t Lw = __funnelshift_r(A, B, 8);  // pixels x-3 .. x
-                const uint32_t M = 0x00ff00ffu;
-                const uint32_t me = kfs_fast_quick2(B & M, U & M, D & M, Rw & M, Lw & M, thr);
-                const uint32_t mo = kfs_fast_quick2((B >> 8) & M, (U >> 8) & M, (D >> 8) & M, (Rw >> 8) & M, (Lw >> 8) & M, thr);
-                pass4 = ((me >> 15) & 1u) | (((mo >> 15) & 1u) << 1) | (((me >> 31) & 1u) << 2) | (((mo >> 31) & 1u) << 3);
-                pass4 &= vm;
-            }
-        }
-        const uint32_t b0 = __ballot_sync(0xffffffffu, pass4 & 1u), b1 = __ballot_sync(0xffffffffu, pass4 & 2u);
-        const uint32_t b2 = __ballot_sync(0xffffffffu, pass4 & 4u), b3 = __ballot_sync(0xffffffffu, pass4 & 8u);
+    uint32_t vme = 0, vmo = 0; // validity of this lane's 4 pixels, in kfs_fast_quick2's result bit positions
+    {
+        const int x = tx0 - 4 + 4 * lane;
+        if (x + 0 >= xlo && x + 0 <= xhi) vme |= 0x00008000u;
+        if (x + 2 >= xlo && x + 2 <= xhi) vme |= 0x80000000u;
+        if (x + 1 >= xlo && x + 1 <= xhi) vmo |= 0x00008000u;
+        if (x + 3 >= xlo && x + 3 <= xhi) vmo |= 0x80000000u;
+    }
+    const int sy_lo = max(ylo - (ty0 - 1), 0), sy_hi = min(yhi - (ty0 - 1), SC_H - 1);
+#pragma unroll 2
+    for (int sy = sy_lo + warp; sy <= sy_hi; sy += FAST_THREADS / 32) {
+        const uint8_t *rowc = s_src + (sy + 3) * FS_P + 4 + 4 * lane;
+        const uint32_t B = *reinterpret_cast<const uint32_t *>(rowc);
+        const uint32_t A = *reinterpret_cast<const uint32_t *>(rowc - 4);
+        const uint32_t C = *reinterpret_cast<const uint32_t *>(rowc + 4);
+        const uint32_t U = *reinterpret_cast<const uint32_t *>(rowc - 3 * FS_P);
+        const uint32_t D = *reinterpret_cast<const uint32_t *>(rowc + 3 * FS_P);
+        const uint32_t Rw = __funnelshift_r(B, C, 24); // pixels x+3 .. x+6
+        const uint32_t Lw = __funnelshift_r(A, B, 8);  // pixels x-3 .. x
+        // even bytes -> (px0, px2), odd bytes -> (px1, px3) as u16x2
+        const uint32_t me = vme & kfs_fast_quick2(__byte_perm(B, 0, 0x4240), __byte_perm(U, 0, 0x4240), __byte_perm(D, 0, 0x4240),
+                                                  __byte_perm(Rw, 0, 0x4240), __byte_perm(Lw, 0, 0x4240), thr);
+        const uint32_t mo = vmo & kfs_fast_quick2(__byte_perm(B, 0, 0x4341), __byte_perm(U, 0, 0x4341), __byte_perm(D, 0, 0x4341),
+                                                  __byte_perm(Rw, 0, 0x4341), __byte_perm(Lw, 0, 0x4341), thr);
+        if (!__any_sync(0xffffffffu, (me | mo) != 0u)) continue;
+        const uint32_t b0 = __ballot_sync(0xffffffffu, me & 0x00008000u), b1 = __ballot_sync(0xffffffffu, mo & 0x00008000u);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, me & 0x80000000u), b3 = __ballot_sync(0xffffffffu, mo & 0x80000000u);
         const int c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
-        const int tot = c0 + c1 + c2 + c3;
-        if (tot) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(&s_nq, tot);
-            base = __shfl_sync(0xffffffffu, base, 0);
-            const uint32_t lt = (1u << lane) - 1u;
-            const int pi = qr * SC_W + 4 * qc;
-            if (pass4 & 1u) s_q[base + __popc(b0 & lt)] = (uint16_t)(pi);
-            if (pass4 & 2u) s_q[base + c0 + __popc(b1 & lt)] = (uint16_t)(pi + 1);
-            if (pass4 & 4u) s_q[base + c0 + c1 + __popc(b2 & lt)] = (uint16_t)(pi + 2);
-            if (pass4 & 8u) s_q[base + c0 + c1 + c2 + __popc(b3 & lt)] = (uint16_t)(pi + 3);
-        }
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&s_nq, c0 + c1 + c2 + c3);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        const uint32_t lt = (1u << lane) - 1u;
+        const int pi = sy * SC_W + 4 * lane;
+        if (me & 0x00008000u) s_q[base + __popc(b0 & lt)] = (uint16_t)(pi);
+        if (mo & 0x00008000u) s_q[base + c0 + __popc(b1 & lt)] = (uint16_t)(pi + 1);
+        if (me & 0x80000000u) s_q[base + c0 + c1 + __popc(b2 & lt)] = (uint16_t)(pi + 2);
+        if (mo & 0x80000000u) s_q[base + c0 + c1 + c2 + __popc(b3 & lt)] = (uint16_t)(pi + 3);
     }
     __syncthreads();
     const int nq = s_nq;
@@ -217,25 +201,27 @@ k_fast(const __grid_constant__ OrbDev g)
     // ---- phase 2: exact score of queued pixels
     for (int e = tid; e < nq; e += FAST_THREADS) {
         const int pi = s_q[e];
-        const int sy = pi / SC_W, sx = pi - sy * SC_W;
-        const uint8_t *c = s_src + (sy + 3) * FS_W + sx + 4;
+        const int sy = pi >> 7, sx = pi & (SC_W - 1);
+        const uint8_t *c = s_src + (sy + 3) * FS_P + sx + 4;
         const uint32_t cv = kfs_fast_cv(c[0]);
         uint32_t ek[16];
-        ek[0] = kfs_fast_e(cv, c[3 * FS_W + 0]);   ek[1] = kfs_fast_e(cv, c[3 * FS_W + 1]);
-        ek[2] = kfs_fast_e(cv, c[2 * FS_W + 2]);   ek[3] = kfs_fast_e(cv, c[1 * FS_W + 3]);
-        ek[4] = kfs_fast_e(cv, c[3]);              ek[5] = kfs_fast_e(cv, c[-1 * FS_W + 3]);
-        ek[6] = kfs_fast_e(cv, c[-2 * FS_W + 2]);  ek[7] = kfs_fast_e(cv, c[-3 * FS_W + 1]);
-        ek[8] = kfs_fast_e(cv, c[-3 * FS_W + 0]);  ek[9] = kfs_fast_e(cv, c[-3 * FS_W - 1]);
-        ek[10] = kfs_fast_e(cv, c[-2 * FS_W - 2]); ek[11] = kfs_fast_e(cv, c[-1 * FS_W - 3]);
-        ek[12] = kfs_fast_e(cv, c[-3]);            ek[13] = kfs_fast_e(cv, c[1 * FS_W - 3]);
-        ek[14] = kfs_fast_e(cv, c[2 * FS_W - 2]);  ek[15] = kfs_fast_e(cv, c[3 * FS_W - 1]);
+        ek[0] = kfs_fast_e(cv, c[3 * FS_P + 0]);   ek[1] = kfs_fast_e(cv, c[3 * FS_P + 1]);
+        ek[2] = kfs_fast_e(cv, c[2 * FS_P + 2]);   ek[3] = kfs_fast_e(cv, c[1 * FS_P + 3]);
+        ek[4] = kfs_fast_e(cv, c[3]);              ek[5] = kfs_fast_e(cv, c[-1 * FS_P + 3]);
+        ek[6] = kfs_fast_e(cv, c[-2 * FS_P + 2]);  ek[7] = kfs_fast_e(cv, c[-3 * FS_P + 1]);
+        ek[8] = kfs_fast_e(cv, c[-3 * FS_P + 0]);  ek[9] = kfs_fast_e(cv, c[-3 * FS_P - 1]);
+        ek[10] = kfs_fast_e(cv, c[-2 * FS_P - 2]); ek[11] = kfs_fast_e(cv, c[-1 * FS_P - 3]);
+        ek[12] = kfs_fast_e(cv, c[-3]);            ek[13] = kfs_fast_e(cv, c[1 * FS_P - 3]);
+        ek[14] = kfs_fast_e(cv, c[2 * FS_P - 2]);  ek[15] = kfs_fast_e(cv, c[3 * FS_P - 1]);
         const int m = kfs_fast9_m(ek);
         if (m > thr) s_sc[pi] = (uint8_t)(m - 1);
     }
     __syncthreads();
 
-    // ---- phase 3: NMS + border/mask filter + emit
+    // ---- phase 3: NMS + border/mask filter + warp-aggregated append to the (frame, level) list
     const uint8_t *mask = L.mask ? L.mask + (long long)f * L.mask_fs : nullptr;
+    uint32_t *out = g.raw + (long long)f * g.list_fs + L.list_off;
+    int *gcount = g.raw_count + f * KFS_MAX_LEVELS + l;
     for (int e0 = 0; e0 < nq; e0 += FAST_THREADS) {
         const int e = e0 + tid;
         uint32_t packed = 0;
@@ -243,7 +229,7 @@ k_fast(const __grid_constant__ OrbDev g)
         if (e < nq) {
             const int pi = s_q[e];
             const int s = s_sc[pi];
-            const int sy = pi / SC_W, sx = pi - sy * SC_W;
+            const int sy = pi >> 7, sx = pi & (SC_W - 1);
             const int x = tx0 - 4 + sx, y = ty0 - 1 + sy;
             if (s > 0 && sx >= 4 && sx < 4 + FT_W && sy >= 1 && sy <= FT_H &&
                 x >= KFS_BORDER && x < W - KFS_BORDER && y >= KFS_BORDER && y < H - KFS_BORDER) {
@@ -257,20 +243,12 @@ k_fast(const __grid_constant__ OrbDev g)
         const uint32_t bk = __ballot_sync(0xffffffffu, keep);
         if (bk) {
             int base = 0;
-            if (lane == 0) base = atomicAdd(&s_nemit, __popc(bk));
+            if (lane == 0) base = atomicAdd(gcount, __popc(bk));
             base = __shfl_sync(0xffffffffu, base, 0);
-            if (keep) s_emit[base + __popc(bk & ((1u << lane) - 1u))] = packed;
+            const int slot = base + __popc(bk & ((1u << lane) - 1u));
+            if (keep && slot < L.list_cap) out[slot] = packed;
         }
     }
-    __syncthreads();
-    const int ne = s_nemit;
-    if (ne == 0) return;
-    if (tid == 0) s_gbase = atomicAdd(g.raw_count + f * KFS_MAX_LEVELS + l, ne);
-    __syncthreads();
-    const int gbase = s_gbase;
-    uint32_t *out = g.raw + (long long)f * g.list_fs + L.list_off;
-    for (int i = tid; i < ne; i += FAST_THREADS)
-        if (gbase + i < L.list_cap) out[gbase + i] = s_emit[i];
 }
 
 // ======================================================================================================
@@ -647,6 +625,7 @@ struct kfs_orb {
     void *arena = nullptr;          // one cudaMalloc for everything above and below
     size_t arena_bytes = 0;
     int *counters = nullptr;        // raw_count | cand_count | kept_count | n_out
+    uint32_t *tile_tab = nullptr;   // FAST tile -> level<<24 | tiy<<12 | tix
     size_t counters_bytes = 0;
     OrbDev g;
     int last_batch = 0;
@@ -728,6 +707,10 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     const size_t o_raw = take(lists * 4), o_cxy = take(lists * 4), o_cr = take(lists * 4), o_kxy = take(lists * 4), o_kr = take(lists * 4);
     const size_t cnt_bytes = ((size_t)batch * KFS_MAX_LEVELS * 3 + (size_t)batch) * sizeof(int);
     const size_t o_cnt = take(cnt_bytes);
+    int n_tiles_total = 0;
+    for (int l = 0; l < L; l++)
+        if (list_cap[l] > 0) n_tiles_total += kfs_div_up(o->lw[l] - KFS_BORDER - FAST_X0, FT_W) * kfs_div_up(o->lh[l] - 2 * KFS_BORDER, FT_H);
+    const size_t o_tt = take((size_t)(n_tiles_total + 1) * 4);
     const size_t outs = (size_t)batch * o->cap_out;
     const size_t o_kp = take(outs * sizeof(kfs_keypoint)), o_desc = take(outs * 32), o_rot = take(outs * sizeof(float2)), o_meta = take(outs * 4);
     KFS_CUDA_TRY(cudaMalloc(&o->arena, off));
@@ -744,7 +727,8 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     g.kept_count = g.cand_count + (size_t)batch * KFS_MAX_LEVELS; g.n_out = g.kept_count + (size_t)batch * KFS_MAX_LEVELS;
     g.kp = (kfs_keypoint *)(base + o_kp); g.desc = base + o_desc; g.rot = (float2 *)(base + o_rot); g.slot_meta = (uint32_t *)(base + o_meta);
     int tile_base = 0;
-    std::vector<uint32_t> tab;
+    std::vector<uint32_t> tab, ttab;
+    o->tile_tab = (uint32_t *)(base + o_tt);
     for (int l = 0; l < L; l++) {
         o->pyr[l] = base + o_pyr[l];
         o->mpyr[l] = need_mask ? base + o_mpyr[l] : nullptr;
@@ -761,6 +745,8 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
         } else { D.tiles_x = 0; D.tiles_y = 0; }
         D.tile_base = tile_base;
         tile_base += D.tiles_x * D.tiles_y;
+        for (int ty = 0; ty < D.tiles_y; ty++)
+            for (int tx = 0; tx < D.tiles_x; tx++) ttab.push_back(((uint32_t)l << 24) | ((uint32_t)ty << 12) | (uint32_t)tx);
         if (l > 0) {
             kfs_axis_table(o->lw[l - 1], o->lw[l], (int)kfs_align_up((size_t)o->lw[l], 4), tab);
             KFS_CUDA_TRY(cudaMemcpyAsync(o->xtab[l], tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, o->stream));
@@ -771,6 +757,10 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
         }
     }
     g.total_tiles = tile_base;
+    if (!ttab.empty()) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(o->tile_tab, ttab.data(), ttab.size() * 4, cudaMemcpyHostToDevice, o->stream));
+        KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    }
     if (o->h_counts) { cudaFreeHost(o->h_counts); o->h_counts = nullptr; }
     KFS_CUDA_TRY(cudaMallocHost(&o->h_counts, sizeof(int) * (size_t)batch));
     o->W = w; o->H = h; o->B = batch; o->has_mask_alloc = need_mask;
@@ -824,7 +814,7 @@ static kfs_status kfs_orb_run(kfs_orb *o, int batch, const uint8_t *d_mask_in, s
     }
     if (kfs_stage_mark(o, KFS_STAGE_FAST)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
-        k_fast<<<dim3(g.total_tiles, batch), FAST_THREADS, 0, st>>>(g);
+        k_fast<<<dim3(g.total_tiles, batch), FAST_THREADS, 0, st>>>(g, o->tile_tab);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_SELECT_HARRIS)) return KFS_ERR_CUDA;
