@@ -5,7 +5,7 @@
 // 256-bit XOR; per query the K smallest in ascending order, ties -> lower trainIdx first; rows hold
 // min(K, Nt) entries; Nt < 2^18.
 //
-// This is integer work: XOR + POPC + add on the ALU/POPC pipes, no tensor cores.  Query descriptors live in
+// This is integer work: XOR / LOP3 on the ALU pipe + POPC on the XU pipe, no tensor cores.  Query descriptors live in
 // registers (QPT per thread), train descriptors are streamed through shared memory in double-buffered
 // chunks (cp.async), every lane of a warp reads the same train row (broadcast LDS.128), and the running
 // top-2 is kept as two packed keys  dist << 18 | trainIdx  so that a plain unsigned min reproduces
@@ -19,9 +19,9 @@
 
 constexpr int BF_THREADS = 256;
 constexpr int BF_QPT = 4;                       // queries per thread
-constexpr int BF_TSPLIT = 4;                    // warp groups scanning disjoint train slices
+constexpr int BF_TSPLIT = 8;                    // warp groups scanning disjoint train slices
 constexpr int BF_QWARPS = BF_THREADS / 32 / BF_TSPLIT;
-constexpr int BF_QTILE = BF_QWARPS * 32 * BF_QPT; // 256 queries per CTA
+constexpr int BF_QTILE = BF_QWARPS * 32 * BF_QPT; // 128 queries per CTA
 constexpr int BF_CHUNK = 512;                   // train rows per smem stage (16 KB)
 constexpr int BF_SLICE = BF_CHUNK / BF_TSPLIT;  // rows one warp group scans per stage
 constexpr uint32_t BF_INF = 0xffffffffu;
@@ -40,6 +40,19 @@ __device__ __forceinline__ void bf_cp_async16(void *smem, const void *gmem)
 }
 __device__ __forceinline__ void bf_cp_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 template <int N> __device__ __forceinline__ void bf_cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+__device__ __forceinline__ uint32_t bf_xor3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t bf_maj(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xe8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
 
 __device__ __forceinline__ void bf_top2_insert(uint32_t key, uint32_t &b1, uint32_t &b2)
 {
@@ -98,8 +111,18 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k)
             const uint32_t tkey = (uint32_t)(base + j);
 #pragma unroll
             for (int r = 0; r < BF_QPT; r++) {
-                const int d = __popc(q[r][0] ^ ta.x) + __popc(q[r][1] ^ ta.y) + __popc(q[r][2] ^ ta.z) + __popc(q[r][3] ^ ta.w) +
-                              __popc(q[r][4] ^ tb.x) + __popc(q[r][5] ^ tb.y) + __popc(q[r][6] ^ tb.z) + __popc(q[r][7] ^ tb.w);
+                // 256-bit Hamming distance with a carry-save (Harley-Seal) front end: 8 XOR words are compressed by
+                // three full adders (2 LOP3 each, ALU pipe) so that only 5 POPC (XU pipe, 16/clk/SM) are needed:
+                //   x0+x1+x2 = s0 + 2 c0;  x3+x4+x5 = s1 + 2 c1;  s0+s1+x6 = s2 + 2 c2
+                //   popc(all) = popc(s2) + popc(x7) + 2 (popc(c0) + popc(c1) + popc(c2))
+                const uint32_t x0 = q[r][0] ^ ta.x, x1 = q[r][1] ^ ta.y, x2 = q[r][2] ^ ta.z, x3 = q[r][3] ^ ta.w;
+                const uint32_t x4 = q[r][4] ^ tb.x, x5 = q[r][5] ^ tb.y, x6 = q[r][6] ^ tb.z, x7 = q[r][7] ^ tb.w;
+                const uint32_t s0 = bf_xor3(x0, x1, x2), c0 = bf_maj(x0, x1, x2);
+                const uint32_t s1 = bf_xor3(x3, x4, x5), c1 = bf_maj(x3, x4, x5);
+                const uint32_t s2 = bf_xor3(s0, s1, x6), c2 = bf_maj(s0, s1, x6);
+                const uint32_t ones = __popc(s2) + __popc(x7);
+                const uint32_t twos = __popc(c0) + __popc(c1) + __popc(c2);
+                const uint32_t d = ones + 2u * twos;
                 bf_top2_insert(((uint32_t)d << 18) + tkey, b1[r], b2[r]);
             }
         }

@@ -6,7 +6,7 @@
 //
 // Kernel chain per batch:
 //   k_mask_binarise*  k_resize x(L-1) [x2 with a mask]  k_fast  k_select_fast  k_harris  k_select_sort
-//   k_orient  k_describe
+//   k_describe (orientation + blur + rBRIEF)
 #include "kfs_common.cuh"
 #include "kfs_math.cuh"
 #include <math.h>
@@ -363,22 +363,22 @@ k_harris(const __grid_constant__ OrbDev g)
 // exact quota-th largest; everything >= it is kept; the rank of a kept entry among kept entries by
 // (y<<12|x) is its output position.
 constexpr int SORT_THREADS = 512;
-constexpr int SORT_SMEM_N = 4096;
+// dynamic shared memory: key[N] | pos[N] | cpos[N] | cidx[N]  (u32 each), N = smem_n (host: 2*max quota + slack)
 __global__ void __launch_bounds__(SORT_THREADS)
-k_select_sort(const __grid_constant__ OrbDev g)
+k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
 {
-    __shared__ uint32_t s_key[SORT_SMEM_N];
-    __shared__ uint32_t s_pos[SORT_SMEM_N];
+    extern __shared__ __align__(16) uint32_t s_dyn[];
+    uint32_t *s_key = s_dyn, *s_pos = s_dyn + smem_n, *s_cpos = s_dyn + 2 * smem_n, *s_cidx = s_dyn + 3 * smem_n;
     __shared__ int s_hist[256];
     __shared__ uint32_t s_prefix;
     __shared__ int s_need, s_nkept;
-    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
     const LevelDev &L = g.lv[l];
     if (L.list_cap == 0) return;
     const int n = min(g.cand_count[f * KFS_MAX_LEVELS + l], L.list_cap);
     const uint32_t *cand = g.cand_xy + (long long)f * g.list_fs + L.list_off;
     const float *resp = g.cand_resp + (long long)f * g.list_fs + L.list_off;
-    const bool in_smem = n <= SORT_SMEM_N;
+    const bool in_smem = n <= smem_n;
     if (in_smem)
         for (int i = tid; i < n; i += SORT_THREADS) { s_key[i] = kfs_float_key(resp[i]); s_pos[i] = cand[i] & 0xffffffu; }
     if (tid == 0) { s_prefix = 0; s_need = L.quota; s_nkept = 0; }
@@ -397,13 +397,27 @@ k_select_sort(const __grid_constant__ OrbDev g)
                 if ((k & hi_mask) == prefix) atomicAdd(&s_hist[(k >> shift) & 255u], 1);
             }
             __syncthreads();
-            if (tid == 0) {
-                int need = s_need, cum = 0;
-                for (int d = 255; d >= 0; d--) {
-                    const int c = s_hist[d];
-                    if (cum + c >= need) { s_prefix = prefix | ((uint32_t)d << shift); s_need = need - cum; break; }
-                    cum += c;
+            if (tid < 32) {
+                // warp scan from the top bin down, 8 bins per lane: first bin where the running count reaches `need`
+                const int need = s_need;
+                int loc[8], sum = 0;
+#pragma unroll
+                for (int k = 0; k < 8; k++) { loc[k] = s_hist[255 - (lane * 8 + k)]; sum += loc[k]; }
+                int incl = sum;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
                 }
+                int cum = incl - sum, found = -1, before = 0;
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    if (found < 0 && cum + loc[k] >= need) { found = 255 - (lane * 8 + k); before = cum; }
+                    cum += loc[k];
+                }
+                const uint32_t b = __ballot_sync(0xffffffffu, found >= 0);
+                const int src = __ffs(b) - 1;
+                if (b && lane == src) { s_prefix = prefix | ((uint32_t)found << shift); s_need = need - before; }
             }
             __syncthreads();
         }
@@ -411,17 +425,49 @@ k_select_sort(const __grid_constant__ OrbDev g)
     }
     uint32_t *kxy = g.kept_xy + (long long)f * g.list_fs + L.list_off;
     float *kresp = g.kept_resp + (long long)f * g.list_fs + L.list_off;
+    if (in_smem) {
+        // compact the kept entries (position key + source index), then rank each by (y<<12|x) among the kept ones
+        for (int i0 = 0; i0 < n; i0 += SORT_THREADS) {
+            const int i = i0 + tid;
+            const bool keep = i < n && s_key[i] >= thr_key;
+            const uint32_t b = __ballot_sync(0xffffffffu, keep);
+            if (b) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&s_nkept, __popc(b));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (keep) {
+                    const int slot = base + __popc(b & ((1u << lane) - 1u));
+                    s_cpos[slot] = s_pos[i];
+                    s_cidx[slot] = (uint32_t)i;
+                }
+            }
+        }
+        __syncthreads();
+        const int nk = s_nkept, nk4 = (nk + 3) & ~3;
+        for (int i = nk + tid; i < nk4; i += SORT_THREADS) s_cpos[i] = 0xffffffffu; // pad: never smaller than a real key
+        __syncthreads();
+        for (int e = tid; e < nk; e += SORT_THREADS) {
+            const uint32_t pi = s_cpos[e];
+            int rank = 0;
+#pragma unroll 2
+            for (int j = 0; j < nk4; j += 4) {
+                const uint4 p = *reinterpret_cast<const uint4 *>(s_cpos + j);
+                rank += (p.x < pi) + (p.y < pi) + (p.z < pi) + (p.w < pi);
+            }
+            kxy[rank] = pi;
+            kresp[rank] = resp[s_cidx[e]];
+        }
+        if (tid == 0) g.kept_count[f * KFS_MAX_LEVELS + l] = nk;
+        return;
+    }
+    // oversized candidate list (ties far beyond the slack): same result straight from global memory
     int mine = 0;
     for (int i = tid; i < n; i += SORT_THREADS) {
-        const uint32_t ki = in_smem ? s_key[i] : kfs_float_key(resp[i]);
+        const uint32_t ki = kfs_float_key(resp[i]);
         if (ki < thr_key) continue;
-        const uint32_t pi = in_smem ? s_pos[i] : (cand[i] & 0xffffffu);
+        const uint32_t pi = cand[i] & 0xffffffu;
         int rank = 0;
-        if (in_smem) {
-            for (int j = 0; j < n; j++) rank += (s_key[j] >= thr_key && s_pos[j] < pi) ? 1 : 0;
-        } else {
-            for (int j = 0; j < n; j++) rank += (kfs_float_key(resp[j]) >= thr_key && (cand[j] & 0xffffffu) < pi) ? 1 : 0;
-        }
+        for (int j = 0; j < n; j++) rank += (kfs_float_key(resp[j]) >= thr_key && (cand[j] & 0xffffffu) < pi) ? 1 : 0;
         kxy[rank] = pi;
         kresp[rank] = resp[i];
         mine++;
@@ -432,19 +478,34 @@ k_select_sort(const __grid_constant__ OrbDev g)
 }
 
 // ======================================================================================================
-// a1.7 / a1.8  intensity-centroid orientation + keypoint record
+// a1.7 - a1.10  orientation + keypoint record + on-demand blur + rotated BRIEF: one WARP per keypoint
 // ======================================================================================================
-// grid (ceil(cap_out/8), frame); one warp per output slot.  Lane = column u of the radius-15 disc; the
-// disc is symmetric so column u spans rows |v| <= umax[|u|].  fp64 sincos for the descriptor rotation is
-// done once per keypoint by lanes 0..7 of warp 0 (dense) instead of once per warp.
-constexpr int ORI_KP_PER_CTA = 8;
-__global__ void __launch_bounds__(32 * ORI_KP_PER_CTA)
-k_orient(const __grid_constant__ OrbDev g)
+// grid (ceil(cap_out/4), frame), 4 warps per CTA, warp = output slot.
+//   1. slot -> (level, rank) through the per-level kept counts (warp prefix), read (x, y, response)
+//   2. the 43x43 window around the keypoint -> shared memory as bytes: 43 rows x 4 aligned 16-byte chunks
+//      (uint4 loads; the window's x origin is absorbed into a 0..15 byte shift `sh`)
+//   3. intensity-centroid moments from the window (lane = disc column; the disc is symmetric so column u spans
+//      |v| <= umax[|u|]); kfs_fast_atan2 (OpenCV's polynomial, no FMA)
+//   4. fp64 sincos of the 4 keypoints of the CTA by 4 lanes (dense) instead of once per warp; cv::KeyPoint record
+//   5. row pass of the 7x7 blur (43 rows x 37 cols, exact sepFilter2D order kfs_blur_row), 86 items over 3 rounds
+//   6. rotated BRIEF: every sampled point is blurred on demand with the column pass (kfs_blur_col) from the
+//      row-pass buffer — only the <= 512 sampled positions are ever blurred, not the 37x37 patch; 8 ballots give
+//      the 8 descriptor words.
+// The reference blurs every level in full (Σpx read + Σpx write per frame); keypoints sit >= 31 px inside the
+// level and the rotated pattern reaches <= 18 px, so this is exact and the blurred level never exists in HBM.
+constexpr int DK = 4;                 // keypoints (warps) per CTA
+constexpr int WIN = 43, RAW_P = 68;   // raw window rows: 64 bytes + 4 pad (17 words: odd => rows hit distinct banks)
+constexpr int BL_P = 40;              // blurred 37x37 patch (u8), aliases the raw window once the row pass is done
+constexpr int ROW_C = 37, ROW_P = 37; // row-pass output 43 rows x 37 cols (odd pitch: conflict-free row items)
+__global__ void __launch_bounds__(32 * DK)
+k_describe(const __grid_constant__ OrbDev g)
 {
-    __shared__ float s_angle[ORI_KP_PER_CTA], s_resp[ORI_KP_PER_CTA];
-    __shared__ uint32_t s_meta[ORI_KP_PER_CTA];
+    __shared__ __align__(16) uint8_t s_raw[DK][WIN * RAW_P + 4];
+    __shared__ float s_row[DK][WIN * ROW_P];
+    __shared__ float s_angle[DK];
+    __shared__ float2 s_rot[DK];
     const int f = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * ORI_KP_PER_CTA + warp;
+    const int slot = blockIdx.x * DK + warp;
     // per-level kept counts -> prefix
     int cnt = 0;
     if (lane < g.nlevels) cnt = min(g.kept_count[f * KFS_MAX_LEVELS + lane], g.lv[lane].list_cap);
@@ -456,24 +517,43 @@ k_orient(const __grid_constant__ OrbDev g)
     }
     const int total = __shfl_sync(0xffffffffu, incl, 31);
     if (blockIdx.x == 0 && threadIdx.x == 0) g.n_out[f] = total;
+    if (blockIdx.x * DK >= min(total, g.cap_out)) return; // whole CTA beyond the last keypoint
     const bool valid = slot < min(total, g.cap_out);
-    uint32_t meta = 0xffffffffu;
+    int x = 0, y = 0, level = 0, sh = 0;
+    float resp = 0.f, angle = 0.f;
+    uint8_t *raw = s_raw[warp];
+    float *rowb = s_row[warp];
     if (valid) {
-        const int level = __popc(__ballot_sync(0xffffffffu, incl <= slot));
+        level = __popc(__ballot_sync(0xffffffffu, incl <= slot));
         const int excl = __shfl_sync(0xffffffffu, incl - cnt, level);
-        const int rank = slot - excl;
         const LevelDev &L = g.lv[level];
-        const long long li = (long long)f * g.list_fs + L.list_off + rank;
+        const long long li = (long long)f * g.list_fs + L.list_off + (slot - excl);
         const uint32_t xy = g.kept_xy[li];
-        const int x = xy & 0xfff, y = (xy >> 12) & 0xfff;
+        x = xy & 0xfff; y = (xy >> 12) & 0xfff;
+        resp = g.kept_resp[li];
+        // ---- window -> smem
+        const int ox = x - 21, ax = ox & ~15;
+        sh = ox & 15;
+        const uint8_t *src = L.img + (long long)f * L.img_fs + (long long)(y - 21) * L.pitch + ax;
+#pragma unroll 2
+        for (int i = lane; i < WIN * 4; i += 32) {
+            const int r = i >> 2, q = i & 3;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (ax + 16 * q < L.pitch) v = __ldg(reinterpret_cast<const uint4 *>(src + (long long)r * L.pitch + 16 * q));
+            uint32_t *dst = reinterpret_cast<uint32_t *>(raw + r * RAW_P + 16 * q);
+            dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+        }
+        __syncwarp();
+        // ---- IC moments: lane = column u
         int m10 = 0, m01 = 0;
         if (lane < 31) {
             const int u = lane - 15, au = u < 0 ? -u : u;
             const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * au)) & 15ull);
-            const uint8_t *c = L.img + (long long)f * L.img_fs + (long long)y * L.pitch + x + u;
+            const uint8_t *c = raw + 21 * RAW_P + sh + 21 + u;
             int colsum = 0;
+#pragma unroll 4
             for (int v = -d; v <= d; v++) {
-                const int I = __ldg(c + (long long)v * L.pitch);
+                const int I = c[v * RAW_P];
                 colsum += I;
                 m01 += v * I;
             }
@@ -484,124 +564,85 @@ k_orient(const __grid_constant__ OrbDev g)
             m10 += __shfl_xor_sync(0xffffffffu, m10, d);
             m01 += __shfl_xor_sync(0xffffffffu, m01, d);
         }
-        if (lane == 0) {
-            s_angle[warp] = kfs_fast_atan2((float)m01, (float)m10);
-            s_resp[warp] = g.kept_resp[li];
-        }
-        meta = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)level << 24);
-    }
-    if (lane == 0) s_meta[warp] = meta;
-    __syncthreads();
-    if (threadIdx.x < ORI_KP_PER_CTA) {
-        const uint32_t m = s_meta[threadIdx.x];
-        if (m != 0xffffffffu) {
-            const int k = blockIdx.x * ORI_KP_PER_CTA + threadIdx.x;
-            const int x = m & 0xfff, y = (m >> 12) & 0xfff, level = m >> 24;
-            const float sc = g.lv[level].scale, ang = s_angle[threadIdx.x];
-            kfs_keypoint kp;
-            kp.x = kfs_mul((float)x, sc);
-            kp.y = kfs_mul((float)y, sc);
-            kp.size = kfs_mul(31.f, sc);
-            kp.angle = ang;
-            kp.response = s_resp[threadIdx.x];
-            kp.octave = level;
-            kp.class_id = -1;
-            const long long o = (long long)f * g.cap_out + k;
-            g.kp[o] = kp;
-            const float rad = kfs_mul(ang, (float)(3.1415926535897932384626433832795 / 180.f));
-            double sn, cs;
-            sincos((double)rad, &sn, &cs);
-            g.rot[o] = make_float2((float)cs, (float)sn);
-            g.slot_meta[o] = m;
-        }
-    }
-}
-
-// ======================================================================================================
-// a1.9 / a1.10  on-demand 7x7 blur of the 43x43 patch + rotated BRIEF-256, one CTA per keypoint
-// ======================================================================================================
-// The reference blurs every level in full (Σpx read + Σpx write per frame).  Keypoints sit >= 31 px inside
-// the level and the rotated pattern reaches at most 18 px, so only the 37x37 blurred patch around each
-// keypoint is ever sampled; it is produced here in shared memory with the exact sepFilter2D operation
-// order (kfs_blur_row / kfs_blur_col) and never written to HBM.
-constexpr int DESC_THREADS = 128;
-constexpr int WIN = 43, WIN_P = 45;   // raw window as float, pitch 45 (odd: conflict-free row items)
-constexpr int ROW_C = 37, ROW_P = 37; // row-pass output 43 rows x 37 cols
-constexpr int BL_P = 40;              // blurred patch 37 x 37, u8, pitch 40
-__global__ void __launch_bounds__(DESC_THREADS)
-k_describe(const __grid_constant__ OrbDev g)
-{
-    __shared__ float s_win[WIN * WIN_P];
-    __shared__ float s_row[WIN * ROW_P];
-    __shared__ __align__(4) uint8_t s_bl[ROW_C * BL_P];
-    const int f = blockIdx.y, slot = blockIdx.x, tid = threadIdx.x;
-    const int n = min(g.n_out[f], g.cap_out);
-    if (slot >= n) return;
-    const long long o = (long long)f * g.cap_out + slot;
-    const uint32_t meta = g.slot_meta[o];
-    const int level = meta >> 24;
-    const LevelDev &L = g.lv[level];
-    const kfs_keypoint kp = g.kp[o];
-    const float inv = kfs_div(1.f, L.scale);
-    const int cx = kfs_rint(kfs_mul(kp.x, inv)), cy = kfs_rint(kfs_mul(kp.y, inv));
-    const uint8_t *img = L.img + (long long)f * L.img_fs + (long long)(cy - 21) * L.pitch + (cx - 21);
-    for (int i = tid; i < WIN * WIN; i += DESC_THREADS) {
-        const int r = i / WIN, c = i - r * WIN;
-        s_win[r * WIN_P + c] = (float)__ldg(img + (long long)r * L.pitch + c);
+        angle = kfs_fast_atan2((float)m01, (float)m10);
+        if (lane == 0) s_angle[warp] = angle;
     }
     __syncthreads();
-    // row pass: 86 items = (segment, row); segment 0 -> cols 0..18, segment 1 -> cols 19..36
-    if (tid < 2 * WIN) {
-        const int seg = tid / WIN, r = tid - seg * WIN;
-        const int c0 = seg * 19, cnt = seg ? 18 : 19;
-        const float *w = s_win + r * WIN_P + c0;
-        float *out = s_row + r * ROW_P + c0;
-        float p0 = w[0], p1 = w[1], p2 = w[2], p3 = w[3], p4 = w[4], p5 = w[5], p6;
+    if (threadIdx.x < DK && blockIdx.x * DK + (int)threadIdx.x < min(total, g.cap_out)) {
+        const float rad = kfs_mul(s_angle[threadIdx.x], (float)(3.1415926535897932384626433832795 / 180.f));
+        double sn, cs;
+        sincos((double)rad, &sn, &cs);
+        s_rot[threadIdx.x] = make_float2((float)cs, (float)sn);
+    }
+    if (valid) {
+        // ---- row pass: item = (segment, row); segment 0 -> cols 0..18, segment 1 -> cols 19..36
+#pragma unroll 1
+        for (int item = lane; item < 2 * WIN; item += 32) {
+            const int seg = item >= WIN ? 1 : 0, r = item - seg * WIN;
+            const int c0 = seg * 19, n = seg ? 18 : 19;
+            const uint8_t *w = raw + r * RAW_P + sh + c0;
+            float *out = rowb + r * ROW_P + c0;
+            float p0 = (float)w[0], p1 = (float)w[1], p2 = (float)w[2], p3 = (float)w[3], p4 = (float)w[4], p5 = (float)w[5], p6;
 #pragma unroll
-        for (int k = 0; k < 19; k++) {
-            if (k < cnt) {
-                p6 = w[k + 6];
-                out[k] = kfs_blur_row(p0, p1, p2, p3, p4, p5, p6);
-                p0 = p1; p1 = p2; p2 = p3; p3 = p4; p4 = p5; p5 = p6;
+            for (int k = 0; k < 19; k++) {
+                if (k < n) {
+                    p6 = (float)w[k + 6];
+                    out[k] = kfs_blur_row(p0, p1, p2, p3, p4, p5, p6);
+                    p0 = p1; p1 = p2; p2 = p3; p3 = p4; p4 = p5; p5 = p6;
+                }
             }
         }
     }
-    __syncthreads();
-    // column pass: 111 items = (vertical segment, column); rows [0,13) [13,25) [25,37)
-    if (tid < 3 * ROW_C) {
-        const int vs = tid / ROW_C, c = tid - vs * ROW_C;
-        const int o0 = vs == 0 ? 0 : (vs == 1 ? 13 : 25), cnt = vs == 0 ? 13 : 12;
-        const float *r = s_row + o0 * ROW_P + c;
+    __syncthreads(); // s_rot ready (and this warp's row buffer complete)
+    if (!valid) return;
+    const float2 ab = s_rot[warp];
+    const float sc = g.lv[level].scale;
+    const long long o = (long long)f * g.cap_out + slot;
+    if (lane == 0) {
+        kfs_keypoint kp;
+        kp.x = kfs_mul((float)x, sc);
+        kp.y = kfs_mul((float)y, sc);
+        kp.size = kfs_mul(31.f, sc);
+        kp.angle = angle;
+        kp.response = resp;
+        kp.octave = level;
+        kp.class_id = -1;
+        g.kp[o] = kp;
+    }
+    // ---- column pass: 111 items = (vertical segment, column); rows [0,13) [13,25) [25,37); the blurred patch
+    // overwrites the raw window (no longer needed: every lane of this warp passed the barrier after its row items)
+    uint8_t *bl = raw;
+#pragma unroll 1
+    for (int item = lane; item < 3 * ROW_C; item += 32) {
+        const int vs = item >= 2 * ROW_C ? 2 : (item >= ROW_C ? 1 : 0), c = item - vs * ROW_C;
+        const int o0 = vs == 0 ? 0 : (vs == 1 ? 13 : 25), n = vs == 0 ? 13 : 12;
+        const float *r = rowb + o0 * ROW_P + c;
         float q0 = r[0], q1 = r[ROW_P], q2 = r[2 * ROW_P], q3 = r[3 * ROW_P], q4 = r[4 * ROW_P], q5 = r[5 * ROW_P], q6;
 #pragma unroll
         for (int k = 0; k < 13; k++) {
-            if (k < cnt) {
+            if (k < n) {
                 q6 = r[(k + 6) * ROW_P];
-                s_bl[(o0 + k) * BL_P + c] = (uint8_t)kfs_blur_col(q0, q1, q2, q3, q4, q5, q6);
+                bl[(o0 + k) * BL_P + c] = (uint8_t)kfs_blur_col(q0, q1, q2, q3, q4, q5, q6);
                 q0 = q1; q1 = q2; q2 = q3; q3 = q4; q4 = q5; q5 = q6;
             }
         }
     }
-    __syncthreads();
-    // rBRIEF: warp w, lane i -> pairs 64w+i and 64w+32+i; ballots give descriptor words 2w and 2w+1
-    const float2 ab = g.rot[o];
-    const int warp = tid >> 5, lane = tid & 31;
-    uint32_t words[2];
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-        const int pair = 64 * warp + 32 * h + lane;
+    __syncwarp();
+    // OpenCV recomputes the integer centre from the scaled float point: cvRound(pt * (1.f/scale)).  The window was
+    // fetched around (x, y); (x*s)*(1/s) is within 1e-3 of x for x < 4096, so the rounded centre is (x, y) itself.
+    uint32_t word = 0;
+#pragma unroll 2
+    for (int h = 0; h < 8; h++) {
+        const int pair = 32 * h + lane;
         const char4 pt = *reinterpret_cast<const char4 *>(d_pattern + 4 * pair);
         int ix0, iy0, ix1, iy1;
         kfs_brief_rot(pt.x, pt.y, ab.x, ab.y, &ix0, &iy0);
         kfs_brief_rot(pt.z, pt.w, ab.x, ab.y, &ix1, &iy1);
-        const int v0 = s_bl[(18 + iy0) * BL_P + 18 + ix0], v1 = s_bl[(18 + iy1) * BL_P + 18 + ix1];
-        words[h] = __ballot_sync(0xffffffffu, v0 < v1);
+        const int v0 = bl[(18 + iy0) * BL_P + 18 + ix0], v1 = bl[(18 + iy1) * BL_P + 18 + ix1];
+        const uint32_t b = __ballot_sync(0xffffffffu, v0 < v1);
+        if (lane == h) word = b;
     }
-    if (lane == 0) {
-        uint32_t *d = reinterpret_cast<uint32_t *>(g.desc + o * 32);
-        d[2 * warp] = words[0];
-        d[2 * warp + 1] = words[1];
-    }
+    if (lane < 8) reinterpret_cast<uint32_t *>(g.desc + o * 32)[lane] = word;
 }
 
 // ======================================================================================================
@@ -635,6 +676,7 @@ struct kfs_orb {
     bool ev_made = false;
     float stage_ms[KFS_STAGE_COUNT];
     int *h_counts = nullptr; // pinned staging for n_out
+    size_t sort_smem_set = 0;
 };
 
 static int kfs_cvround(double v) { return (int)lrint(v); }
@@ -828,14 +870,21 @@ static kfs_status kfs_orb_run(kfs_orb *o, int batch, const uint8_t *d_mask_in, s
     }
     if (kfs_stage_mark(o, KFS_STAGE_SELECT_SORT)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
-        k_select_sort<<<dim3(L, batch), SORT_THREADS, 0, st>>>(g);
+        int maxq = 1;
+        for (int l = 0; l < L; l++) maxq = o->quota[l] > maxq ? o->quota[l] : maxq;
+        int smem_n = (2 * maxq + maxq / 2 + 64 + 63) / 64 * 64;
+        if (smem_n > 13312) smem_n = 13312; // 16 B per entry -> 208 KB, under the 227 KB opt-in limit
+        const size_t dyn = (size_t)smem_n * 16;
+        if (dyn > 48 * 1024 && dyn != o->sort_smem_set) {
+            KFS_CUDA_TRY(cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+            o->sort_smem_set = dyn;
+        }
+        k_select_sort<<<dim3(L, batch), SORT_THREADS, dyn, st>>>(g, smem_n);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_ORIENT)) return KFS_ERR_CUDA;
-    k_orient<<<dim3(kfs_div_up(g.cap_out, ORI_KP_PER_CTA), batch), 32 * ORI_KP_PER_CTA, 0, st>>>(g);
-    KFS_LAUNCH_CHECK(o);
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
-    k_describe<<<dim3(g.cap_out, batch), DESC_THREADS, 0, st>>>(g);
+    k_describe<<<dim3(kfs_div_up(g.cap_out, DK), batch), 32 * DK, 0, st>>>(g);
     KFS_LAUNCH_CHECK(o);
     if (kfs_stage_mark(o, KFS_STAGE_COUNT)) return KFS_ERR_CUDA;
     o->last_batch = batch;
