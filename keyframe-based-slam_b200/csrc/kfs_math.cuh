@@ -84,7 +84,7 @@ KFS_HD int kfs_fast9_m(const uint32_t e[16])
 // max(p0,p8) > v+t and max(p4,p12) > v+t   (min(p0,p8) < v-t and min(p4,p12) < v-t).
 // Inputs are u16x2 words holding the two pixels' values (0..255 per half).  Returns a word whose bit 15
 // (bit 31) is set iff pixel a (b) MAY be a corner.
-KFS_HD uint32_t kfs_fast_quick2(uint32_t V, uint32_t U, uint32_t D, uint32_t R, uint32_t L, int thr)
+KFS_HD uint32_t kfs_fast_quick2m(uint32_t V, uint32_t U, uint32_t D, uint32_t R, uint32_t L, int thr, uint32_t mask)
 {
     // per half: q + (0x8000 - t - 1) - v  >= 0x8000  <=>  q > v + t ;  v + (0x8000 - t - 1) - r >= 0x8000  <=>  r < v - t
     // (each half stays in [0x8000 - 511, 0x8000 + 254]: no borrow/carry crosses the halves)
@@ -93,7 +93,11 @@ KFS_HD uint32_t kfs_fast_quick2(uint32_t V, uint32_t U, uint32_t D, uint32_t R, 
     uint32_t r = kfs_max2(kfs_min2(U, D), kfs_min2(R, L));   // dark side
     uint32_t X = q + K - V;
     uint32_t Y = V + K - r;
-    return (X | Y) & 0x80008000u;
+    return (X | Y) & mask;   // mask: subset of 0x80008000 (pixel validity), folded into the same LOP3
+}
+KFS_HD uint32_t kfs_fast_quick2(uint32_t V, uint32_t U, uint32_t D, uint32_t R, uint32_t L, int thr)
+{
+    return kfs_fast_quick2m(V, U, D, R, L, thr, 0x80008000u);
 }
 
 // ---- a1.5 Harris response from the integer sums -----------------------------------------------------

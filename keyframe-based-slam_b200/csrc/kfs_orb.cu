@@ -55,7 +55,7 @@ __device__ __align__(4) const int8_t d_pattern[1024] = {
 // of 4 entries with (sw-1, 0) so the pad bytes of a row replicate the last column.
 // mask_mode: after the resize keep only ==255 (threshold(254, TOZERO) of a 0/255 mask).
 __global__ void __launch_bounds__(256)
-k_resize(const uint8_t *__restrict__ src, long long sfs, int spitch, int sw, int sh,
+k_resize_generic(const uint8_t *__restrict__ src, long long sfs, int spitch, int sw, int sh,
          uint8_t *__restrict__ dst, long long dfs, int dpitch, int dw, int dh,
          const uint32_t *__restrict__ xtab, const uint32_t *__restrict__ ytab, int mask_mode)
 {
@@ -84,6 +84,64 @@ k_resize(const uint8_t *__restrict__ src, long long sfs, int spitch, int sw, int
     *reinterpret_cast<uint32_t *>(dst + (long long)f * dfs + (long long)y * dpitch + x4) = outw;
 }
 
+// Fast path (scale factor <= 2, i.e. every level ratio ORB is used with): one thread = 4 adjacent output
+// pixels x RZ_ROWS output rows.  The 4 pixels' taps span <= 8 source bytes starting at a0, so per source row
+// three aligned 32-bit loads + two funnel shifts give a 64-bit window from which PRMT (run-time selector from
+// the table) picks each pixel's (a, b) pair; the horizontal lerp m0*a + m1*b is one IDP.2A (u16x2 . u8x2), the
+// vertical one two IMADs; byte 2 of n0*h0 + n1*h1 + 32768 is the output pixel, so three PRMTs pack the word.
+// Table per 4-pixel group (2 x uint4, built on the host): {a0, sel[4 x 8 bit: rel_a | rel_b << 4], -, -},
+// {M0..M3} with M = m0 | m1 << 16.
+constexpr int RZ_ROWS = 4;
+__device__ __forceinline__ uint32_t kfs_prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+}
+__global__ void __launch_bounds__(256)
+k_resize(const uint8_t *__restrict__ src, long long sfs, int spitch, int sh,
+         uint8_t *__restrict__ dst, long long dfs, int dpitch, int dw, int dh,
+         const uint4 *__restrict__ xt, const uint32_t *__restrict__ ytab, int mask_mode)
+{
+    const int gx = blockIdx.x * 32 + threadIdx.x;
+    const int ybase = (blockIdx.y * 8 + threadIdx.y) * RZ_ROWS;
+    if (gx * 4 >= dw || ybase >= dh) return;
+    const uint4 ta = __ldg(xt + 2 * gx), tm = __ldg(xt + 2 * gx + 1);
+    const uint32_t spw = (uint32_t)spitch >> 2, wmax = spw - 1u;
+    const uint32_t w0 = ta.x >> 2;
+    const int shb = (int)(ta.x & 3u) * 8;
+    const uint32_t w1 = min(w0 + 1u, wmax), w2 = min(w0 + 2u, wmax); // a clamped word is never one whose bytes are needed
+    // selectors: nibbles (rel_a, rel_b) of pixel j in bits [8j, 8j+8); prmt reads 4 nibbles, the upper two pick
+    // don't-care bytes (every nibble is <= 7, so no sign-replicate mode is ever selected)
+    const uint32_t s0 = ta.y, s1 = ta.y >> 8, s2 = ta.y >> 16, s3 = ta.y >> 24;
+    const uint32_t *sf = reinterpret_cast<const uint32_t *>(src + (long long)blockIdx.z * sfs); // CTA-uniform base
+    uint32_t *df = reinterpret_cast<uint32_t *>(dst + (long long)blockIdx.z * dfs);
+    const uint32_t dpw = (uint32_t)dpitch >> 2;
+#pragma unroll
+    for (int r = 0; r < RZ_ROWS; r++) {
+        const int y = ybase + r;
+        if (y >= dh) break;
+        const uint32_t yt = __ldg(ytab + y);
+        const uint32_t y0 = yt & 0xffffu, y1 = min(y0 + 1u, (uint32_t)sh - 1u);
+        const uint32_t n1 = yt >> 16, n0 = 256u - n1;
+        const uint32_t o0 = y0 * spw, o1 = y1 * spw; // 32-bit word offsets from the uniform base
+        const uint32_t a0 = __ldg(sf + (o0 + w0)), a1 = __ldg(sf + (o0 + w1)), a2 = __ldg(sf + (o0 + w2));
+        const uint32_t b0 = __ldg(sf + (o1 + w0)), b1 = __ldg(sf + (o1 + w1)), b2 = __ldg(sf + (o1 + w2));
+        const uint32_t lo0 = __funnelshift_r(a0, a1, shb), hi0 = __funnelshift_r(a1, a2, shb);
+        const uint32_t lo1 = __funnelshift_r(b0, b1, shb), hi1 = __funnelshift_r(b1, b2, shb);
+        const uint32_t S0 = n0 * __dp2a_lo(tm.x, kfs_prmt(lo0, hi0, s0), 0u) + (n1 * __dp2a_lo(tm.x, kfs_prmt(lo1, hi1, s0), 0u) + 32768u);
+        const uint32_t S1 = n0 * __dp2a_lo(tm.y, kfs_prmt(lo0, hi0, s1), 0u) + (n1 * __dp2a_lo(tm.y, kfs_prmt(lo1, hi1, s1), 0u) + 32768u);
+        const uint32_t S2 = n0 * __dp2a_lo(tm.z, kfs_prmt(lo0, hi0, s2), 0u) + (n1 * __dp2a_lo(tm.z, kfs_prmt(lo1, hi1, s2), 0u) + 32768u);
+        const uint32_t S3 = n0 * __dp2a_lo(tm.w, kfs_prmt(lo0, hi0, s3), 0u) + (n1 * __dp2a_lo(tm.w, kfs_prmt(lo1, hi1, s3), 0u) + 32768u);
+        uint32_t outw = kfs_prmt(kfs_prmt(S0, S1, 0x0062u), kfs_prmt(S2, S3, 0x0062u), 0x5410u);
+        if (mask_mode) { // keep only bytes == 255
+            const uint32_t t = ((outw & 0x7f7f7f7fu) + 0x01010101u) & outw & 0x80808080u;
+            outw = (t >> 7) * 255u;
+        }
+        df[(uint32_t)y * dpw + (uint32_t)gx] = outw;
+    }
+}
+
 // a1.2 level 0 of the mask pyramid: mask != 0 -> 255
 __global__ void __launch_bounds__(256)
 k_mask_binarise(const uint8_t *__restrict__ src, long long sfs, long long sstep,
@@ -106,29 +164,44 @@ k_mask_binarise(const uint8_t *__restrict__ src, long long sfs, long long sstep,
 // ======================================================================================================
 // a1.3 / a1.4  FAST-9/16 score + 3x3 NMS + border / mask filter -> per-(frame, level) corner list
 // ======================================================================================================
-// One CTA = one 120x62 tile of the keepable region [31, W-31) x [31, H-31) of one level of one frame
+// One CTA = one 112x62 tile of the keepable region [31, W-31) x [31, H-31) of one level of one frame
 // (tile -> (level, tix, tiy) through a table, so one launch covers every level of every frame).
-//   source tile 136 x 70 bytes (pitch 144), origin (tx0-8, ty0-4), 8-byte aligned rows -> uint2 loads
-//   score  tile 128 x 64 bytes,             origin (tx0-4, ty0-1)
+//   source tile 128 x 70 bytes, origin (tx0-4, ty0-4): rows are 16-byte aligned in HBM -> one 128-byte line per
+//               row, 8 LDG.128 per row
+//   score  tile 128 x 64 bytes, origin (tx0-4, ty0-1)  (same x origin as the source tile)
 // phase 1: each warp owns score rows w, w+8, ...; a lane tests 4 horizontally adjacent pixels with the
-//          necessary condition kfs_fast_quick2 (u16x2 SIMD, two pixels per op, conflict-free LDS.32); rows
-//          where no lane passes cost one vote and nothing else; survivors are compacted into a shared queue
-//          by ballot + popc prefix with one shared atomic per warp-row
+//          necessary condition kfs_fast_quick2 (u16x2 SIMD, two pixels per op, conflict-free LDS.32); the
+//          pass flags of a row leave the warp as 4 ballots = one 128-bit mask row in shared memory
+// scan   : one mask word per thread -> popc -> block exclusive scan -> the set bits are expanded into a
+//          dense queue of pixel indices (no atomics, deterministic order)
 // phase 2: exact score of the queued pixels (both polarities in one u16x2 word, VIMNMX3 trees)
-// phase 3: 3x3 NMS on the score tile, border/mask predicate, warp-aggregated append to the global list
-constexpr int FT_W = 120, FT_H = 62;
-constexpr int FS_W = 136, FS_P = 144, FS_H = FT_H + 8;
+// phase 3: 3x3 NMS on the score tile, border/mask predicate; survivors are gathered in shared memory and
+//          appended to the (frame, level) list with ONE global atomic per tile
+constexpr int FT_W = 112, FT_H = 62;
+constexpr int FS_P = 128, FS_H = FT_H + 8;
 constexpr int SC_W = 128, SC_H = FT_H + 2;
-constexpr int FAST_X0 = 24; // interior x origin of tile column 0; source origin 16 (+120k) keeps rows 8B-aligned
+constexpr int FAST_X0 = 20; // interior x origin of tile column 0; source origin 16 (+112k) keeps rows 16B-aligned
 constexpr int FAST_THREADS = 256;
+constexpr int FAST_MAXOUT = (FT_W / 2) * (FT_H / 2); // strict 3x3 maxima: at most one per 2x2 block
+static_assert(SC_H * 4 == FAST_THREADS, "one mask word per thread");
+static_assert(FAST_MAXOUT * 4 <= FS_P * FS_H, "survivor list aliases the source tile");
+
+__device__ __forceinline__ int kfs_atoms_add(int *p, int v)
+{
+    int r;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+    return r;
+}
 
 __global__ void __launch_bounds__(FAST_THREADS)
 k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
 {
-    __shared__ __align__(16) uint8_t s_src[FS_P * FS_H];
+    __shared__ __align__(16) uint8_t s_src[FS_P * FS_H + 16];
     __shared__ __align__(16) uint8_t s_sc[SC_W * SC_H];
     __shared__ uint16_t s_q[SC_W * SC_H];
-    __shared__ int s_nq;
+    __shared__ __align__(16) uint32_t s_mask[SC_H * 4];
+    __shared__ int s_wsum[FAST_THREADS / 32];
+    __shared__ int s_nout, s_gbase;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int f = blockIdx.y;
@@ -137,29 +210,30 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     const LevelDev &L = g.lv[l];
     const int W = L.w, H = L.h, pitch = L.pitch;
     const int tx0 = FAST_X0 + FT_W * tix, ty0 = KFS_BORDER + FT_H * tiy;
-    const int sx0 = tx0 - 8, sy0 = ty0 - 4;
+    const int ox = tx0 - 4, sy0 = ty0 - 4;
     const uint8_t *img = L.img + (long long)f * L.img_fs;
     const int thr = g.fast_thr;
 
-    // ---- load the source tile (uint2 per thread), clear the score tile
-    for (int i = tid; i < FS_H * (FS_W / 8); i += FAST_THREADS) {
-        const int r = i / (FS_W / 8), c = i - r * (FS_W / 8);
-        const int gy = min(max(sy0 + r, 0), H - 1), gx = sx0 + 8 * c;
-        uint2 v = make_uint2(0, 0);
-        if (gx + 8 <= pitch) v = __ldg(reinterpret_cast<const uint2 *>(img + (long long)gy * pitch + gx));
-        *reinterpret_cast<uint2 *>(s_src + r * FS_P + 8 * c) = v;
+    // ---- load the source tile (uint4 per thread), clear the score tile and the mask rows
+    for (int i = tid; i < FS_H * (FS_P / 16); i += FAST_THREADS) {
+        const int r = i >> 3, c = i & 7;
+        const int gy = min(max(sy0 + r, 0), H - 1), gx = ox + 16 * c;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
+        *reinterpret_cast<uint4 *>(s_src + r * FS_P + 16 * c) = v;
     }
     for (int i = tid; i < SC_W * SC_H / 16; i += FAST_THREADS) reinterpret_cast<uint4 *>(s_sc)[i] = make_uint4(0, 0, 0, 0);
-    if (tid == 0) s_nq = 0;
+    s_mask[tid] = 0;
+    if (tid == 0) s_nout = 0;
     __syncthreads();
 
     // ---- phase 1: quick reject, one score row per warp-iteration, 4 pixels per lane
-    // x range whose score this tile needs: [tx0-1, tx0+120] clipped to [30, W-31]; y likewise
+    // x range whose score this tile needs: [tx0-1, tx0+FT_W] clipped to [30, W-31]; y likewise
     const int xlo = max(tx0 - 1, KFS_BORDER - 1), xhi = min(tx0 + FT_W, W - KFS_BORDER);
     const int ylo = max(ty0 - 1, KFS_BORDER - 1), yhi = min(ty0 + FT_H, H - KFS_BORDER);
     uint32_t vme = 0, vmo = 0; // validity of this lane's 4 pixels, in kfs_fast_quick2's result bit positions
     {
-        const int x = tx0 - 4 + 4 * lane;
+        const int x = ox + 4 * lane;
         if (x + 0 >= xlo && x + 0 <= xhi) vme |= 0x00008000u;
         if (x + 2 >= xlo && x + 2 <= xhi) vme |= 0x80000000u;
         if (x + 1 >= xlo && x + 1 <= xhi) vmo |= 0x00008000u;
@@ -168,7 +242,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     const int sy_lo = max(ylo - (ty0 - 1), 0), sy_hi = min(yhi - (ty0 - 1), SC_H - 1);
 #pragma unroll 2
     for (int sy = sy_lo + warp; sy <= sy_hi; sy += FAST_THREADS / 32) {
-        const uint8_t *rowc = s_src + (sy + 3) * FS_P + 4 + 4 * lane;
+        const uint8_t *rowc = s_src + (sy + 3) * FS_P + 4 * lane;
         const uint32_t B = *reinterpret_cast<const uint32_t *>(rowc);
         const uint32_t A = *reinterpret_cast<const uint32_t *>(rowc - 4);
         const uint32_t C = *reinterpret_cast<const uint32_t *>(rowc + 4);
@@ -177,32 +251,51 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
         const uint32_t Rw = __funnelshift_r(B, C, 24); // pixels x+3 .. x+6
         const uint32_t Lw = __funnelshift_r(A, B, 8);  // pixels x-3 .. x
         // even bytes -> (px0, px2), odd bytes -> (px1, px3) as u16x2
-        const uint32_t me = vme & kfs_fast_quick2(__byte_perm(B, 0, 0x4240), __byte_perm(U, 0, 0x4240), __byte_perm(D, 0, 0x4240),
-                                                  __byte_perm(Rw, 0, 0x4240), __byte_perm(Lw, 0, 0x4240), thr);
-        const uint32_t mo = vmo & kfs_fast_quick2(__byte_perm(B, 0, 0x4341), __byte_perm(U, 0, 0x4341), __byte_perm(D, 0, 0x4341),
-                                                  __byte_perm(Rw, 0, 0x4341), __byte_perm(Lw, 0, 0x4341), thr);
-        if (!__any_sync(0xffffffffu, (me | mo) != 0u)) continue;
+        const uint32_t me = kfs_fast_quick2m(__byte_perm(B, 0, 0x4240), __byte_perm(U, 0, 0x4240), __byte_perm(D, 0, 0x4240),
+                                             __byte_perm(Rw, 0, 0x4240), __byte_perm(Lw, 0, 0x4240), thr, vme);
+        const uint32_t mo = kfs_fast_quick2m(__byte_perm(B, 0, 0x4341), __byte_perm(U, 0, 0x4341), __byte_perm(D, 0, 0x4341),
+                                             __byte_perm(Rw, 0, 0x4341), __byte_perm(Lw, 0, 0x4341), thr, vmo);
         const uint32_t b0 = __ballot_sync(0xffffffffu, me & 0x00008000u), b1 = __ballot_sync(0xffffffffu, mo & 0x00008000u);
         const uint32_t b2 = __ballot_sync(0xffffffffu, me & 0x80000000u), b3 = __ballot_sync(0xffffffffu, mo & 0x80000000u);
-        const int c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&s_nq, c0 + c1 + c2 + c3);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        const uint32_t lt = (1u << lane) - 1u;
-        const int pi = sy * SC_W + 4 * lane;
-        if (me & 0x00008000u) s_q[base + __popc(b0 & lt)] = (uint16_t)(pi);
-        if (mo & 0x00008000u) s_q[base + c0 + __popc(b1 & lt)] = (uint16_t)(pi + 1);
-        if (me & 0x80000000u) s_q[base + c0 + c1 + __popc(b2 & lt)] = (uint16_t)(pi + 2);
-        if (mo & 0x80000000u) s_q[base + c0 + c1 + c2 + __popc(b3 & lt)] = (uint16_t)(pi + 3);
+        if (lane == 0) *reinterpret_cast<uint4 *>(s_mask + 4 * sy) = make_uint4(b0, b1, b2, b3);
     }
     __syncthreads();
-    const int nq = s_nq;
+
+    // ---- scan: mask word tid = (row tid>>2, pixel phase tid&3); bit b of it <-> score column 4*b + phase
+    int nq;
+    {
+        uint32_t w = s_mask[tid];
+        const int cnt = __popc(w);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        int pos = incl - cnt;
+        nq = 0;
+#pragma unroll
+        for (int j = 0; j < FAST_THREADS / 32; j++) {
+            const int t = s_wsum[j];
+            if (j < warp) pos += t;
+            nq += t;
+        }
+        const int base_pi = (tid >> 2) * SC_W + (tid & 3);
+        while (w) {
+            const int b = __ffs(w) - 1;
+            w &= w - 1;
+            s_q[pos++] = (uint16_t)(base_pi + 4 * b);
+        }
+    }
+    __syncthreads();
 
     // ---- phase 2: exact score of queued pixels
     for (int e = tid; e < nq; e += FAST_THREADS) {
         const int pi = s_q[e];
         const int sy = pi >> 7, sx = pi & (SC_W - 1);
-        const uint8_t *c = s_src + (sy + 3) * FS_P + sx + 4;
+        const uint8_t *c = s_src + (sy + 3) * FS_P + sx;
         const uint32_t cv = kfs_fast_cv(c[0]);
         uint32_t ek[16];
         ek[0] = kfs_fast_e(cv, c[3 * FS_P + 0]);   ek[1] = kfs_fast_e(cv, c[3 * FS_P + 1]);
@@ -218,10 +311,9 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     }
     __syncthreads();
 
-    // ---- phase 3: NMS + border/mask filter + warp-aggregated append to the (frame, level) list
+    // ---- phase 3: NMS + border/mask filter -> survivor list in shared memory (aliases the source tile)
     const uint8_t *mask = L.mask ? L.mask + (long long)f * L.mask_fs : nullptr;
-    uint32_t *out = g.raw + (long long)f * g.list_fs + L.list_off;
-    int *gcount = g.raw_count + f * KFS_MAX_LEVELS + l;
+    uint32_t *s_out = reinterpret_cast<uint32_t *>(s_src);
     for (int e0 = 0; e0 < nq; e0 += FAST_THREADS) {
         const int e = e0 + tid;
         uint32_t packed = 0;
@@ -230,7 +322,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
             const int pi = s_q[e];
             const int s = s_sc[pi];
             const int sy = pi >> 7, sx = pi & (SC_W - 1);
-            const int x = tx0 - 4 + sx, y = ty0 - 1 + sy;
+            const int x = ox + sx, y = ty0 - 1 + sy;
             if (s > 0 && sx >= 4 && sx < 4 + FT_W && sy >= 1 && sy <= FT_H &&
                 x >= KFS_BORDER && x < W - KFS_BORDER && y >= KFS_BORDER && y < H - KFS_BORDER) {
                 const uint8_t *p = s_sc + pi;
@@ -243,12 +335,20 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
         const uint32_t bk = __ballot_sync(0xffffffffu, keep);
         if (bk) {
             int base = 0;
-            if (lane == 0) base = atomicAdd(gcount, __popc(bk));
+            if (lane == 0) base = kfs_atoms_add(&s_nout, __popc(bk));
             base = __shfl_sync(0xffffffffu, base, 0);
-            const int slot = base + __popc(bk & ((1u << lane) - 1u));
-            if (keep && slot < L.list_cap) out[slot] = packed;
+            if (keep) s_out[base + __popc(bk & ((1u << lane) - 1u))] = packed;
         }
     }
+    __syncthreads();
+    const int nout = s_nout;
+    if (nout == 0) return;
+    if (tid == 0) s_gbase = atomicAdd(g.raw_count + f * KFS_MAX_LEVELS + l, nout);
+    __syncthreads();
+    const int gbase = s_gbase;
+    uint32_t *out = g.raw + (long long)f * g.list_fs + L.list_off;
+    for (int i = tid; i < nout; i += FAST_THREADS)
+        if (gbase + i < L.list_cap) out[gbase + i] = s_out[i];
 }
 
 // ======================================================================================================
@@ -663,6 +763,8 @@ struct kfs_orb {
     uint8_t *pyr[KFS_MAX_LEVELS];   // internal level buffers (level 0 included)
     uint8_t *mpyr[KFS_MAX_LEVELS];  // mask pyramid
     uint32_t *xtab[KFS_MAX_LEVELS], *ytab[KFS_MAX_LEVELS];
+    uint4 *xtab4[KFS_MAX_LEVELS];   // per 4-pixel group tables of the fast resize path
+    bool resize_fast[KFS_MAX_LEVELS];
     void *arena = nullptr;          // one cudaMalloc for everything above and below
     size_t arena_bytes = 0;
     int *counters = nullptr;        // raw_count | cand_count | kept_count | n_out
@@ -733,12 +835,13 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     // arena layout
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t r = off; off = kfs_align_up(off + bytes, 256); return r; };
-    size_t o_pyr[KFS_MAX_LEVELS], o_mpyr[KFS_MAX_LEVELS], o_xt[KFS_MAX_LEVELS], o_yt[KFS_MAX_LEVELS];
+    size_t o_pyr[KFS_MAX_LEVELS], o_mpyr[KFS_MAX_LEVELS], o_xt[KFS_MAX_LEVELS], o_xt4[KFS_MAX_LEVELS], o_yt[KFS_MAX_LEVELS];
     int list_off[KFS_MAX_LEVELS], list_cap[KFS_MAX_LEVELS], list_fs = 0;
     for (int l = 0; l < L; l++) {
         o_pyr[l] = take((size_t)o->lfs[l] * batch + 256);
         o_mpyr[l] = need_mask ? take((size_t)o->lfs[l] * batch + 256) : 0;
         o_xt[l] = take(kfs_align_up((size_t)o->lw[l], 4) * 4);
+        o_xt4[l] = take(kfs_align_up((size_t)o->lw[l], 4) * 8);
         o_yt[l] = take((size_t)o->lh[l] * 4);
         const int W = o->lw[l], H = o->lh[l];
         list_cap[l] = (W > 2 * KFS_BORDER && H > 2 * KFS_BORDER) ? ((W - 62) / 2 + 2) * ((H - 62) / 2 + 2) : 0;
@@ -775,6 +878,8 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
         o->pyr[l] = base + o_pyr[l];
         o->mpyr[l] = need_mask ? base + o_mpyr[l] : nullptr;
         o->xtab[l] = (uint32_t *)(base + o_xt[l]);
+        o->xtab4[l] = (uint4 *)(base + o_xt4[l]);
+        o->resize_fast[l] = false;
         o->ytab[l] = (uint32_t *)(base + o_yt[l]);
         LevelDev &D = g.lv[l];
         D.img = o->pyr[l]; D.img_fs = o->lfs[l]; D.pitch = o->lpitch[l];
@@ -793,6 +898,29 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
             kfs_axis_table(o->lw[l - 1], o->lw[l], (int)kfs_align_up((size_t)o->lw[l], 4), tab);
             KFS_CUDA_TRY(cudaMemcpyAsync(o->xtab[l], tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, o->stream));
             KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+            {   // group tables of the fast path: {a0, sel, 0, 0} {M0..M3}; usable when every group's taps fit 8 bytes
+                const int sw = o->lw[l - 1], ngroups = (int)tab.size() / 4;
+                std::vector<uint32_t> t4((size_t)ngroups * 8, 0u);
+                bool ok = true;
+                for (int gi = 0; gi < ngroups; gi++) {
+                    const int a0 = (int)(tab[(size_t)4 * gi] & 0xffffu);
+                    uint32_t sel = 0;
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t e = tab[(size_t)4 * gi + j];
+                        const int a = (int)(e & 0xffffu), m1 = (int)(e >> 16);
+                        const int b = a + 1 < sw ? a + 1 : sw - 1;
+                        const int ra = a - a0, rb = b - a0;
+                        if (ra < 0 || rb > 7) ok = false;
+                        sel |= (uint32_t)((ra & 7) | ((rb & 7) << 4)) << (8 * j);
+                        t4[(size_t)8 * gi + 4 + j] = (uint32_t)(256 - m1) | ((uint32_t)m1 << 16);
+                    }
+                    t4[(size_t)8 * gi + 0] = (uint32_t)a0;
+                    t4[(size_t)8 * gi + 1] = sel;
+                }
+                o->resize_fast[l] = ok;
+                KFS_CUDA_TRY(cudaMemcpyAsync(o->xtab4[l], t4.data(), t4.size() * 4, cudaMemcpyHostToDevice, o->stream));
+                KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+            }
             kfs_axis_table(o->lh[l - 1], o->lh[l], o->lh[l], tab);
             KFS_CUDA_TRY(cudaMemcpyAsync(o->ytab[l], tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, o->stream));
             KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
@@ -844,14 +972,30 @@ static kfs_status kfs_orb_run(kfs_orb *o, int batch, const uint8_t *d_mask_in, s
         KFS_LAUNCH_CHECK(o);
     }
     for (int l = 1; l < L; l++) {
-        const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8), batch);
-        k_resize<<<grid, rb, 0, st>>>(g.lv[l - 1].img, g.lv[l - 1].img_fs, g.lv[l - 1].pitch, o->lw[l - 1], o->lh[l - 1],
-                                      o->pyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 0);
-        KFS_LAUNCH_CHECK(o);
-        if (has_mask) {
-            k_resize<<<grid, rb, 0, st>>>(o->mpyr[l - 1], o->lfs[l - 1], o->lpitch[l - 1], o->lw[l - 1], o->lh[l - 1],
-                                          o->mpyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 1);
+        const uint8_t *simg = g.lv[l - 1].img;
+        const long long sfs = g.lv[l - 1].img_fs;
+        const int spitch = g.lv[l - 1].pitch;
+        const bool fast = o->resize_fast[l] && ((uintptr_t)simg % 4 == 0) && (spitch % 4 == 0) && (sfs % 4 == 0);
+        if (fast) {
+            const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8 * RZ_ROWS), batch);
+            k_resize<<<grid, rb, 0, st>>>(simg, sfs, spitch, o->lh[l - 1], o->pyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l],
+                                          o->xtab4[l], o->ytab[l], 0);
             KFS_LAUNCH_CHECK(o);
+            if (has_mask) {
+                k_resize<<<grid, rb, 0, st>>>(o->mpyr[l - 1], o->lfs[l - 1], o->lpitch[l - 1], o->lh[l - 1], o->mpyr[l], o->lfs[l], o->lpitch[l],
+                                              o->lw[l], o->lh[l], o->xtab4[l], o->ytab[l], 1);
+                KFS_LAUNCH_CHECK(o);
+            }
+        } else { // scale factor > 2 (taps of a 4-pixel group span more than 8 bytes) or an unaligned caller buffer
+            const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8), batch);
+            k_resize_generic<<<grid, rb, 0, st>>>(simg, sfs, spitch, o->lw[l - 1], o->lh[l - 1],
+                                                  o->pyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 0);
+            KFS_LAUNCH_CHECK(o);
+            if (has_mask) {
+                k_resize_generic<<<grid, rb, 0, st>>>(o->mpyr[l - 1], o->lfs[l - 1], o->lpitch[l - 1], o->lw[l - 1], o->lh[l - 1],
+                                                      o->mpyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 1);
+                KFS_LAUNCH_CHECK(o);
+            }
         }
     }
     if (kfs_stage_mark(o, KFS_STAGE_FAST)) return KFS_ERR_CUDA;

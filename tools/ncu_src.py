@@ -15,6 +15,14 @@ for r in csv.reader(open(path, errors="replace")):
     try: v = float(r[ie])
     except ValueError: continue
     out.append((v, cur_file, r[0], r[1], r[sm]))
+agg = {}
+for v, f, ln, s, smp in out:  # aggregate SASS rows (and repeated launches) by CUDA source line
+    k = (f, ln, s)
+    a = agg.setdefault(k, [0.0, 0])
+    a[0] += v
+    try: a[1] += int(smp)
+    except ValueError: pass
+out = [(a[0], k[0], k[1], k[2], a[1]) for k, a in agg.items()]
 tot = sum(o[0] for o in out)
 print("total warp-instructions: %.4g" % tot)
 out.sort(reverse=True)
