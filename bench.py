@@ -316,16 +316,25 @@ def run_ours(args):
     N = import_module("keyframe-based-slam_b200._native")
     pair_arr = (N.BfPair * B)()
 
+    e2e_t = {"orb": 0.0, "knn": 0.0}
+    if args.e2e_chunk:
+        orb.set_pipeline_chunk(args.e2e_chunk)
+
     def e2e_step(s):
         src = pinned[s % nrot].numpy()
+        ta = time.perf_counter()
         N.check(L.kfs_orb_detect_and_compute_batch(orb._h, src.ctypes.data, W, W * H, W, H, B, None, 0, 0,
                                                    kp_h.ctypes.data, desc_h.ctypes.data, cap, n_h))
+        tb = time.perf_counter()
+        e2e_t["orb"] += tb - ta
         up = 0
         for i in range(B):
             k = keyframe_of(i)
             pair_arr[i] = N.BfPair(desc_h[k].ctypes.data, min(n_h[k], cap), None, desc_h[i].ctypes.data, min(n_h[i], cap), None,
                                    match_h[i].ctypes.data, None)
+        tc = time.perf_counter()
         N.check(L.kfs_bf_knn_match_pairs(bf._h, pair_arr, B, 2))
+        e2e_t["knn"] += time.perf_counter() - tc
         nq = [min(n_h[keyframe_of(i)], cap) for i in range(B)]
         h2d = B * W * H + 32 * (sum(min(n_h[i], cap) for i in range(B)) + sum(min(n_h[k], cap) for k in set(keyframe_of(i) for i in range(B))))
         d2h = B * cap * 60 + 4 * B + sum(nq) * 32
@@ -335,6 +344,7 @@ def run_ours(args):
     for s in range(min(Wm, 2)):
         e2e_step(s)
     barrier()
+    e2e_t["orb"] = e2e_t["knn"] = 0.0
     t0 = time.perf_counter()
     for s in range(Ke):
         h2d, d2h = e2e_step(s)
@@ -343,7 +353,70 @@ def run_ours(args):
     t_e = torch.tensor([e2e_dt], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-    e2e_value = world * B * Ke / float(t_e.item())
+    dropin_value = world * B * Ke / float(t_e.item())
+    dropin = {"value": round(dropin_value, 1), "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+              "api": "kfs_orb_detect_and_compute_batch + kfs_bf_knn_match_pairs (the two drop-in calls, each blocking) on pinned host buffers",
+              "ms_per_step_orb_call": round(e2e_t["orb"] / Ke * 1e3, 3), "ms_per_step_knn_call": round(e2e_t["knn"] / Ke * 1e3, 3),
+              "pipeline_chunk_frames": args.e2e_chunk or "auto (batch/4)"}
+
+    # ---- e2e through the replay executor (kfs_replay_*): same host buffers in, keypoints + descriptors + kNN matches +
+    # ratio-test survivors out, descriptors matched where they were produced; batch s+1 is submitted before batch s is awaited
+    rp = C.c_void_p()
+    rpar = N.ReplayParams()
+    L.kfs_replay_default_params(C.byref(rpar))
+    rpar.orb.nfeatures, rpar.max_batch, rpar.keyframe_slots, rpar.ratio = NF, B, 2, 0.6
+    N.check(L.kfs_replay_create(C.byref(rpar), local_rank, C.byref(rp)))
+    rcap = L.kfs_replay_capacity(rp)
+    plan = (N.ReplayFrame * B)(*[N.ReplayFrame(keyframe_of(i), -1) for i in range(B)])
+    r_out, r_io = [], []
+    for b in range(2):
+        o = dict(kp=torch.empty((B, rcap, 28), dtype=torch.uint8).pin_memory().numpy(),
+                 desc=torch.empty((B, rcap, 32), dtype=torch.uint8).pin_memory().numpy(),
+                 knn=torch.empty((B, rcap, 2, 16), dtype=torch.uint8).pin_memory().numpy(),
+                 good=torch.empty((B, rcap, 16), dtype=torch.uint8).pin_memory().numpy(),
+                 n_kp=np.zeros(B, np.int32), n_query=np.zeros(B, np.int32), n_good=np.zeros(B, np.int32))
+        r_out.append(o)
+    def r_submit(s):
+        o = r_out[s & 1]
+        io = N.ReplayIO(pinned[s % nrot].data_ptr(), W, W * H, W, H, o["kp"].ctypes.data, o["desc"].ctypes.data, rcap, o["n_kp"].ctypes.data,
+                        o["knn"].ctypes.data, o["n_query"].ctypes.data, o["good"].ctypes.data, o["n_good"].ctypes.data)
+        t = C.c_int(-1)
+        N.check(L.kfs_replay_submit(rp, C.byref(io), plan, B, C.byref(t)))
+        return t.value
+
+    def r_run(n):
+        prev = None
+        for s in range(n):
+            t = r_submit(s)
+            if prev is not None:
+                N.check(L.kfs_replay_wait(rp, prev))
+            prev = t
+        N.check(L.kfs_replay_wait(rp, prev))
+
+    Kr = max(2, Ke)
+    r_run(3)
+    barrier()
+    t0 = time.perf_counter()
+    r_run(Kr)
+    rep_dt = time.perf_counter() - t0
+    t_r = torch.tensor([rep_dt], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t_r, op=dist.ReduceOp.MAX)
+    e2e_value = world * B * Kr / float(t_r.item())
+    rep_launches = L.kfs_replay_last_launches(rp)
+    rep_h2d = B * W * H
+    rep_d2h = B * rcap * (28 + 32 + 32 + 16) + 3 * 4 * B
+    # sanity: the executor's last batch equals the drop-in calls' results on the same frames
+    last = r_out[(Kr - 1) & 1]
+    src_last = pinned[(Kr - 1) % nrot].numpy()
+    N.check(L.kfs_orb_detect_and_compute_batch(orb._h, src_last.ctypes.data, W, W * H, W, H, B, None, 0, 0,
+                                               kp_h.ctypes.data, desc_h.ctypes.data, cap, n_h))
+    for i in (0, 1, B - 1):
+        n_i = int(last["n_kp"][i])
+        assert n_i == n_h[i] and np.array_equal(last["desc"][i, :n_i], desc_h[i, :n_i]) and np.array_equal(last["kp"][i, :n_i], kp_h[i, :n_i]), \
+            "replay executor and drop-in call disagree on frame %d" % i
+    rep_good = float(np.mean(last["n_good"]))
+    L.kfs_replay_destroy(rp)
 
     if rank != 0:
         if dist is not None:
@@ -438,8 +511,11 @@ def run_ours(args):
                        "keypoints_per_frame": round(nkp, 1), "ratio_survivors_per_frame": round(float(np.mean(good)), 1),
                        "fast_corners_per_level_frame0": fast_counts, "synth_gen_s": round(gen_s, 2)},
             "clocks": clocks,
-            "e2e": {"value": round(e2e_value, 1), "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "steps": Ke, "api": "kfs_orb_detect_and_compute_batch + kfs_bf_knn_match_pairs on pinned host buffers"},
+            "e2e": {"value": round(e2e_value, 1), "unit": "frames/s", "h2d_bytes_per_step": int(rep_h2d), "d2h_bytes_per_step": int(rep_d2h),
+                    "steps": Kr, "api": "kfs_replay_submit/kfs_replay_wait (C ABI replay executor): pinned host frames in; keypoints, descriptors, "
+                                        "k=2 matches vs keyframe and ratio-test survivors out to pinned host buffers; two batches in flight",
+                    "ratio_survivors_per_frame": round(rep_good, 1), "launches_per_step": int(rep_launches),
+                    "drop_in_calls": dropin},
             "gpu_launches": int(launches),
             "roofline": roofline, "roofline_popc": roofline_popc, "kernels": kernels,
             "cpu_baseline": cpu}
@@ -458,6 +534,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--batch", type=int, default=64, help="frames per GPU per step")
     ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--e2e-chunk", type=int, default=0, help="frames per chunk of the host-buffer pipeline (0 = library default)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--ref-frames-per-worker", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")

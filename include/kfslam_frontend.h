@@ -25,6 +25,7 @@
 
 #include <stddef.h>
 #include <stdint.h>
+#include <limits.h>
 
 #ifdef __cplusplus
 extern "C" {
@@ -133,6 +134,10 @@ KFS_API kfs_status kfs_orb_sync(kfs_orb *orb);
  * (e.g. torch.cuda.current_stream().cuda_stream) can install it.  Passing NULL restores the own stream. */
 KFS_API kfs_status kfs_orb_set_stream(kfs_orb *orb, void *cuda_stream);
 KFS_API void *kfs_orb_get_stream(kfs_orb *orb);
+/* kfs_orb_detect_and_compute_batch cuts the batch into chunks of frames that flow through three streams (H2D of
+ * chunk i+1 | kernels of chunk i | D2H of chunk i-1).  frames = chunk size; 0 = automatic (batch/4, whole batch when
+ * batch < 8).  Use pinned host buffers (cudaHostAlloc / cudaHostRegister) for the copies to overlap. */
+KFS_API kfs_status kfs_orb_set_pipeline_chunk(kfs_orb *orb, int frames);
 
 /* Stage taps (parity tests and profiling; not needed by the tracker). */
 KFS_API kfs_status kfs_orb_level_info(kfs_orb *orb, int level, int *w, int *h, int *quota, float *scale);
@@ -185,6 +190,44 @@ KFS_API kfs_status kfs_bf_set_stream(kfs_bf *bf, void *cuda_stream);
 KFS_API void *kfs_bf_get_stream(kfs_bf *bf);
 KFS_API kfs_status kfs_bf_sync(kfs_bf *bf);
 KFS_API int kfs_bf_last_launches(const kfs_bf *bf);
+
+/* ---- Replay executor: the tracker's per-frame loop on batches of frames ------------------------------
+ * Replaces the body of VisualOdometry::Track (VisualOdometry.cpp:129-172) up to the PnP call: ExtractFeatures
+ * (:138 -> detectAndCompute :30), MatchFeatures against the last keyframe (:144 -> knnMatch :39, query = keyframe
+ * descriptors, train = current frame) and the ratio test (:46).  Frames come from host memory; descriptors stay on
+ * the device between extraction and matching, keyframes of earlier batches live in a device-resident cache
+ * (KeyFrame::matDescriptors, KeyFrame.hpp:39), and two arenas double-buffer the batches: kfs_replay_submit only
+ * enqueues (H2D, kernels, D2H are stream-ordered), kfs_replay_wait blocks until that batch's results are in the
+ * host buffers.  At most two batches are in flight; submitting a third first completes the oldest.
+ * Use pinned host buffers (cudaHostAlloc / cudaHostRegister) for the copies to overlap with the kernels. */
+typedef struct kfs_replay kfs_replay;
+typedef struct kfs_replay_params {
+    kfs_orb_params orb;      /* extractor parameters (VisualOdometry.cpp:10-16) */
+    int32_t max_batch;       /* frames per submit */
+    int32_t keyframe_slots;  /* entries of the device-resident keyframe descriptor cache (>= 1) */
+    float ratio;             /* ratio-test threshold (reference: 0.6f, :46); <= 0 disables the fused `good` output */
+} kfs_replay_params;
+#define KFS_REPLAY_NO_MATCH INT32_MIN
+typedef struct kfs_replay_frame {
+    int32_t keyframe;   /* >= 0: index of the frame of THIS batch that is this frame's keyframe; < 0: -(1 + slot) of the
+                         * keyframe cache (content stored by an EARLIER submit); KFS_REPLAY_NO_MATCH: extract only */
+    int32_t store_slot; /* >= 0: after this batch's matching, keep this frame's descriptors in that cache slot; -1: no */
+} kfs_replay_frame;
+typedef struct kfs_replay_io { /* host buffers; must stay valid until kfs_replay_wait returns */
+    const uint8_t *gray; size_t step, frame_stride; int32_t w, h;   /* batch frames, 8-bit gray */
+    kfs_keypoint *kp; uint8_t *desc; int32_t capacity; int32_t *n_kp; /* [batch][capacity] (x32 B for desc), [batch] */
+    kfs_dmatch *knn;    /* [batch][capacity][2]: row q = the keyframe's descriptor q; NULL: not wanted */
+    int32_t *n_query;   /* [batch]: valid rows of knn = the keyframe's keypoint count; may be NULL */
+    kfs_dmatch *good;   /* [batch][capacity]: ratio-test survivors in query order; NULL: not wanted */
+    int32_t *n_good;    /* [batch]; may be NULL */
+} kfs_replay_io;
+KFS_API void kfs_replay_default_params(kfs_replay_params *p); /* ORB defaults, max_batch 64, 8 slots, ratio 0.6 */
+KFS_API kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_replay **out);
+KFS_API void kfs_replay_destroy(kfs_replay *r);
+KFS_API int kfs_replay_capacity(const kfs_replay *r);           /* per-frame capacity the outputs should have */
+KFS_API kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_replay_frame *plan, int batch, int *ticket);
+KFS_API kfs_status kfs_replay_wait(kfs_replay *r, int ticket);
+KFS_API int kfs_replay_last_launches(const kfs_replay *r);      /* kernels launched by the last submit */
 
 /* ---- microbenchmarks used by bench.py for the integer-pipe roofline -------------------- */
 /* Dependency-free POPC.32 (what=0) or LOP3.32 (what=1) issue-rate probe on `device`; returns 1e9 ops/s. */

@@ -33,6 +33,22 @@ class BfPair(C.Structure):
                 ("out", C.c_void_p), ("counts", C.c_void_p)]
 
 
+class ReplayParams(C.Structure):
+    _fields_ = [("orb", OrbParams), ("max_batch", C.c_int32), ("keyframe_slots", C.c_int32), ("ratio", C.c_float)]
+
+
+class ReplayFrame(C.Structure):
+    _fields_ = [("keyframe", C.c_int32), ("store_slot", C.c_int32)]
+
+
+class ReplayIO(C.Structure):
+    _fields_ = [("gray", C.c_void_p), ("step", C.c_size_t), ("frame_stride", C.c_size_t), ("w", C.c_int32), ("h", C.c_int32),
+                ("kp", C.c_void_p), ("desc", C.c_void_p), ("capacity", C.c_int32), ("n_kp", C.c_void_p),
+                ("knn", C.c_void_p), ("n_query", C.c_void_p), ("good", C.c_void_p), ("n_good", C.c_void_p)]
+
+
+REPLAY_NO_MATCH = -2**31
+
 # name -> (restype, argtypes); this table is also what tests/test_abi.py checks against the header.
 _vp, _i, _sz, _f = C.c_void_p, C.c_int, C.c_size_t, C.c_float
 _ip = C.POINTER(C.c_int)
@@ -53,6 +69,7 @@ SIGNATURES = {
     "kfs_orb_sync": (_i, [_vp]),
     "kfs_orb_set_stream": (_i, [_vp, _vp]),
     "kfs_orb_get_stream": (_vp, [_vp]),
+    "kfs_orb_set_pipeline_chunk": (_i, [_vp, _i]),
     "kfs_orb_level_info": (_i, [_vp, _i, _ip, _ip, _ip, C.POINTER(_f)]),
     "kfs_orb_download_level": (_i, [_vp, _i, _i, _vp, _sz]),
     "kfs_orb_download_fast_corners": (_i, [_vp, _i, _i, _vp, _i, _ip]),
@@ -69,6 +86,13 @@ SIGNATURES = {
     "kfs_bf_get_stream": (_vp, [_vp]),
     "kfs_bf_sync": (_i, [_vp]),
     "kfs_bf_last_launches": (_i, [_vp]),
+    "kfs_replay_default_params": (None, [C.POINTER(ReplayParams)]),
+    "kfs_replay_create": (_i, [C.POINTER(ReplayParams), _i, C.POINTER(_vp)]),
+    "kfs_replay_destroy": (None, [_vp]),
+    "kfs_replay_capacity": (_i, [_vp]),
+    "kfs_replay_submit": (_i, [_vp, C.POINTER(ReplayIO), C.POINTER(ReplayFrame), _i, _ip]),
+    "kfs_replay_wait": (_i, [_vp, _i]),
+    "kfs_replay_last_launches": (_i, [_vp]),
     "kfs_pipe_peak": (_i, [_i, _i, C.POINTER(C.c_double)]),
 }
 

@@ -15,6 +15,7 @@
 #include <float.h>
 #include <string.h>
 #include <vector>
+#include <unordered_map>
 #include <new>
 
 constexpr int BF_THREADS = 256;
@@ -26,12 +27,6 @@ constexpr int BF_CHUNK = 512;                   // train rows per smem stage (16
 constexpr int BF_SLICE = BF_CHUNK / BF_TSPLIT;  // rows one warp group scans per stage
 constexpr uint32_t BF_INF = 0xffffffffu;
 
-struct BfPairDev {
-    const uint8_t *query; const uint8_t *train;
-    const int *d_nq; const int *d_nt;
-    kfs_dmatch *out; int *counts;
-    int nq, nt;
-};
 
 __device__ __forceinline__ void bf_cp_async16(void *smem, const void *gmem)
 {
@@ -161,13 +156,19 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k)
     }
 }
 
-// Fused ratio test (VisualOdometry.cpp:46): one CTA per pair, ordered compaction of rows passing
-// d0 < ratio*d1 (both present).  Single block scan keeps query order, like the reference's loop.
+// Fused ratio test (VisualOdometry.cpp:46): one CTA per pair (blockIdx.x), ordered compaction of rows passing
+// d0 < ratio*d1 (both present).  A single block scan keeps query order, like the reference's loop.
 __global__ void __launch_bounds__(1024)
-k_ratio_compact(const kfs_dmatch *__restrict__ knn, int nq, float ratio, kfs_dmatch *__restrict__ good, int *__restrict__ n_good)
+k_ratio_compact(const BfPairDev *__restrict__ pairs, float ratio, kfs_dmatch *__restrict__ good_base, long long good_stride,
+                int *__restrict__ n_good)
 {
     __shared__ int s_warp[32];
     __shared__ int s_base, s_total;
+    const BfPairDev P = pairs[blockIdx.x];
+    int nq = P.nq;
+    if (P.d_nq) nq = min(nq, *P.d_nq);
+    const kfs_dmatch *knn = P.out;
+    kfs_dmatch *good = good_base + (long long)blockIdx.x * good_stride;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_base = 0;
     __syncthreads();
@@ -202,7 +203,7 @@ k_ratio_compact(const kfs_dmatch *__restrict__ knn, int nq, float ratio, kfs_dma
         if (tid == 0) s_base += s_total;
         __syncthreads();
     }
-    if (tid == 0) n_good[0] = s_base;
+    if (tid == 0) n_good[blockIdx.x] = s_base;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -280,6 +281,29 @@ static kfs_status bf_launch(kfs_bf *b, const BfPairDev *h, int npairs, int k)
     return KFS_OK;
 }
 
+// ---- library-internal hooks for kfs_replay.cu (not exported) ------------------------------------------
+// kNN over a pair table that already lives in device memory, on an explicit stream.
+kfs_status kfs_bf_launch_table(kfs_bf *b, const BfPairDev *d_table, int npairs, int max_nq, int k, cudaStream_t st)
+{
+    if (npairs == 0 || max_nq == 0) return KFS_OK;
+    k_hamming_knn2<<<dim3(kfs_div_up(max_nq, BF_QTILE), npairs), BF_THREADS, 0, st>>>(d_table, k);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_hamming_knn2 launch: %s", cudaGetErrorString(e));
+    b->launches++;
+    return KFS_OK;
+}
+// Ratio test of every pair of the table: good_base[pair * good_stride ..], n_good[pair].
+kfs_status kfs_bf_launch_ratio_table(kfs_bf *b, const BfPairDev *d_table, int npairs, float ratio, kfs_dmatch *good_base, long long good_stride,
+                                     int *n_good, cudaStream_t st)
+{
+    if (npairs == 0) return KFS_OK;
+    k_ratio_compact<<<npairs, 1024, 0, st>>>(d_table, ratio, good_base, good_stride, n_good);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_ratio_compact launch: %s", cudaGetErrorString(e));
+    b->launches++;
+    return KFS_OK;
+}
+
 extern "C" {
 
 kfs_status kfs_bf_create(int norm_type, int cross_check, int device, kfs_bf **out)
@@ -347,6 +371,32 @@ kfs_status kfs_bf_knn_match_pairs_device(kfs_bf *b, const kfs_bf_pair *pairs, in
     return bf_launch(b, h.data(), npairs, k);
 }
 
+// Host-buffer entry point.  Every distinct host descriptor matrix (keyed by pointer + row count; a keyframe that
+// is the query of several pairs, or a frame that is train of one pair and query of another, is uploaded once)
+// gets a fixed-size device slot; runs of equally sized matrices at a constant host stride (the rows of one
+// [frames][capacity][32] array, the usual layout) travel as ONE 2-D copy instead of one copy per pair, and the
+// results come back the same way.
+struct BfBufKey {
+    const uint8_t *p; int rows;
+    bool operator==(const BfBufKey &o) const { return p == o.p && rows == o.rows; }
+};
+struct BfBufKeyHash {
+    size_t operator()(const BfBufKey &k) const { return (size_t)(((uint64_t)(uintptr_t)k.p * 0x9E3779B97F4A7C15ull) ^ (uint64_t)(uint32_t)k.rows); }
+};
+struct BfCopyRun { const uint8_t *h; size_t d_off; size_t bytes; size_t hstride; int count; };
+
+static void bf_add_to_runs(std::vector<BfCopyRun> &runs, const uint8_t *h, size_t d_off, size_t bytes, size_t dstride)
+{
+    if (!runs.empty()) {
+        BfCopyRun &r = runs.back();
+        if (r.bytes == bytes && d_off == r.d_off + (size_t)r.count * dstride) {
+            if (r.count == 1 && h > r.h && (size_t)(h - r.h) >= bytes) { r.hstride = (size_t)(h - r.h); r.count = 2; return; }
+            if (r.count > 1 && h == r.h + (size_t)r.count * r.hstride) { r.count++; return; }
+        }
+    }
+    runs.push_back(BfCopyRun{h, d_off, bytes, bytes, 1});
+}
+
 kfs_status kfs_bf_knn_match_pairs(kfs_bf *b, const kfs_bf_pair *pairs, int npairs, int k)
 {
     if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
@@ -355,40 +405,56 @@ kfs_status kfs_bf_knn_match_pairs(kfs_bf *b, const kfs_bf_pair *pairs, int npair
     if (npairs == 0) return KFS_OK;
     KfsDeviceGuard guard(b->device);
     b->launches = 0;
-    // device staging layout: [queries | trains | outs | counts], every block 256-byte aligned;
-    // identical host pointers (one query set against a window of train sets) are uploaded once.
-    std::vector<size_t> oq((size_t)npairs), ot((size_t)npairs), oo((size_t)npairs), oc((size_t)npairs);
-    std::vector<char> upq((size_t)npairs), upt((size_t)npairs);
-    size_t off = 0;
-    auto take = [&](size_t bytes) { size_t r = off; off = kfs_align_up(off + bytes + 1, 256); return r; };
+    int max_rows = 0, max_nq = 0;
     for (int i = 0; i < npairs; i++) {
-        int jq = -1, jt = -1;
-        for (int j = 0; j < i; j++) {
-            if (jq < 0 && pairs[j].query == pairs[i].query && pairs[j].nq == pairs[i].nq) jq = j;
-            if (jt < 0 && pairs[j].train == pairs[i].train && pairs[j].nt == pairs[i].nt) jt = j;
-        }
-        upq[i] = jq < 0; upt[i] = jt < 0;
-        oq[i] = jq >= 0 ? oq[jq] : take((size_t)pairs[i].nq * 32);
-        ot[i] = jt >= 0 ? ot[jt] : take((size_t)pairs[i].nt * 32);
-        oo[i] = take((size_t)pairs[i].nq * k * sizeof(kfs_dmatch));
-        oc[i] = take((size_t)pairs[i].nq * sizeof(int));
+        max_rows = pairs[i].nq > max_rows ? pairs[i].nq : max_rows;
+        max_rows = pairs[i].nt > max_rows ? pairs[i].nt : max_rows;
+        max_nq = pairs[i].nq > max_nq ? pairs[i].nq : max_nq;
     }
-    s = bf_reserve_buf(b, off + 256);
+    const size_t in_slot = kfs_align_up((size_t)max_rows * 32 + 1, 256);
+    const size_t out_slot = kfs_align_up((size_t)max_nq * k * sizeof(kfs_dmatch) + 1, 256);
+    const size_t cnt_slot = kfs_align_up((size_t)max_nq * sizeof(int) + 1, 256);
+    std::unordered_map<BfBufKey, int, BfBufKeyHash> slot_of; // (pointer, rows) -> input slot
+    slot_of.reserve((size_t)npairs * 2);
+    std::vector<BfCopyRun> up, down, down_cnt;
+    std::vector<int> sq((size_t)npairs), st((size_t)npairs);
+    int nslots = 0;
+    auto slot_for = [&](const uint8_t *h, int rows) {
+        const BfBufKey key{h, rows};
+        auto it = slot_of.find(key);
+        if (it != slot_of.end()) return it->second;
+        const int sl = nslots++;
+        slot_of.emplace(key, sl);
+        if (rows > 0) bf_add_to_runs(up, h, (size_t)sl * in_slot, (size_t)rows * 32, in_slot);
+        return sl;
+    };
+    for (int i = 0; i < npairs; i++) { sq[i] = slot_for(pairs[i].query, pairs[i].nq); st[i] = slot_for(pairs[i].train, pairs[i].nt); }
+    const size_t o_out = (size_t)nslots * in_slot, o_cnt = o_out + (size_t)npairs * out_slot;
+    s = bf_reserve_buf(b, o_cnt + (size_t)npairs * cnt_slot + 256);
     if (s) return s;
+    for (const BfCopyRun &r : up) {
+        if (r.count == 1) KFS_CUDA_TRY(cudaMemcpyAsync(b->d_buf + r.d_off, r.h, r.bytes, cudaMemcpyHostToDevice, b->stream));
+        else KFS_CUDA_TRY(cudaMemcpy2DAsync(b->d_buf + r.d_off, in_slot, r.h, r.hstride, r.bytes, (size_t)r.count, cudaMemcpyHostToDevice, b->stream));
+    }
     std::vector<BfPairDev> h((size_t)npairs);
     for (int i = 0; i < npairs; i++) {
-        if (upq[i] && pairs[i].nq) KFS_CUDA_TRY(cudaMemcpyAsync(b->d_buf + oq[i], pairs[i].query, (size_t)pairs[i].nq * 32, cudaMemcpyHostToDevice, b->stream));
-        if (upt[i] && pairs[i].nt) KFS_CUDA_TRY(cudaMemcpyAsync(b->d_buf + ot[i], pairs[i].train, (size_t)pairs[i].nt * 32, cudaMemcpyHostToDevice, b->stream));
-        h[i].query = b->d_buf + oq[i]; h[i].train = b->d_buf + ot[i]; h[i].d_nq = nullptr; h[i].d_nt = nullptr;
-        h[i].out = (kfs_dmatch *)(b->d_buf + oo[i]); h[i].counts = (int *)(b->d_buf + oc[i]);
+        h[i].query = b->d_buf + (size_t)sq[i] * in_slot; h[i].train = b->d_buf + (size_t)st[i] * in_slot; h[i].d_nq = nullptr; h[i].d_nt = nullptr;
+        h[i].out = (kfs_dmatch *)(b->d_buf + o_out + (size_t)i * out_slot); h[i].counts = (int *)(b->d_buf + o_cnt + (size_t)i * cnt_slot);
         h[i].nq = pairs[i].nq; h[i].nt = pairs[i].nt;
+        if (pairs[i].nq) {
+            bf_add_to_runs(down, (const uint8_t *)pairs[i].out, o_out + (size_t)i * out_slot, (size_t)pairs[i].nq * k * sizeof(kfs_dmatch), out_slot);
+            if (pairs[i].counts) bf_add_to_runs(down_cnt, (const uint8_t *)pairs[i].counts, o_cnt + (size_t)i * cnt_slot, (size_t)pairs[i].nq * sizeof(int), cnt_slot);
+        }
     }
     s = bf_launch(b, h.data(), npairs, k);
     if (s) return s;
-    for (int i = 0; i < npairs; i++) {
-        if (!pairs[i].nq) continue;
-        KFS_CUDA_TRY(cudaMemcpyAsync(pairs[i].out, b->d_buf + oo[i], (size_t)pairs[i].nq * k * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, b->stream));
-        if (pairs[i].counts) KFS_CUDA_TRY(cudaMemcpyAsync(pairs[i].counts, b->d_buf + oc[i], (size_t)pairs[i].nq * sizeof(int), cudaMemcpyDeviceToHost, b->stream));
+    for (int pass = 0; pass < 2; pass++) {
+        const std::vector<BfCopyRun> &runs = pass ? down_cnt : down;
+        const size_t dstride = pass ? cnt_slot : out_slot;
+        for (const BfCopyRun &r : runs) {
+            if (r.count == 1) KFS_CUDA_TRY(cudaMemcpyAsync((void *)r.h, b->d_buf + r.d_off, r.bytes, cudaMemcpyDeviceToHost, b->stream));
+            else KFS_CUDA_TRY(cudaMemcpy2DAsync((void *)r.h, r.hstride, b->d_buf + r.d_off, dstride, r.bytes, (size_t)r.count, cudaMemcpyDeviceToHost, b->stream));
+        }
     }
     KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
     return KFS_OK;
@@ -425,7 +491,7 @@ kfs_status kfs_bf_knn_match_ratio(kfs_bf *b, const uint8_t *query, int nq, const
     h.out = (kfs_dmatch *)(b->d_buf + oo); h.counts = nullptr; h.nq = nq; h.nt = nt;
     s = bf_launch(b, &h, 1, 2);
     if (s) return s;
-    k_ratio_compact<<<1, 1024, 0, b->stream>>>(h.out, nq, ratio, (kfs_dmatch *)(b->d_buf + og), (int *)(b->d_buf + on));
+    k_ratio_compact<<<1, 1024, 0, b->stream>>>(b->d_pairs, ratio, (kfs_dmatch *)(b->d_buf + og), 0, (int *)(b->d_buf + on));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_ratio_compact launch: %s", cudaGetErrorString(e));
     b->launches++;

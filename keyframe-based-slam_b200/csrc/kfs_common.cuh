@@ -40,3 +40,21 @@ struct KfsDeviceGuard {
         if (prev >= 0) cudaSetDevice(prev);
     }
 };
+
+// ---- library-internal interfaces between the translation units (not part of the C ABI) -----------------
+// One (query, train) matching problem as the kernels see it (device pointers).
+struct BfPairDev {
+    const uint8_t *query; const uint8_t *train;
+    const int *d_nq; const int *d_nt;
+    kfs_dmatch *out; int *counts;
+    int nq, nt;
+};
+kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const uint8_t *gray, size_t step, size_t frame_stride, int w, int h, int batch,
+                                      const uint8_t *mask, size_t mask_step, size_t mask_frame_stride,
+                                      kfs_keypoint *kp_out, uint8_t *desc_out, int capacity);
+kfs_status kfs_orb_finish_host_batch(kfs_orb *o, int batch, int *n_out);
+void kfs_orb_internal_streams(kfs_orb *o, cudaStream_t *s_in, cudaStream_t *s_out);
+void kfs_orb_internal_start_fence(kfs_orb *o, bool on);
+kfs_status kfs_bf_launch_table(kfs_bf *b, const BfPairDev *d_table, int npairs, int max_nq, int k, cudaStream_t st);
+kfs_status kfs_bf_launch_ratio_table(kfs_bf *b, const BfPairDev *d_table, int npairs, float ratio, kfs_dmatch *good_base, long long good_stride,
+                                     int *n_good, cudaStream_t st);

@@ -30,6 +30,7 @@ struct LevelDev {
 
 struct OrbDev {
     int nlevels, batch, fast_thr, cap_out, list_fs, total_tiles;
+    int frame0;          // first frame of this launch (chunked host pipeline); frame = blockIdx + frame0
     uint32_t *raw;       // [batch][list_fs]  FAST corners after NMS/border/mask: score<<24 | y<<12 | x
     uint32_t *cand_xy;   // [batch][list_fs]  survivors of retainBest(2*quota) on the FAST score
     float *cand_resp;    // [batch][list_fs]  their Harris responses
@@ -204,7 +205,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     __shared__ int s_nout, s_gbase;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + g.frame0;
     const uint32_t tt = __ldg(tile_tab + blockIdx.x);
     const int l = tt >> 24, tiy = (tt >> 12) & 0xfff, tix = tt & 0xfff;
     const LevelDev &L = g.lv[l];
@@ -361,7 +362,7 @@ k_select_fast(const __grid_constant__ OrbDev g)
 {
     __shared__ int s_hist[256];
     __shared__ int s_thr;
-    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+    const int l = blockIdx.x, f = blockIdx.y + g.frame0, tid = threadIdx.x, lane = tid & 31;
     const LevelDev &L = g.lv[l];
     if (L.list_cap == 0) return;
     const int n = min(g.raw_count[f * KFS_MAX_LEVELS + l], L.list_cap);
@@ -422,7 +423,7 @@ k_select_fast(const __grid_constant__ OrbDev g)
 __global__ void __launch_bounds__(256)
 k_harris(const __grid_constant__ OrbDev g)
 {
-    const int l = blockIdx.y, f = blockIdx.z;
+    const int l = blockIdx.y, f = blockIdx.z + g.frame0;
     const LevelDev &L = g.lv[l];
     if (L.list_cap == 0) return;
     const int n = min(g.cand_count[f * KFS_MAX_LEVELS + l], L.list_cap);
@@ -472,7 +473,7 @@ k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
     __shared__ int s_hist[256];
     __shared__ uint32_t s_prefix;
     __shared__ int s_need, s_nkept;
-    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+    const int l = blockIdx.x, f = blockIdx.y + g.frame0, tid = threadIdx.x, lane = tid & 31;
     const LevelDev &L = g.lv[l];
     if (L.list_cap == 0) return;
     const int n = min(g.cand_count[f * KFS_MAX_LEVELS + l], L.list_cap);
@@ -604,7 +605,7 @@ k_describe(const __grid_constant__ OrbDev g)
     __shared__ float s_row[DK][WIN * ROW_P];
     __shared__ float s_angle[DK];
     __shared__ float2 s_rot[DK];
-    const int f = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int f = blockIdx.y + g.frame0, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = blockIdx.x * DK + warp;
     // per-level kept counts -> prefix
     int cnt = 0;
@@ -778,6 +779,15 @@ struct kfs_orb {
     bool ev_made = false;
     float stage_ms[KFS_STAGE_COUNT];
     int *h_counts = nullptr; // pinned staging for n_out
+    // host-buffer pipeline (kfs_orb_detect_and_compute_batch): H2D / kernels / D2H of frame chunks on three streams
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    std::vector<cudaEvent_t> ev_in, ev_cmp;
+    cudaEvent_t ev_start = nullptr;
+    int pipeline_chunk = 0;       // frames per chunk; 0 = auto
+    bool start_fence = true;      // copy streams wait for work already queued on the compute stream (off: replay executor)
+    int pending_capacity = 0;     // capacity of the host batch in flight (enqueue -> finish)
+    uint8_t *mask_stage = nullptr; // raw host mask staged on the device
+    size_t mask_stage_bytes = 0;
     size_t sort_smem_set = 0;
 };
 
@@ -955,67 +965,71 @@ static kfs_status kfs_stage_mark(kfs_orb *o, int idx)
     return KFS_OK;
 }
 
-// Runs the kernel chain on `batch` frames whose level 0 is already described by g.lv[0].img / .mask.
-static kfs_status kfs_orb_run(kfs_orb *o, int batch, const uint8_t *d_mask_in, size_t mask_step, size_t mask_fs)
+// Runs the kernel chain on frames [f0, f0 + nb) whose level 0 is already described by g.lv[0].img / .mask.
+// d_mask_in points at frame f0 of the raw mask (or nullptr).  `first` = first chunk of a call: clears the counters.
+static kfs_status kfs_orb_run(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_in, size_t mask_step, size_t mask_fs, bool first)
 {
     OrbDev &g = o->g;
     const int L = g.nlevels;
     cudaStream_t st = o->stream;
-    g.batch = batch;
-    KFS_CUDA_TRY(cudaMemsetAsync(o->counters, 0, o->counters_bytes, st));
+    g.frame0 = f0;
     const dim3 rb(32, 8);
     const bool has_mask = d_mask_in != nullptr;
-    for (int l = 0; l < L; l++) g.lv[l].mask = has_mask ? o->mpyr[l] : nullptr;
+    if (first) {
+        KFS_CUDA_TRY(cudaMemsetAsync(o->counters, 0, o->counters_bytes, st));
+        for (int l = 0; l < L; l++) g.lv[l].mask = has_mask ? o->mpyr[l] : nullptr;
+    }
     if (has_mask) {
-        k_mask_binarise<<<dim3(kfs_div_up(o->lw[0], 128), kfs_div_up(o->lh[0], 8), batch), rb, 0, st>>>(
-            d_mask_in, (long long)mask_fs, (long long)mask_step, o->mpyr[0], o->lfs[0], o->lpitch[0], o->lw[0], o->lh[0]);
+        k_mask_binarise<<<dim3(kfs_div_up(o->lw[0], 128), kfs_div_up(o->lh[0], 8), nb), rb, 0, st>>>(
+            d_mask_in, (long long)mask_fs, (long long)mask_step, o->mpyr[0] + (size_t)f0 * o->lfs[0], o->lfs[0], o->lpitch[0], o->lw[0], o->lh[0]);
         KFS_LAUNCH_CHECK(o);
     }
     for (int l = 1; l < L; l++) {
-        const uint8_t *simg = g.lv[l - 1].img;
         const long long sfs = g.lv[l - 1].img_fs;
+        const uint8_t *simg = g.lv[l - 1].img + (long long)f0 * sfs;
         const int spitch = g.lv[l - 1].pitch;
+        uint8_t *dimg = o->pyr[l] + (size_t)f0 * o->lfs[l];
+        const uint8_t *smask = has_mask ? o->mpyr[l - 1] + (size_t)f0 * o->lfs[l - 1] : nullptr;
+        uint8_t *dmask = has_mask ? o->mpyr[l] + (size_t)f0 * o->lfs[l] : nullptr;
         const bool fast = o->resize_fast[l] && ((uintptr_t)simg % 4 == 0) && (spitch % 4 == 0) && (sfs % 4 == 0);
         if (fast) {
-            const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8 * RZ_ROWS), batch);
-            k_resize<<<grid, rb, 0, st>>>(simg, sfs, spitch, o->lh[l - 1], o->pyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l],
+            const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8 * RZ_ROWS), nb);
+            k_resize<<<grid, rb, 0, st>>>(simg, sfs, spitch, o->lh[l - 1], dimg, o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l],
                                           o->xtab4[l], o->ytab[l], 0);
             KFS_LAUNCH_CHECK(o);
             if (has_mask) {
-                k_resize<<<grid, rb, 0, st>>>(o->mpyr[l - 1], o->lfs[l - 1], o->lpitch[l - 1], o->lh[l - 1], o->mpyr[l], o->lfs[l], o->lpitch[l],
+                k_resize<<<grid, rb, 0, st>>>(smask, o->lfs[l - 1], o->lpitch[l - 1], o->lh[l - 1], dmask, o->lfs[l], o->lpitch[l],
                                               o->lw[l], o->lh[l], o->xtab4[l], o->ytab[l], 1);
                 KFS_LAUNCH_CHECK(o);
             }
         } else { // scale factor > 2 (taps of a 4-pixel group span more than 8 bytes) or an unaligned caller buffer
-            const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8), batch);
+            const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8), nb);
             k_resize_generic<<<grid, rb, 0, st>>>(simg, sfs, spitch, o->lw[l - 1], o->lh[l - 1],
-                                                  o->pyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 0);
+                                                  dimg, o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 0);
             KFS_LAUNCH_CHECK(o);
             if (has_mask) {
-                k_resize_generic<<<grid, rb, 0, st>>>(o->mpyr[l - 1], o->lfs[l - 1], o->lpitch[l - 1], o->lw[l - 1], o->lh[l - 1],
-                                                      o->mpyr[l], o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 1);
+                k_resize_generic<<<grid, rb, 0, st>>>(smask, o->lfs[l - 1], o->lpitch[l - 1], o->lw[l - 1], o->lh[l - 1],
+                                                      dmask, o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l], o->xtab[l], o->ytab[l], 1);
                 KFS_LAUNCH_CHECK(o);
             }
         }
     }
     if (kfs_stage_mark(o, KFS_STAGE_FAST)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
-        k_fast<<<dim3(g.total_tiles, batch), FAST_THREADS, 0, st>>>(g, o->tile_tab);
+        k_fast<<<dim3(g.total_tiles, nb), FAST_THREADS, 0, st>>>(g, o->tile_tab);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_SELECT_HARRIS)) return KFS_ERR_CUDA;
+    int maxq = 1;
+    for (int l = 0; l < L; l++) maxq = o->quota[l] > maxq ? o->quota[l] : maxq;
     if (g.total_tiles > 0) {
-        k_select_fast<<<dim3(L, batch), SEL_THREADS, 0, st>>>(g);
+        k_select_fast<<<dim3(L, nb), SEL_THREADS, 0, st>>>(g);
         KFS_LAUNCH_CHECK(o);
-        int maxq = 1;
-        for (int l = 0; l < L; l++) maxq = o->quota[l] > maxq ? o->quota[l] : maxq;
-        k_harris<<<dim3(kfs_div_up(2 * maxq + 256, 256), L, batch), 256, 0, st>>>(g);
+        k_harris<<<dim3(kfs_div_up(2 * maxq + 256, 256), L, nb), 256, 0, st>>>(g);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_SELECT_SORT)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
-        int maxq = 1;
-        for (int l = 0; l < L; l++) maxq = o->quota[l] > maxq ? o->quota[l] : maxq;
         int smem_n = (2 * maxq + maxq / 2 + 64 + 63) / 64 * 64;
         if (smem_n > 13312) smem_n = 13312; // 16 B per entry -> 208 KB, under the 227 KB opt-in limit
         const size_t dyn = (size_t)smem_n * 16;
@@ -1023,15 +1037,15 @@ static kfs_status kfs_orb_run(kfs_orb *o, int batch, const uint8_t *d_mask_in, s
             KFS_CUDA_TRY(cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
             o->sort_smem_set = dyn;
         }
-        k_select_sort<<<dim3(L, batch), SORT_THREADS, dyn, st>>>(g, smem_n);
+        k_select_sort<<<dim3(L, nb), SORT_THREADS, dyn, st>>>(g, smem_n);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_ORIENT)) return KFS_ERR_CUDA;
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
-    k_describe<<<dim3(kfs_div_up(g.cap_out, DK), batch), 32 * DK, 0, st>>>(g);
+    k_describe<<<dim3(kfs_div_up(g.cap_out, DK), nb), 32 * DK, 0, st>>>(g);
     KFS_LAUNCH_CHECK(o);
     if (kfs_stage_mark(o, KFS_STAGE_COUNT)) return KFS_ERR_CUDA;
-    o->last_batch = batch;
+    o->last_batch = f0 + nb;
     return KFS_OK;
 }
 
@@ -1095,6 +1109,12 @@ void kfs_orb_destroy(kfs_orb *o)
     kfs_orb_free_arena(o);
     if (o->h_counts) cudaFreeHost(o->h_counts);
     if (o->ev_made) for (int i = 0; i <= KFS_STAGE_COUNT; i++) cudaEventDestroy(o->ev[i]);
+    for (cudaEvent_t e : o->ev_in) cudaEventDestroy(e);
+    for (cudaEvent_t e : o->ev_cmp) cudaEventDestroy(e);
+    if (o->ev_start) cudaEventDestroy(o->ev_start);
+    if (o->mask_stage) cudaFree(o->mask_stage);
+    if (o->s_in) cudaStreamDestroy(o->s_in);
+    if (o->s_out) cudaStreamDestroy(o->s_out);
     if (o->own_stream) cudaStreamDestroy(o->own_stream);
     delete o;
 }
@@ -1159,7 +1179,7 @@ kfs_status kfs_orb_extract_device(kfs_orb *o, const uint8_t *d_gray, size_t step
         }
     }
     if (kfs_stage_mark(o, KFS_STAGE_PYRAMID)) return KFS_ERR_CUDA;
-    return kfs_orb_run(o, batch, d_mask, mask_step, mask_frame_stride);
+    return kfs_orb_run(o, 0, batch, d_mask, mask_step, mask_frame_stride, true);
 }
 
 kfs_status kfs_orb_device_results(kfs_orb *o, const kfs_keypoint **d_kp, const uint8_t **d_desc, const int **d_counts, int *capacity, int *batch)
@@ -1206,55 +1226,165 @@ kfs_status kfs_orb_fetch_results(kfs_orb *o, kfs_keypoint *kp_out, uint8_t *desc
     return rc;
 }
 
+static kfs_status kfs_orb_pipeline_init(kfs_orb *o, int nchunks)
+{
+    if (!o->s_in) KFS_CUDA_TRY(cudaStreamCreateWithFlags(&o->s_in, cudaStreamNonBlocking));
+    if (!o->s_out) KFS_CUDA_TRY(cudaStreamCreateWithFlags(&o->s_out, cudaStreamNonBlocking));
+    if (!o->ev_start) KFS_CUDA_TRY(cudaEventCreateWithFlags(&o->ev_start, cudaEventDisableTiming));
+    while ((int)o->ev_in.size() < nchunks) {
+        cudaEvent_t a, b;
+        KFS_CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        o->ev_in.push_back(a);
+        KFS_CUDA_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        o->ev_cmp.push_back(b);
+    }
+    return KFS_OK;
+}
+
+static kfs_status kfs_h2d_frames(uint8_t *d, size_t dpitch, size_t dfs, const uint8_t *h, size_t step, size_t frame_stride,
+                                 int w, int h_rows, int f0, int nb, cudaStream_t st)
+{
+    if (frame_stride == step * (size_t)h_rows && dfs == dpitch * (size_t)h_rows) {
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(d + (size_t)f0 * dfs, dpitch, h + (size_t)f0 * frame_stride, step, (size_t)w, (size_t)h_rows * nb,
+                                       cudaMemcpyHostToDevice, st));
+    } else {
+        for (int f = f0; f < f0 + nb; f++)
+            KFS_CUDA_TRY(cudaMemcpy2DAsync(d + (size_t)f * dfs, dpitch, h + (size_t)f * frame_stride, step, (size_t)w, (size_t)h_rows,
+                                           cudaMemcpyHostToDevice, st));
+    }
+    return KFS_OK;
+}
+
+// Host-buffer entry point.  The batch is cut into chunks of frames that flow through three streams:
+//   s_in : H2D of chunk i+1        | stream : kernel chain of chunk i        | s_out : D2H of chunk i-1's results
+// so PCIe in, the SMs and PCIe out work concurrently (pinned host buffers give true overlap; pageable ones
+// still work, the copies just serialise inside the driver).  The call returns when everything is on the host.
+} // extern "C"  (the two functions below are library-internal: kfs_replay.cu drives them)
+
+// Enqueues the whole host-buffer pipeline (chunked H2D | kernel chain | D2H of keypoints, descriptors and the
+// per-frame counts) WITHOUT synchronising.  Results are complete once the handle's copy-out stream has drained;
+// kfs_orb_finish_host_batch then hands out the counts.
+kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const uint8_t *gray, size_t step, size_t frame_stride, int w, int h, int batch,
+                                      const uint8_t *mask, size_t mask_step, size_t mask_frame_stride,
+                                      kfs_keypoint *kp_out, uint8_t *desc_out, int capacity)
+{
+    kfs_status s = kfs_orb_check_frame_args(o, gray, step, w, h, batch);
+    if (s) return s;
+    if (capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "capacity < 0");
+    if (w == 0 || h == 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "empty image");
+    if (mask && mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < width");
+    if ((!kp_out || !desc_out) && capacity > 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
+    KfsDeviceGuard guard(o->device);
+    o->launches = 0;
+    s = kfs_orb_ensure(o, w, h, batch, mask != nullptr);
+    if (s) return s;
+    int chunk = o->pipeline_chunk > 0 ? o->pipeline_chunk : (batch >= 8 ? kfs_div_up(batch, 4) : batch);
+    if (chunk > batch) chunk = batch;
+    if (o->profiling) chunk = batch; // per-stage event timing describes one unchunked pass
+    const int nchunks = kfs_div_up(batch, chunk);
+    s = kfs_orb_pipeline_init(o, nchunks);
+    if (s) return s;
+    if (mask) {
+        const size_t need = (size_t)o->lfs[0] * batch;
+        if (need > o->mask_stage_bytes) {
+            if (o->mask_stage) { cudaFree(o->mask_stage); o->mask_stage = nullptr; o->mask_stage_bytes = 0; }
+            KFS_CUDA_TRY(cudaMalloc((void **)&o->mask_stage, need));
+            o->mask_stage_bytes = need;
+        }
+    }
+    if (kfs_stage_mark(o, KFS_STAGE_INGEST)) return KFS_ERR_CUDA;
+    LevelDev &L0 = o->g.lv[0];
+    L0.img = o->pyr[0]; L0.pitch = o->lpitch[0]; L0.img_fs = o->lfs[0];
+    // the copy streams must not start before work already queued on the compute stream (a caller-provided
+    // stream may still be producing / consuming the buffers of an earlier call)
+    if (o->start_fence) {
+        KFS_CUDA_TRY(cudaEventRecord(o->ev_start, o->stream));
+        KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_in, o->ev_start, 0));
+        KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_out, o->ev_start, 0));
+    }
+    const int cp = capacity < o->cap_out ? capacity : o->cap_out;
+    for (int c = 0; c < nchunks; c++) {
+        const int f0 = c * chunk, nb = (f0 + chunk <= batch) ? chunk : batch - f0;
+        s = kfs_h2d_frames(o->pyr[0], (size_t)o->lpitch[0], (size_t)o->lfs[0], gray, step, frame_stride, w, h, f0, nb, o->s_in);
+        if (s) return s;
+        if (mask) {
+            s = kfs_h2d_frames(o->mask_stage, (size_t)o->lpitch[0], (size_t)o->lfs[0], mask, mask_step, mask_frame_stride, w, h, f0, nb, o->s_in);
+            if (s) return s;
+        }
+        KFS_CUDA_TRY(cudaEventRecord(o->ev_in[c], o->s_in));
+        KFS_CUDA_TRY(cudaStreamWaitEvent(o->stream, o->ev_in[c], 0));
+        if (c == 0 && kfs_stage_mark(o, KFS_STAGE_PYRAMID)) return KFS_ERR_CUDA;
+        s = kfs_orb_run(o, f0, nb, mask ? o->mask_stage + (size_t)f0 * o->lfs[0] : nullptr, (size_t)o->lpitch[0], (size_t)o->lfs[0], c == 0);
+        if (s) return s;
+        KFS_CUDA_TRY(cudaEventRecord(o->ev_cmp[c], o->stream));
+        KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_out, o->ev_cmp[c], 0));
+        if (cp > 0) {
+            KFS_CUDA_TRY(cudaMemcpy2DAsync(kp_out + (size_t)f0 * capacity, (size_t)capacity * sizeof(kfs_keypoint),
+                                           o->g.kp + (size_t)f0 * o->cap_out, (size_t)o->cap_out * sizeof(kfs_keypoint),
+                                           (size_t)cp * sizeof(kfs_keypoint), (size_t)nb, cudaMemcpyDeviceToHost, o->s_out));
+            KFS_CUDA_TRY(cudaMemcpy2DAsync(desc_out + (size_t)f0 * capacity * 32, (size_t)capacity * 32,
+                                           o->g.desc + (size_t)f0 * o->cap_out * 32, (size_t)o->cap_out * 32,
+                                           (size_t)cp * 32, (size_t)nb, cudaMemcpyDeviceToHost, o->s_out));
+        }
+    }
+    KFS_CUDA_TRY(cudaMemcpyAsync(o->h_counts, o->g.n_out, sizeof(int) * (size_t)batch, cudaMemcpyDeviceToHost, o->s_out));
+    o->pending_capacity = capacity;
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_finish_host_batch(kfs_orb *o, int batch, int *n_out)
+{
+    const int capacity = o->pending_capacity;
+    const int cp = capacity < o->cap_out ? capacity : o->cap_out;
+    kfs_status rc = KFS_OK;
+    for (int f = 0; f < batch; f++) {
+        n_out[f] = o->h_counts[f];
+        if (n_out[f] > cp) rc = KFS_ERR_CAPACITY;
+    }
+    if (rc == KFS_ERR_CAPACITY) kfs_set_error("output capacity %d too small (handle capacity %d); n_out holds the required counts", capacity, o->cap_out);
+    if (o->profiling && o->ev_made) {
+        for (int i = 0; i < KFS_STAGE_COUNT; i++) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, o->ev[i], o->ev[i + 1]) == cudaSuccess) o->stage_ms[i] = ms;
+            else cudaGetLastError();
+        }
+    }
+    return rc;
+}
+
+void kfs_orb_internal_start_fence(kfs_orb *o, bool on) { o->start_fence = on; }
+
+void kfs_orb_internal_streams(kfs_orb *o, cudaStream_t *s_in, cudaStream_t *s_out)
+{
+    if (s_in) *s_in = o->s_in;
+    if (s_out) *s_out = o->s_out;
+}
+
+extern "C" {
+
+// Host-buffer entry point: enqueue, wait, hand out the counts.
 kfs_status kfs_orb_detect_and_compute_batch(kfs_orb *o, const uint8_t *gray, size_t step, size_t frame_stride, int w, int h, int batch,
                                             const uint8_t *mask, size_t mask_step, size_t mask_frame_stride,
                                             kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out)
 {
     kfs_status s = kfs_orb_check_frame_args(o, gray, step, w, h, batch);
     if (s) return s;
-    if (!n_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "n_out is NULL");
+    if (!n_out || capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "n_out is NULL or capacity < 0");
     for (int f = 0; f < batch; f++) n_out[f] = 0;
     if (w == 0 || h == 0) return KFS_OK; // OpenCV returns early on an empty image
-    if (mask && mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < width");
+    s = kfs_orb_enqueue_host_batch(o, gray, step, frame_stride, w, h, batch, mask, mask_step, mask_frame_stride, kp_out, desc_out, capacity);
+    if (s) return s;
     KfsDeviceGuard guard(o->device);
-    o->launches = 0;
-    s = kfs_orb_ensure(o, w, h, batch, mask != nullptr);
-    if (s) return s;
-    if (kfs_stage_mark(o, KFS_STAGE_INGEST)) return KFS_ERR_CUDA;
-    LevelDev &L0 = o->g.lv[0];
-    L0.img = o->pyr[0]; L0.pitch = o->lpitch[0]; L0.img_fs = o->lfs[0];
-    // host -> device straight into level 0 (and into the scratch half of the mask pyramid's level-0 slot)
-    if (frame_stride == step * (size_t)h) {
-        KFS_CUDA_TRY(cudaMemcpy2DAsync(o->pyr[0], (size_t)o->lpitch[0], gray, step, (size_t)w, (size_t)h * batch, cudaMemcpyHostToDevice, o->stream));
-    } else {
-        for (int f = 0; f < batch; f++)
-            KFS_CUDA_TRY(cudaMemcpy2DAsync(o->pyr[0] + (size_t)f * o->lfs[0], (size_t)o->lpitch[0], gray + (size_t)f * frame_stride, step,
-                                           (size_t)w, (size_t)h, cudaMemcpyHostToDevice, o->stream));
-    }
-    const uint8_t *d_mask = nullptr;
-    if (mask) {
-        // stage the raw mask in the LAST level-0-sized region we own that is not read before it is
-        // overwritten: the kept_xy list area is free until k_select_sort, but may be smaller than a frame;
-        // simplest robust choice: a temporary device buffer.
-        uint8_t *tmp = nullptr;
-        KFS_CUDA_TRY(cudaMallocAsync((void **)&tmp, (size_t)o->lfs[0] * batch, o->stream));
-        if (mask_frame_stride == mask_step * (size_t)h) {
-            KFS_CUDA_TRY(cudaMemcpy2DAsync(tmp, (size_t)o->lpitch[0], mask, mask_step, (size_t)w, (size_t)h * batch, cudaMemcpyHostToDevice, o->stream));
-        } else {
-            for (int f = 0; f < batch; f++)
-                KFS_CUDA_TRY(cudaMemcpy2DAsync(tmp + (size_t)f * o->lfs[0], (size_t)o->lpitch[0], mask + (size_t)f * mask_frame_stride, mask_step,
-                                               (size_t)w, (size_t)h, cudaMemcpyHostToDevice, o->stream));
-        }
-        d_mask = tmp;
-        if (kfs_stage_mark(o, KFS_STAGE_PYRAMID)) return KFS_ERR_CUDA;
-        s = kfs_orb_run(o, batch, d_mask, (size_t)o->lpitch[0], (size_t)o->lfs[0]);
-        cudaFreeAsync(tmp, o->stream);
-    } else {
-        if (kfs_stage_mark(o, KFS_STAGE_PYRAMID)) return KFS_ERR_CUDA;
-        s = kfs_orb_run(o, batch, nullptr, 0, 0);
-    }
-    if (s) return s;
-    return kfs_orb_fetch_results(o, kp_out, desc_out, capacity, n_out);
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->s_out));
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    return kfs_orb_finish_host_batch(o, batch, n_out);
+}
+
+kfs_status kfs_orb_set_pipeline_chunk(kfs_orb *o, int frames)
+{
+    if (!o || frames < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_set_pipeline_chunk: bad arguments");
+    o->pipeline_chunk = frames;
+    return KFS_OK;
 }
 
 kfs_status kfs_orb_detect_and_compute(kfs_orb *o, const uint8_t *gray, size_t step, int w, int h,

@@ -1,0 +1,259 @@
+// kfs_replay.cu — replay executor: the tracker's per-frame loop for batches of frames, kept on the device.
+//
+// Mirrors /root/reference/src/lib/VisualOdometry.cpp:129-172 (VisualOdometry::Track): ExtractFeatures (:138,
+// detectAndCompute :30) -> MatchFeatures against the last keyframe (:144, knnMatch :39, query = keyframe
+// descriptors, train = current frame) -> ratio test (:46).  The reference does this one frame at a time through
+// host memory; here a batch of frames goes through
+//     H2D (chunked) | ORB kernel chain | Hamming kNN on the DEVICE-RESIDENT descriptors | ratio compaction | D2H
+// with two arenas (double buffering): batch i+1 is uploaded while batch i is still being matched and downloaded.
+// Keyframe descriptors never travel back to the device: a keyframe is either a frame of the same batch or an
+// entry of the device-resident keyframe cache (KeyFrame::matDescriptors, KeyFrame.hpp:39).
+// No host threads: everything is stream-ordered; kfs_replay_submit only enqueues, kfs_replay_wait blocks.
+#include "kfs_common.cuh"
+#include <string.h>
+#include <limits.h>
+#include <vector>
+#include <new>
+
+struct ReplaySlot {
+    bool in_flight = false;
+    int batch = 0, ticket = -1;
+    kfs_replay_io io;
+    cudaEvent_t ev_knn = nullptr, ev_done = nullptr;
+    kfs_dmatch *d_knn = nullptr, *d_good = nullptr;
+    int *d_small = nullptr;   // [2][max_batch]: n_good | n_query
+    int *h_small = nullptr;   // pinned mirror
+    BfPairDev *d_table = nullptr, *h_table = nullptr; // device / pinned
+    std::vector<BfPairDev> last_table;
+};
+
+struct kfs_replay {
+    kfs_replay_params p;
+    int device = 0;
+    kfs_orb *orb[2] = {nullptr, nullptr};
+    kfs_bf *bf = nullptr;
+    cudaStream_t compute = nullptr;
+    ReplaySlot slot[2];
+    uint8_t *d_kf_desc = nullptr; // [slots][cap][32]
+    int *d_kf_count = nullptr;    // [slots]
+    int cap = 0;
+    int seq = 0;
+    int launches = 0;
+};
+
+__global__ void k_replay_nquery(const BfPairDev *__restrict__ pairs, int npairs, int *__restrict__ n_query)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npairs) return;
+    const BfPairDev P = pairs[i];
+    int nq = P.nq;
+    if (P.d_nq) nq = min(nq, *P.d_nq);
+    n_query[i] = nq;
+}
+
+static kfs_status replay_finish(kfs_replay *r, int b)
+{
+    ReplaySlot &S = r->slot[b];
+    if (!S.in_flight) return KFS_OK;
+    KFS_CUDA_TRY(cudaEventSynchronize(S.ev_done));
+    S.in_flight = false;
+    kfs_status rc = kfs_orb_finish_host_batch(r->orb[b], S.batch, S.io.n_kp);
+    const int mb = r->p.max_batch;
+    for (int i = 0; i < S.batch; i++) {
+        if (S.io.n_good) S.io.n_good[i] = S.h_small[i];
+        if (S.io.n_query) S.io.n_query[i] = S.h_small[mb + i];
+    }
+    return rc;
+}
+
+extern "C" {
+
+void kfs_replay_default_params(kfs_replay_params *p)
+{
+    if (!p) return;
+    kfs_orb_default_params(&p->orb);
+    p->max_batch = 64;
+    p->keyframe_slots = 8;
+    p->ratio = 0.6f; /* VisualOdometry.cpp:46 */
+}
+
+void kfs_replay_destroy(kfs_replay *r)
+{
+    if (!r) return;
+    KfsDeviceGuard guard(r->device);
+    if (r->compute) cudaStreamSynchronize(r->compute);
+    for (int b = 0; b < 2; b++) {
+        ReplaySlot &S = r->slot[b];
+        if (S.ev_done) { if (S.in_flight) cudaEventSynchronize(S.ev_done); cudaEventDestroy(S.ev_done); }
+        if (S.ev_knn) cudaEventDestroy(S.ev_knn);
+        if (S.d_knn) cudaFree(S.d_knn);
+        if (S.d_good) cudaFree(S.d_good);
+        if (S.d_small) cudaFree(S.d_small);
+        if (S.h_small) cudaFreeHost(S.h_small);
+        if (S.d_table) cudaFree(S.d_table);
+        if (S.h_table) cudaFreeHost(S.h_table);
+        if (r->orb[b]) kfs_orb_destroy(r->orb[b]);
+    }
+    if (r->bf) kfs_bf_destroy(r->bf);
+    if (r->d_kf_desc) cudaFree(r->d_kf_desc);
+    if (r->d_kf_count) cudaFree(r->d_kf_count);
+    if (r->compute) cudaStreamDestroy(r->compute);
+    delete r;
+}
+
+kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_replay **out)
+{
+    if (!params || !out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_replay_create: NULL argument");
+    *out = nullptr;
+    if (params->max_batch < 1 || params->max_batch > 65535 || params->keyframe_slots < 1)
+        KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_replay_create: 1 <= max_batch <= 65535 and keyframe_slots >= 1 required");
+    kfs_replay *r = new (std::nothrow) kfs_replay();
+    if (!r) KFS_FAIL(KFS_ERR_INVALID_ARG, "out of host memory");
+    r->p = *params;
+    r->device = device;
+    kfs_status s = KFS_OK;
+    for (int b = 0; b < 2 && !s; b++) s = kfs_orb_create(&params->orb, device, &r->orb[b]);
+    if (!s) s = kfs_bf_create(KFS_NORM_HAMMING, 0, device, &r->bf);
+    if (s) { kfs_replay_destroy(r); return s; }
+    KfsDeviceGuard guard(device);
+    r->cap = kfs_orb_capacity(r->orb[0]);
+    const size_t mb = (size_t)params->max_batch, cap = (size_t)r->cap;
+#define RP_TRY(expr)                                                                                       \
+    do {                                                                                                   \
+        cudaError_t e__ = (expr);                                                                          \
+        if (e__ != cudaSuccess) {                                                                          \
+            kfs_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__));          \
+            kfs_replay_destroy(r);                                                                         \
+            return KFS_ERR_CUDA;                                                                           \
+        }                                                                                                  \
+    } while (0)
+    RP_TRY(cudaStreamCreateWithFlags(&r->compute, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; b++) {
+        ReplaySlot &S = r->slot[b];
+        kfs_orb_set_stream(r->orb[b], (void *)r->compute);
+        kfs_orb_internal_start_fence(r->orb[b], false); // arena reuse is ordered by replay_finish instead
+        RP_TRY(cudaEventCreateWithFlags(&S.ev_knn, cudaEventDisableTiming));
+        RP_TRY(cudaEventCreateWithFlags(&S.ev_done, cudaEventDisableTiming));
+        RP_TRY(cudaMalloc((void **)&S.d_knn, mb * cap * 2 * sizeof(kfs_dmatch)));
+        RP_TRY(cudaMalloc((void **)&S.d_good, mb * cap * sizeof(kfs_dmatch)));
+        RP_TRY(cudaMalloc((void **)&S.d_small, 2 * mb * sizeof(int)));
+        RP_TRY(cudaMallocHost((void **)&S.h_small, 2 * mb * sizeof(int)));
+        RP_TRY(cudaMalloc((void **)&S.d_table, mb * sizeof(BfPairDev)));
+        RP_TRY(cudaMallocHost((void **)&S.h_table, mb * sizeof(BfPairDev)));
+    }
+    RP_TRY(cudaMalloc((void **)&r->d_kf_desc, (size_t)params->keyframe_slots * cap * 32));
+    RP_TRY(cudaMalloc((void **)&r->d_kf_count, (size_t)params->keyframe_slots * sizeof(int)));
+    RP_TRY(cudaMemset(r->d_kf_count, 0, (size_t)params->keyframe_slots * sizeof(int)));
+#undef RP_TRY
+    *out = r;
+    return KFS_OK;
+}
+
+int kfs_replay_capacity(const kfs_replay *r) { return r ? r->cap : 0; }
+int kfs_replay_last_launches(const kfs_replay *r) { return r ? r->launches : 0; }
+
+kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_replay_frame *plan, int batch, int *ticket)
+{
+    if (!r || !io || !plan || !ticket) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_replay_submit: NULL argument");
+    if (batch < 1 || batch > r->p.max_batch) KFS_FAIL(KFS_ERR_INVALID_ARG, "batch %d outside 1..max_batch=%d", batch, r->p.max_batch);
+    if (!io->n_kp) KFS_FAIL(KFS_ERR_INVALID_ARG, "io->n_kp is NULL");
+    if (io->w <= 0 || io->h <= 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "empty frames");
+    for (int i = 0; i < batch; i++) {
+        const int k = plan[i].keyframe;
+        if (k != KFS_REPLAY_NO_MATCH && (k >= batch || (k < 0 && -(k + 1) >= r->p.keyframe_slots)))
+            KFS_FAIL(KFS_ERR_INVALID_ARG, "plan[%d].keyframe = %d: not a frame of this batch nor a cache slot", i, k);
+        if (plan[i].store_slot < -1 || plan[i].store_slot >= r->p.keyframe_slots)
+            KFS_FAIL(KFS_ERR_INVALID_ARG, "plan[%d].store_slot = %d out of range", i, plan[i].store_slot);
+    }
+    KfsDeviceGuard guard(r->device);
+    const int b = r->seq & 1;
+    ReplaySlot &S = r->slot[b];
+    kfs_status s = replay_finish(r, b); // the arena is reused: its previous batch must be complete (results already delivered)
+    if (s && s != KFS_ERR_CAPACITY) return s;
+    kfs_orb *o = r->orb[b];
+    // 1. upload + extraction (+ D2H of keypoints / descriptors / counts), nothing synchronises
+    s = kfs_orb_enqueue_host_batch(o, io->gray, io->step, io->frame_stride, io->w, io->h, batch, nullptr, 0, 0, io->kp, io->desc, io->capacity);
+    if (s) return s;
+    r->launches = kfs_orb_last_launches(o);
+    const kfs_keypoint *d_kp; const uint8_t *d_desc; const int *d_cnt; int cap = 0, nb = 0;
+    s = kfs_orb_device_results(o, &d_kp, &d_desc, &d_cnt, &cap, &nb);
+    if (s) return s;
+    cudaStream_t s_out;
+    kfs_orb_internal_streams(o, nullptr, &s_out);
+    const bool want_knn = io->knn != nullptr || io->good != nullptr;
+    if (want_knn) {
+        // 2. pair table: query = keyframe descriptors (same batch or cache), train = the frame's own
+        for (int i = 0; i < batch; i++) {
+            BfPairDev P;
+            const int k = plan[i].keyframe;
+            P.train = d_desc + (size_t)i * cap * 32; P.nt = cap; P.d_nt = d_cnt + i;
+            P.out = S.d_knn + (size_t)i * cap * 2; P.counts = nullptr;
+            if (k == KFS_REPLAY_NO_MATCH) { P.query = d_desc; P.nq = 0; P.d_nq = nullptr; P.nt = 0; }
+            else if (k >= 0) { P.query = d_desc + (size_t)k * cap * 32; P.nq = cap; P.d_nq = d_cnt + k; }
+            else { const int sl = -(k + 1); P.query = r->d_kf_desc + (size_t)sl * cap * 32; P.nq = cap; P.d_nq = r->d_kf_count + sl; }
+            S.h_table[i] = P;
+        }
+        const bool same = (int)S.last_table.size() == batch && memcmp(S.last_table.data(), S.h_table, sizeof(BfPairDev) * (size_t)batch) == 0;
+        if (!same) {
+            KFS_CUDA_TRY(cudaMemcpyAsync(S.d_table, S.h_table, sizeof(BfPairDev) * (size_t)batch, cudaMemcpyHostToDevice, r->compute));
+            S.last_table.assign(S.h_table, S.h_table + batch);
+        }
+        // 3. matching (+ ratio test) on the device-resident descriptors
+        s = kfs_bf_launch_table(r->bf, S.d_table, batch, cap, 2, r->compute);
+        if (s) return s;
+        r->launches++;
+        const int mb = r->p.max_batch;
+        if (io->good && r->p.ratio > 0.f) {
+            s = kfs_bf_launch_ratio_table(r->bf, S.d_table, batch, r->p.ratio, S.d_good, (long long)cap, S.d_small, r->compute);
+            if (s) return s;
+            r->launches++;
+        } else {
+            KFS_CUDA_TRY(cudaMemsetAsync(S.d_small, 0, sizeof(int) * (size_t)mb, r->compute));
+        }
+        k_replay_nquery<<<kfs_div_up(batch, 128), 128, 0, r->compute>>>(S.d_table, batch, S.d_small + mb);
+        if (cudaGetLastError() != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_replay_nquery launch failed");
+        r->launches++;
+    }
+    // 4. frames that become keyframes for later batches: descriptors + count into the cache (after this batch's
+    //    matching, so a cache reference in this batch still sees the previous keyframe)
+    for (int i = 0; i < batch; i++) {
+        const int sl = plan[i].store_slot;
+        if (sl < 0) continue;
+        KFS_CUDA_TRY(cudaMemcpyAsync(r->d_kf_desc + (size_t)sl * cap * 32, d_desc + (size_t)i * cap * 32, (size_t)cap * 32, cudaMemcpyDeviceToDevice, r->compute));
+        KFS_CUDA_TRY(cudaMemcpyAsync(r->d_kf_count + sl, d_cnt + i, sizeof(int), cudaMemcpyDeviceToDevice, r->compute));
+    }
+    KFS_CUDA_TRY(cudaEventRecord(S.ev_knn, r->compute));
+    KFS_CUDA_TRY(cudaStreamWaitEvent(s_out, S.ev_knn, 0));
+    if (want_knn) {
+        const int cp = io->capacity < cap ? io->capacity : cap;
+        if (io->knn && cp > 0)
+            KFS_CUDA_TRY(cudaMemcpy2DAsync(io->knn, (size_t)io->capacity * 2 * sizeof(kfs_dmatch), S.d_knn, (size_t)cap * 2 * sizeof(kfs_dmatch),
+                                           (size_t)cp * 2 * sizeof(kfs_dmatch), (size_t)batch, cudaMemcpyDeviceToHost, s_out));
+        if (io->good && cp > 0 && r->p.ratio > 0.f)
+            KFS_CUDA_TRY(cudaMemcpy2DAsync(io->good, (size_t)io->capacity * sizeof(kfs_dmatch), S.d_good, (size_t)cap * sizeof(kfs_dmatch),
+                                           (size_t)cp * sizeof(kfs_dmatch), (size_t)batch, cudaMemcpyDeviceToHost, s_out));
+        KFS_CUDA_TRY(cudaMemcpyAsync(S.h_small, S.d_small, 2 * sizeof(int) * (size_t)r->p.max_batch, cudaMemcpyDeviceToHost, s_out));
+    } else {
+        memset(S.h_small, 0, 2 * sizeof(int) * (size_t)r->p.max_batch);
+    }
+    KFS_CUDA_TRY(cudaEventRecord(S.ev_done, s_out));
+    S.in_flight = true;
+    S.batch = batch;
+    S.io = *io;
+    S.ticket = r->seq;
+    *ticket = r->seq;
+    r->seq++;
+    return KFS_OK;
+}
+
+kfs_status kfs_replay_wait(kfs_replay *r, int ticket)
+{
+    if (!r) KFS_FAIL(KFS_ERR_INVALID_ARG, "replay handle is NULL");
+    KfsDeviceGuard guard(r->device);
+    for (int b = 0; b < 2; b++)
+        if (r->slot[b].in_flight && r->slot[b].ticket == ticket) return replay_finish(r, b);
+    if (ticket >= 0 && ticket < r->seq) return KFS_OK; // already delivered (its arena was reused, or waited before)
+    KFS_FAIL(KFS_ERR_INVALID_ARG, "unknown ticket %d", ticket);
+}
+
+} // extern "C"

@@ -101,6 +101,10 @@ class ORB:
     def set_stream(self, cuda_stream):
         N.check(N.lib().kfs_orb_set_stream(self._h, cuda_stream))
 
+    def set_pipeline_chunk(self, frames):
+        """Frames per chunk of the host-buffer pipeline (0 = automatic)."""
+        N.check(N.lib().kfs_orb_set_pipeline_chunk(self._h, int(frames)))
+
     @property
     def capacity(self):
         return N.lib().kfs_orb_capacity(self._h)
@@ -235,3 +239,62 @@ def pipe_peak(device=0, what="popc"):
     g = C.c_double()
     N.check(N.lib().kfs_pipe_peak(device, 0 if what == "popc" else 1, C.byref(g)))
     return g.value
+
+
+class Replay:
+    """Replay executor (kfs_replay_*): batches of host frames -> keypoints, descriptors, kNN matches against each
+    frame's keyframe and ratio-test survivors, double-buffered on the device (VisualOdometry::Track's front half,
+    /root/reference/src/lib/VisualOdometry.cpp:129-172).  submit() only enqueues; wait() blocks.  All buffers
+    passed to submit() must stay alive (and unmodified) until the matching wait()."""
+    NO_MATCH = N.REPLAY_NO_MATCH
+
+    def __init__(self, nfeatures=500, scaleFactor=1.2, nlevels=8, fastThreshold=20, max_batch=64, keyframe_slots=8,
+                 ratio=0.6, device=0):
+        self._h = C.c_void_p()
+        p = N.ReplayParams()
+        N.lib().kfs_replay_default_params(C.byref(p))
+        p.orb.nfeatures, p.orb.scale_factor, p.orb.nlevels, p.orb.fast_threshold = nfeatures, scaleFactor, nlevels, fastThreshold
+        p.max_batch, p.keyframe_slots, p.ratio = max_batch, keyframe_slots, ratio
+        N.check(N.lib().kfs_replay_create(C.byref(p), device, C.byref(self._h)))
+        self.max_batch = max_batch
+        self._keep = {}
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            N.lib().kfs_replay_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    @property
+    def capacity(self):
+        return N.lib().kfs_replay_capacity(self._h)
+
+    @property
+    def last_launches(self):
+        return N.lib().kfs_replay_last_launches(self._h)
+
+    def alloc_outputs(self, batch, pinned=None):
+        """Output buffers for one submit: dict of numpy arrays (pass pinned=callable(shape, dtype) to place them)."""
+        cap = self.capacity
+        mk = pinned or (lambda shape, dtype: np.zeros(shape, dtype))
+        return dict(kp=mk((batch, cap), KP_DTYPE), desc=mk((batch, cap, 32), np.uint8), n_kp=mk((batch,), np.int32),
+                    knn=mk((batch, cap, 2), DM_DTYPE), n_query=mk((batch,), np.int32),
+                    good=mk((batch, cap), DM_DTYPE), n_good=mk((batch,), np.int32))
+
+    def submit(self, frames, plan, out):
+        """frames uint8 [B,H,W] (host, C-contiguous); plan: list of (keyframe, store_slot); out: alloc_outputs()."""
+        B, H, W = frames.shape
+        assert frames.dtype == np.uint8 and frames.flags.c_contiguous
+        io = N.ReplayIO(frames.ctypes.data, W, W * H, W, H, out["kp"].ctypes.data, out["desc"].ctypes.data, out["kp"].shape[1],
+                        out["n_kp"].ctypes.data, _ptr(out.get("knn")), _ptr(out.get("n_query")), _ptr(out.get("good")), _ptr(out.get("n_good")))
+        pl = (N.ReplayFrame * B)(*[N.ReplayFrame(int(k), int(s)) for k, s in plan])
+        t = C.c_int(-1)
+        N.check(N.lib().kfs_replay_submit(self._h, C.byref(io), pl, B, C.byref(t)))
+        self._keep[t.value] = (frames, out, io, pl)
+        return t.value
+
+    def wait(self, ticket):
+        st = N.check(N.lib().kfs_replay_wait(self._h, ticket), allow=(N.KFS_ERR_CAPACITY,))
+        self._keep.pop(ticket, None)
+        return st
