@@ -364,7 +364,7 @@ def run_ours(args):
     rp = C.c_void_p()
     rpar = N.ReplayParams()
     L.kfs_replay_default_params(C.byref(rpar))
-    rpar.orb.nfeatures, rpar.max_batch, rpar.keyframe_slots, rpar.ratio = NF, B, 2, 0.6
+    rpar.orb.nfeatures, rpar.max_batch, rpar.keyframe_slots, rpar.ratio, rpar.chunk_frames = NF, B, 2, 0.6, args.replay_chunk
     N.check(L.kfs_replay_create(C.byref(rpar), local_rank, C.byref(rp)))
     rcap = L.kfs_replay_capacity(rp)
     plan = (N.ReplayFrame * B)(*[N.ReplayFrame(keyframe_of(i), -1) for i in range(B)])
@@ -515,6 +515,7 @@ def run_ours(args):
                     "steps": Kr, "api": "kfs_replay_submit/kfs_replay_wait (C ABI replay executor): pinned host frames in; keypoints, descriptors, "
                                         "k=2 matches vs keyframe and ratio-test survivors out to pinned host buffers; two batches in flight",
                     "ratio_survivors_per_frame": round(rep_good, 1), "launches_per_step": int(rep_launches),
+                    "replay_chunk_frames": args.replay_chunk or B,
                     "drop_in_calls": dropin},
             "gpu_launches": int(launches),
             "roofline": roofline, "roofline_popc": roofline_popc, "kernels": kernels,
@@ -534,6 +535,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--batch", type=int, default=64, help="frames per GPU per step")
     ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--replay-chunk", type=int, default=0, help="frames per chunk inside one replay batch (0 = whole batch)")
     ap.add_argument("--e2e-chunk", type=int, default=0, help="frames per chunk of the host-buffer pipeline (0 = library default)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--ref-frames-per-worker", type=int, default=8)

@@ -206,6 +206,8 @@ typedef struct kfs_replay_params {
     int32_t max_batch;       /* frames per submit */
     int32_t keyframe_slots;  /* entries of the device-resident keyframe descriptor cache (>= 1) */
     float ratio;             /* ratio-test threshold (reference: 0.6f, :46); <= 0 disables the fused `good` output */
+    int32_t chunk_frames;    /* frames per H2D/kernel/D2H chunk inside one batch; 0 = the whole batch (batches already
+                              * overlap each other; smaller chunks only cut the latency of a lone batch) */
 } kfs_replay_params;
 #define KFS_REPLAY_NO_MATCH INT32_MIN
 typedef struct kfs_replay_frame {

@@ -34,7 +34,8 @@ class BfPair(C.Structure):
 
 
 class ReplayParams(C.Structure):
-    _fields_ = [("orb", OrbParams), ("max_batch", C.c_int32), ("keyframe_slots", C.c_int32), ("ratio", C.c_float)]
+    _fields_ = [("orb", OrbParams), ("max_batch", C.c_int32), ("keyframe_slots", C.c_int32), ("ratio", C.c_float),
+                ("chunk_frames", C.c_int32)]
 
 
 class ReplayFrame(C.Structure):

@@ -75,6 +75,7 @@ void kfs_replay_default_params(kfs_replay_params *p)
     p->max_batch = 64;
     p->keyframe_slots = 8;
     p->ratio = 0.6f; /* VisualOdometry.cpp:46 */
+    p->chunk_frames = 0;
 }
 
 void kfs_replay_destroy(kfs_replay *r)
@@ -105,7 +106,7 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
 {
     if (!params || !out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_replay_create: NULL argument");
     *out = nullptr;
-    if (params->max_batch < 1 || params->max_batch > 65535 || params->keyframe_slots < 1)
+    if (params->max_batch < 1 || params->max_batch > 65535 || params->keyframe_slots < 1 || params->chunk_frames < 0)
         KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_replay_create: 1 <= max_batch <= 65535 and keyframe_slots >= 1 required");
     kfs_replay *r = new (std::nothrow) kfs_replay();
     if (!r) KFS_FAIL(KFS_ERR_INVALID_ARG, "out of host memory");
@@ -132,6 +133,7 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
         ReplaySlot &S = r->slot[b];
         kfs_orb_set_stream(r->orb[b], (void *)r->compute);
         kfs_orb_internal_start_fence(r->orb[b], false); // arena reuse is ordered by replay_finish instead
+        kfs_orb_set_pipeline_chunk(r->orb[b], params->chunk_frames > 0 ? params->chunk_frames : params->max_batch);
         RP_TRY(cudaEventCreateWithFlags(&S.ev_knn, cudaEventDisableTiming));
         RP_TRY(cudaEventCreateWithFlags(&S.ev_done, cudaEventDisableTiming));
         RP_TRY(cudaMalloc((void **)&S.d_knn, mb * cap * 2 * sizeof(kfs_dmatch)));

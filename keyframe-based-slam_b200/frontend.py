@@ -249,12 +249,12 @@ class Replay:
     NO_MATCH = N.REPLAY_NO_MATCH
 
     def __init__(self, nfeatures=500, scaleFactor=1.2, nlevels=8, fastThreshold=20, max_batch=64, keyframe_slots=8,
-                 ratio=0.6, device=0):
+                 ratio=0.6, chunk_frames=0, device=0):
         self._h = C.c_void_p()
         p = N.ReplayParams()
         N.lib().kfs_replay_default_params(C.byref(p))
         p.orb.nfeatures, p.orb.scale_factor, p.orb.nlevels, p.orb.fast_threshold = nfeatures, scaleFactor, nlevels, fastThreshold
-        p.max_batch, p.keyframe_slots, p.ratio = max_batch, keyframe_slots, ratio
+        p.max_batch, p.keyframe_slots, p.ratio, p.chunk_frames = max_batch, keyframe_slots, ratio, chunk_frames
         N.check(N.lib().kfs_replay_create(C.byref(p), device, C.byref(self._h)))
         self.max_batch = max_batch
         self._keep = {}
