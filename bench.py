@@ -460,17 +460,18 @@ def run_ours(args):
         "fast": sum(px),
         "select_harris": 2 * sum(quotas) * 81 + 4 * sum(fast_counts),
         "select_sort": 2 * sum(quotas) * 16,
-        "describe": nkp * (43 * 43 + 32 + 28),
+        "blur": 2 * sum(px),
+        "describe": nkp * (709 + 512 + 32 + 28),
     }
     kernels = []
-    for k_ in ("pyramid", "fast", "select_harris", "select_sort", "describe"):
+    for k_ in ("pyramid", "fast", "select_harris", "select_sort", "blur", "describe"):
         t = acc.get(k_, 0.0)
         gbs = alg[k_] * B / (t * 1e-3) / 1e9 if t > 0 else 0.0
         kernels.append({"stage": k_, "ms_per_batch": round(t, 4), "us_per_frame": round(t * 1e3 / B, 3), "alg_bytes_per_frame": int(alg[k_]),
                         "achieved_gbs": round(gbs, 1), "frac_hbm": round(gbs / hbm_peak, 4)})
     dom = max(kernels, key=lambda d: d["ms_per_batch"])
     dom_kernel = {"pyramid": "k_resize", "fast": "k_fast", "select_harris": "k_select_fast+k_harris", "select_sort": "k_select_sort",
-                  "describe": "k_describe"}[dom["stage"]]
+                  "blur": "k_blur7", "describe": "k_describe"}[dom["stage"]]
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(dom_kernel)

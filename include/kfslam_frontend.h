@@ -147,7 +147,7 @@ KFS_API kfs_status kfs_orb_download_fast_corners(kfs_orb *orb, int frame, int le
 /* Per-stage device time of the last extraction when profiling is on (cudaEvent pairs on the handle's
  * stream). Stage ids: KFS_STAGE_*.  ms[KFS_STAGE_COUNT]. */
 enum { KFS_STAGE_INGEST = 0, KFS_STAGE_PYRAMID = 1, KFS_STAGE_FAST = 2, KFS_STAGE_SELECT_HARRIS = 3,
-       KFS_STAGE_SELECT_SORT = 4, KFS_STAGE_ORIENT = 5, KFS_STAGE_DESCRIBE = 6, KFS_STAGE_COUNT = 7 };
+       KFS_STAGE_SELECT_SORT = 4, KFS_STAGE_BLUR = 5, KFS_STAGE_DESCRIBE = 6, KFS_STAGE_COUNT = 7 };
 KFS_API kfs_status kfs_orb_set_profiling(kfs_orb *orb, int on);
 KFS_API kfs_status kfs_orb_stage_times(kfs_orb *orb, float *ms);
 /* Number of kernel launches the last extraction issued (bench.py's gpu_launches). */

@@ -16,7 +16,7 @@ assert KP_DTYPE.itemsize == 28 and DM_DTYPE.itemsize == 16
 
 KFS_OK, KFS_ERR_INVALID_ARG, KFS_ERR_UNSUPPORTED, KFS_ERR_CAPACITY, KFS_ERR_CUDA, KFS_ERR_NO_DEVICE = range(6)
 STATUS_NAMES = ["KFS_OK", "KFS_ERR_INVALID_ARG", "KFS_ERR_UNSUPPORTED", "KFS_ERR_CAPACITY", "KFS_ERR_CUDA", "KFS_ERR_NO_DEVICE"]
-STAGE_NAMES = ["ingest", "pyramid", "fast", "select_harris", "select_sort", "orient", "describe"]
+STAGE_NAMES = ["ingest", "pyramid", "fast", "select_harris", "select_sort", "blur", "describe"]
 NORM_HAMMING = 6
 ORB_HARRIS_SCORE, ORB_FAST_SCORE = 0, 1
 

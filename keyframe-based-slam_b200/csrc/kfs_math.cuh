@@ -21,7 +21,8 @@ KFS_HD float kfs_add(float a, float b) { return __fadd_rn(a, b); }
 KFS_HD float kfs_sub(float a, float b) { return __fsub_rn(a, b); }
 KFS_HD float kfs_div(float a, float b) { return __fdiv_rn(a, b); }
 KFS_HD float kfs_fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
-KFS_HD int kfs_rint(float a) { return __float2int_rn(a); }
+// round-half-even through the 1.5*2^23 magic add (exact for |a| < 2^22): keeps the XU pipe (F2I) out of the loops
+KFS_HD int kfs_rint(float a) { return __float_as_int(__fadd_rn(a, 12582912.f)) - 0x4B400000; }
 #else
 KFS_HD float kfs_mul(float a, float b) { return a * b; }
 KFS_HD float kfs_add(float a, float b) { return a + b; }
@@ -166,11 +167,33 @@ KFS_HD int kfs_blur_col(float rm3, float rm2, float rm1, float r0, float rp1, fl
     return v < 0 ? 0 : (v > 255 ? 255 : v);
 }
 
+// same, result left as the bits of (s + 1.5*2^23): byte 0 is the rounded pixel (s is a convex combination of u8 values,
+// so 0 <= rint(s) <= 255 and no saturation can trigger)
+KFS_HD uint32_t kfs_blur_col_bits(float rm3, float rm2, float rm1, float r0, float rp1, float rp2, float rp3)
+{
+    float s = kfs_mul(KFS_G3, r0);
+    s = kfs_fma(KFS_G2, kfs_add(rp1, rm1), s);
+    s = kfs_fma(KFS_G1, kfs_add(rp2, rm2), s);
+    s = kfs_fma(KFS_G0, kfs_add(rp3, rm3), s);
+    s = kfs_add(s, 12582912.f);
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(s);
+#else
+    union { float f; uint32_t u; } c; c.f = s; return c.u;
+#endif
+}
+
 // ---- a1.10 rotated BRIEF sample offset ----------------------------------------------------------------
 // (x,y) pattern point, a = cos, b = sin: X = x*a - y*b, Y = x*b + y*a (mul, mul, sub/add; no FMA), rint.
 KFS_HD void kfs_brief_rot(int px, int py, float a, float b, int *ix, int *iy)
 {
     float fx = (float)px, fy = (float)py;
+    *ix = kfs_rint(kfs_sub(kfs_mul(fx, a), kfs_mul(fy, b)));
+    *iy = kfs_rint(kfs_add(kfs_mul(fx, b), kfs_mul(fy, a)));
+}
+
+KFS_HD void kfs_brief_rotf(float fx, float fy, float a, float b, int *ix, int *iy)
+{
     *ix = kfs_rint(kfs_sub(kfs_mul(fx, a), kfs_mul(fy, b)));
     *iy = kfs_rint(kfs_add(kfs_mul(fx, b), kfs_mul(fy, a)));
 }

@@ -20,6 +20,9 @@
 struct LevelDev {
     const uint8_t *img;      // frame f of this level at img + f*img_fs
     const uint8_t *mask;     // nullptr when no mask
+    uint8_t *blur;           // 7x7-blurred level (a1.9), frame f at blur + f*img_fs_blur
+    long long img_fs_blur;
+    int pitch_blur;
     long long img_fs, mask_fs;
     int pitch, mask_pitch;
     int w, h, quota;
@@ -45,9 +48,6 @@ struct OrbDev {
     LevelDev lv[KFS_MAX_LEVELS];
 };
 
-__device__ __align__(4) const int8_t d_pattern[1024] = {
-#include "orb_pattern.inc"
-};
 
 // ======================================================================================================
 // a1.1 / a1.2  pyramid: INTER_LINEAR_EXACT, 8.8 fixed point, chained level to level
@@ -579,34 +579,126 @@ k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
 }
 
 // ======================================================================================================
-// a1.7 - a1.10  orientation + keypoint record + on-demand blur + rotated BRIEF: one WARP per keypoint
+// a1.9  7x7 sigma=2 blur of every level (OpenCV's sepFilter2D float path, exact FMA order: kfs_blur_row / _col)
 // ======================================================================================================
-// grid (ceil(cap_out/4), frame), 4 warps per CTA, warp = output slot.
+// One CTA = one 128 x 32 tile of one level of one frame (tile table like k_fast's), 128 threads.
+//   source tile 160 x 38 bytes (origin (x0-16, y0-3): rows are 16-byte aligned -> LDG.128)
+//   row pass   : item = (row, 16-pixel segment): 22 source bytes -> I2F.U8 with byte select -> 16 x 7 FFMA (immediate
+//                form) -> 4 x STS.128 into the 38 x 128 float tile
+//   column pass: thread = (4 adjacent columns, 8-row segment): LDS.128 down the column block, sliding 7-row window
+//                in registers, round-half-even by the 1.5*2^23 magic add (no F2I), 4 pixels packed -> one STG.32;
+//                a warp writes 128 contiguous bytes per row
+// Borders: source rows/columns outside the image are clamped / zero-filled instead of REFLECT_101: a descriptor
+// sample lies >= 31-19 = 12 px inside the level and its 7x7 support >= 9 px inside, so those pixels of the blurred
+// level are never read (rotated BRIEF reaches <= 18.4 px from a keypoint that is >= 31 px inside).
+constexpr int BT_W = 128, BT_H = 26, BT_THREADS = 128; // 26 + 6 halo rows = 32 -> the row pass is exactly 2 rounds of 128 items
+constexpr int BT_Y0 = 12;                               // first blurred row / rows [12, H-12) are the only ones ever sampled
+constexpr int BS_P = 160, BS_H = BT_H + 6;
+
+__global__ void __launch_bounds__(BT_THREADS)
+k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
+{
+    __shared__ __align__(16) uint8_t s_src[BS_P * BS_H];
+    __shared__ __align__(16) float s_row[BS_H * BT_W];
+    const int tid = threadIdx.x;
+    const int f = blockIdx.y + g.frame0;
+    const uint32_t tt = __ldg(tile_tab + blockIdx.x);
+    const int l = tt >> 24, tiy = (tt >> 12) & 0xfff, tix = tt & 0xfff;
+    const LevelDev &L = g.lv[l];
+    const int H = L.h, pitch = L.pitch;
+    const int x0 = BT_W * tix, y0 = BT_Y0 + BT_H * tiy;
+    const uint8_t *img = L.img + (long long)f * L.img_fs;
+    for (int i = tid; i < BS_H * (BS_P / 16); i += BT_THREADS) {
+        const int r = i / (BS_P / 16), c = i - r * (BS_P / 16);
+        const int gy = min(max(y0 - 3 + r, 0), H - 1), gx = x0 - 16 + 16 * c;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (gx >= 0 && gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
+        *reinterpret_cast<uint4 *>(s_src + r * BS_P + 16 * c) = v;
+    }
+    __syncthreads();
+    // ---- row pass
+#pragma unroll 1
+    for (int item = tid; item < BS_H * 8; item += BT_THREADS) {
+        const int r = item >> 3, sg = item & 7;
+        const uint8_t *base = s_src + r * BS_P + 16 + 16 * sg;
+        const uint32_t wl = *reinterpret_cast<const uint32_t *>(base - 4);
+        const uint4 wm = *reinterpret_cast<const uint4 *>(base);
+        const uint32_t wr = *reinterpret_cast<const uint32_t *>(base + 16);
+        float p[22];
+        p[0] = (float)((wl >> 8) & 0xffu); p[1] = (float)((wl >> 16) & 0xffu); p[2] = (float)(wl >> 24);
+        const uint32_t w4[4] = {wm.x, wm.y, wm.z, wm.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            p[3 + 4 * k] = (float)(w4[k] & 0xffu); p[4 + 4 * k] = (float)((w4[k] >> 8) & 0xffu);
+            p[5 + 4 * k] = (float)((w4[k] >> 16) & 0xffu); p[6 + 4 * k] = (float)(w4[k] >> 24);
+        }
+        p[19] = (float)(wr & 0xffu); p[20] = (float)((wr >> 8) & 0xffu); p[21] = (float)((wr >> 16) & 0xffu);
+        // float4 slot c4 of a row lives at physical slot c4 ^ ((c4 >> 3) & 3): the 8 lanes of a quarter warp (sg = 0..7,
+        // same k) then hit 8 distinct 16-byte bank groups instead of 2; the column pass reads a permutation of a full row
+        float4 *out = reinterpret_cast<float4 *>(s_row + r * BT_W);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            float4 o;
+            o.x = kfs_blur_row(p[4 * k + 0], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6]);
+            o.y = kfs_blur_row(p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7]);
+            o.z = kfs_blur_row(p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8]);
+            o.w = kfs_blur_row(p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8], p[4 * k + 9]);
+            out[(4 * sg + k) ^ (sg >> 1)] = o;
+        }
+    }
+    __syncthreads();
+    // ---- column pass
+    {
+        const int cg = tid & 31, rs = tid >> 5;           // warp rs owns output rows [r0, r0 + n): 7, 7, 6, 6
+        const int r0 = rs < 2 ? 7 * rs : 14 + 6 * (rs - 2), n = rs < 2 ? 7 : 6;
+        const float4 *col = reinterpret_cast<const float4 *>(s_row + r0 * BT_W) + (cg ^ ((cg >> 3) & 3));
+        float4 q0 = col[0], q1 = col[BT_W / 4], q2 = col[2 * (BT_W / 4)], q3 = col[3 * (BT_W / 4)], q4 = col[4 * (BT_W / 4)],
+               q5 = col[5 * (BT_W / 4)];
+        uint8_t *dst = L.blur + (long long)f * L.img_fs_blur + (long long)(y0 + r0) * L.pitch_blur + x0 + 4 * cg;
+        const int ylim = H - BT_Y0;
+#pragma unroll
+        for (int k = 0; k < 7; k++) {
+            if (k >= n) break;
+            const float4 q6 = col[(k + 6) * (BT_W / 4)];
+            const uint32_t a = kfs_blur_col_bits(q0.x, q1.x, q2.x, q3.x, q4.x, q5.x, q6.x);
+            const uint32_t b = kfs_blur_col_bits(q0.y, q1.y, q2.y, q3.y, q4.y, q5.y, q6.y);
+            const uint32_t c = kfs_blur_col_bits(q0.z, q1.z, q2.z, q3.z, q4.z, q5.z, q6.z);
+            const uint32_t d = kfs_blur_col_bits(q0.w, q1.w, q2.w, q3.w, q4.w, q5.w, q6.w);
+            // byte 0 of each magic-rounded float is the pixel
+            const uint32_t w = __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
+            if (y0 + r0 + k < ylim) *reinterpret_cast<uint32_t *>(dst + (long long)k * L.pitch_blur) = w;
+            q0 = q1; q1 = q2; q2 = q3; q3 = q4; q4 = q5; q5 = q6;
+        }
+    }
+}
+
+// ======================================================================================================
+// a1.7 / a1.8 / a1.10  orientation + keypoint record + rotated BRIEF: one WARP per keypoint
+// ======================================================================================================
+// grid (ceil(cap_out/DK), frame), DK warps per CTA, warp = output slot.
 //   1. slot -> (level, rank) through the per-level kept counts (warp prefix), read (x, y, response)
-//   2. the 43x43 window around the keypoint -> shared memory as bytes: 43 rows x 4 aligned 16-byte chunks
-//      (uint4 loads; the window's x origin is absorbed into a 0..15 byte shift `sh`)
-//   3. intensity-centroid moments from the window (lane = disc column; the disc is symmetric so column u spans
-//      |v| <= umax[|u|]); kfs_fast_atan2 (OpenCV's polynomial, no FMA)
-//   4. fp64 sincos of the 4 keypoints of the CTA by 4 lanes (dense) instead of once per warp; cv::KeyPoint record
-//   5. row pass of the 7x7 blur (43 rows x 37 cols, exact sepFilter2D order kfs_blur_row), 86 items over 3 rounds
-//   6. rotated BRIEF: every sampled point is blurred on demand with the column pass (kfs_blur_col) from the
-//      row-pass buffer — only the <= 512 sampled positions are ever blurred, not the 37x37 patch; 8 ballots give
-//      the 8 descriptor words.
-// The reference blurs every level in full (Σpx read + Σpx write per frame); keypoints sit >= 31 px inside the
-// level and the rotated pattern reaches <= 18 px, so this is exact and the blurred level never exists in HBM.
-constexpr int DK = 4;                 // keypoints (warps) per CTA
-constexpr int WIN = 43, RAW_P = 68;   // raw window rows: 64 bytes + 4 pad (17 words: odd => rows hit distinct banks)
-constexpr int BL_P = 40;              // blurred 37x37 patch (u8), aliases the raw window once the row pass is done
-constexpr int ROW_C = 37, ROW_P = 37; // row-pass output 43 rows x 37 cols (odd pitch: conflict-free row items)
+//   2. intensity-centroid moments on the un-blurred level (lane = disc column u, |v| <= umax[|u|]);
+//      kfs_fast_atan2 (OpenCV's polynomial, no FMA)
+//   3. fp64 sincos of the DK keypoints of the CTA by DK lanes (dense) instead of once per warp; cv::KeyPoint record
+//   4. rotated BRIEF on the blurred level: lane = pair 32h + lane, 8 ballots give the 8 descriptor words; sample
+//      coordinates are rounded half-even with the magic add (kfs_rint), the float pattern table saves the I2Fs
+constexpr int DK = 8;
+constexpr int IW_P = 48, BW_P = 64; // window pitches: un-blurred (IC), blurred (BRIEF)
+__device__ __align__(16) const float d_patf[1024] = {
+#include "orb_pattern.inc"
+};
+
 __global__ void __launch_bounds__(32 * DK)
 k_describe(const __grid_constant__ OrbDev g)
 {
-    __shared__ __align__(16) uint8_t s_raw[DK][WIN * RAW_P + 4];
-    __shared__ float s_row[DK][WIN * ROW_P];
+    __shared__ __align__(16) uint8_t s_wi[DK][31 * IW_P];
+    __shared__ __align__(16) uint8_t s_wb[DK][37 * BW_P];
     __shared__ float s_angle[DK];
     __shared__ float2 s_rot[DK];
     const int f = blockIdx.y + g.frame0, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = blockIdx.x * DK + warp;
+    uint8_t *wi = s_wi[warp], *wb = s_wb[warp];
+    int shi = 0, shb = 0;
     // per-level kept counts -> prefix
     int cnt = 0;
     if (lane < g.nlevels) cnt = min(g.kept_count[f * KFS_MAX_LEVELS + lane], g.lv[lane].list_cap);
@@ -618,12 +710,11 @@ k_describe(const __grid_constant__ OrbDev g)
     }
     const int total = __shfl_sync(0xffffffffu, incl, 31);
     if (blockIdx.x == 0 && threadIdx.x == 0) g.n_out[f] = total;
-    if (blockIdx.x * DK >= min(total, g.cap_out)) return; // whole CTA beyond the last keypoint
-    const bool valid = slot < min(total, g.cap_out);
-    int x = 0, y = 0, level = 0, sh = 0;
+    const int nvalid = min(total, g.cap_out);
+    if (blockIdx.x * DK >= nvalid) return; // whole CTA beyond the last keypoint
+    const bool valid = slot < nvalid;
+    int x = 0, y = 0, level = 0;
     float resp = 0.f, angle = 0.f;
-    uint8_t *raw = s_raw[warp];
-    float *rowb = s_row[warp];
     if (valid) {
         level = __popc(__ballot_sync(0xffffffffu, incl <= slot));
         const int excl = __shfl_sync(0xffffffffu, incl - cnt, level);
@@ -632,17 +723,29 @@ k_describe(const __grid_constant__ OrbDev g)
         const uint32_t xy = g.kept_xy[li];
         x = xy & 0xfff; y = (xy >> 12) & 0xfff;
         resp = g.kept_resp[li];
-        // ---- window -> smem
-        const int ox = x - 21, ax = ox & ~15;
-        sh = ox & 15;
-        const uint8_t *src = L.img + (long long)f * L.img_fs + (long long)(y - 21) * L.pitch + ax;
-#pragma unroll 2
-        for (int i = lane; i < WIN * 4; i += 32) {
-            const int r = i >> 2, q = i & 3;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (ax + 16 * q < L.pitch) v = __ldg(reinterpret_cast<const uint4 *>(src + (long long)r * L.pitch + 16 * q));
-            uint32_t *dst = reinterpret_cast<uint32_t *>(raw + r * RAW_P + 16 * q);
-            dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+        // ---- windows -> shared memory with aligned 16-byte loads: un-blurred 31 rows x 48 B (IC disc), blurred
+        //      37 rows x 64 B (rotated BRIEF reach); the x origins are rounded down to 16, the remainders kept as shifts
+        {
+            const int ox = x - 15, ax = ox & ~15;
+            shi = ox & 15;
+            const uint8_t *src = L.img + (long long)f * L.img_fs + (long long)(y - 15) * L.pitch + ax;
+#pragma unroll 1
+            for (int i = lane; i < 31 * 3; i += 32) {
+                const int r = i / 3, q = i - 3 * r;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (ax + 16 * q + 16 <= L.pitch) v = __ldg(reinterpret_cast<const uint4 *>(src + (long long)r * L.pitch + 16 * q));
+                *reinterpret_cast<uint4 *>(wi + r * IW_P + 16 * q) = v;
+            }
+            const int oxb = x - 18, axb = oxb & ~15;
+            shb = oxb & 15;
+            const uint8_t *srb = L.blur + (long long)f * L.img_fs_blur + (long long)(y - 18) * L.pitch_blur + axb;
+#pragma unroll 1
+            for (int i = lane; i < 37 * 4; i += 32) {
+                const int r = i >> 2, q = i & 3;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (axb + 16 * q + 16 <= L.pitch_blur) v = __ldg(reinterpret_cast<const uint4 *>(srb + (long long)r * L.pitch_blur + 16 * q));
+                *reinterpret_cast<uint4 *>(wb + r * BW_P + 16 * q) = v;
+            }
         }
         __syncwarp();
         // ---- IC moments: lane = column u
@@ -650,11 +753,11 @@ k_describe(const __grid_constant__ OrbDev g)
         if (lane < 31) {
             const int u = lane - 15, au = u < 0 ? -u : u;
             const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * au)) & 15ull);
-            const uint8_t *c = raw + 21 * RAW_P + sh + 21 + u;
+            const uint8_t *c = wi + 15 * IW_P + shi + 15 + u;
             int colsum = 0;
 #pragma unroll 4
             for (int v = -d; v <= d; v++) {
-                const int I = c[v * RAW_P];
+                const int I = c[v * IW_P];
                 colsum += I;
                 m01 += v * I;
             }
@@ -669,35 +772,17 @@ k_describe(const __grid_constant__ OrbDev g)
         if (lane == 0) s_angle[warp] = angle;
     }
     __syncthreads();
-    if (threadIdx.x < DK && blockIdx.x * DK + (int)threadIdx.x < min(total, g.cap_out)) {
+    if (threadIdx.x < DK && blockIdx.x * DK + (int)threadIdx.x < nvalid) {
         const float rad = kfs_mul(s_angle[threadIdx.x], (float)(3.1415926535897932384626433832795 / 180.f));
         double sn, cs;
         sincos((double)rad, &sn, &cs);
         s_rot[threadIdx.x] = make_float2((float)cs, (float)sn);
     }
-    if (valid) {
-        // ---- row pass: item = (segment, row); segment 0 -> cols 0..18, segment 1 -> cols 19..36
-#pragma unroll 1
-        for (int item = lane; item < 2 * WIN; item += 32) {
-            const int seg = item >= WIN ? 1 : 0, r = item - seg * WIN;
-            const int c0 = seg * 19, n = seg ? 18 : 19;
-            const uint8_t *w = raw + r * RAW_P + sh + c0;
-            float *out = rowb + r * ROW_P + c0;
-            float p0 = (float)w[0], p1 = (float)w[1], p2 = (float)w[2], p3 = (float)w[3], p4 = (float)w[4], p5 = (float)w[5], p6;
-#pragma unroll
-            for (int k = 0; k < 19; k++) {
-                if (k < n) {
-                    p6 = (float)w[k + 6];
-                    out[k] = kfs_blur_row(p0, p1, p2, p3, p4, p5, p6);
-                    p0 = p1; p1 = p2; p2 = p3; p3 = p4; p4 = p5; p5 = p6;
-                }
-            }
-        }
-    }
-    __syncthreads(); // s_rot ready (and this warp's row buffer complete)
+    __syncthreads();
     if (!valid) return;
     const float2 ab = s_rot[warp];
-    const float sc = g.lv[level].scale;
+    const LevelDev &L = g.lv[level];
+    const float sc = L.scale;
     const long long o = (long long)f * g.cap_out + slot;
     if (lane == 0) {
         kfs_keypoint kp;
@@ -710,36 +795,17 @@ k_describe(const __grid_constant__ OrbDev g)
         kp.class_id = -1;
         g.kp[o] = kp;
     }
-    // ---- column pass: 111 items = (vertical segment, column); rows [0,13) [13,25) [25,37); the blurred patch
-    // overwrites the raw window (no longer needed: every lane of this warp passed the barrier after its row items)
-    uint8_t *bl = raw;
-#pragma unroll 1
-    for (int item = lane; item < 3 * ROW_C; item += 32) {
-        const int vs = item >= 2 * ROW_C ? 2 : (item >= ROW_C ? 1 : 0), c = item - vs * ROW_C;
-        const int o0 = vs == 0 ? 0 : (vs == 1 ? 13 : 25), n = vs == 0 ? 13 : 12;
-        const float *r = rowb + o0 * ROW_P + c;
-        float q0 = r[0], q1 = r[ROW_P], q2 = r[2 * ROW_P], q3 = r[3 * ROW_P], q4 = r[4 * ROW_P], q5 = r[5 * ROW_P], q6;
-#pragma unroll
-        for (int k = 0; k < 13; k++) {
-            if (k < n) {
-                q6 = r[(k + 6) * ROW_P];
-                bl[(o0 + k) * BL_P + c] = (uint8_t)kfs_blur_col(q0, q1, q2, q3, q4, q5, q6);
-                q0 = q1; q1 = q2; q2 = q3; q3 = q4; q4 = q5; q5 = q6;
-            }
-        }
-    }
-    __syncwarp();
-    // OpenCV recomputes the integer centre from the scaled float point: cvRound(pt * (1.f/scale)).  The window was
-    // fetched around (x, y); (x*s)*(1/s) is within 1e-3 of x for x < 4096, so the rounded centre is (x, y) itself.
+    // OpenCV recomputes the integer centre from the scaled float point: cvRound(pt * (1.f/scale)).  (x*s)*(1/s) is
+    // within 1e-3 of x for x < 4096, so the rounded centre is (x, y) itself.
+    const uint8_t *bl = wb + 18 * BW_P + shb + 18;
     uint32_t word = 0;
-#pragma unroll 2
+#pragma unroll 4
     for (int h = 0; h < 8; h++) {
-        const int pair = 32 * h + lane;
-        const char4 pt = *reinterpret_cast<const char4 *>(d_pattern + 4 * pair);
+        const float4 pt = __ldg(reinterpret_cast<const float4 *>(d_patf) + 32 * h + lane);
         int ix0, iy0, ix1, iy1;
-        kfs_brief_rot(pt.x, pt.y, ab.x, ab.y, &ix0, &iy0);
-        kfs_brief_rot(pt.z, pt.w, ab.x, ab.y, &ix1, &iy1);
-        const int v0 = bl[(18 + iy0) * BL_P + 18 + ix0], v1 = bl[(18 + iy1) * BL_P + 18 + ix1];
+        kfs_brief_rotf(pt.x, pt.y, ab.x, ab.y, &ix0, &iy0);
+        kfs_brief_rotf(pt.z, pt.w, ab.x, ab.y, &ix1, &iy1);
+        const int v0 = bl[iy0 * BW_P + ix0], v1 = bl[iy1 * BW_P + ix1];
         const uint32_t b = __ballot_sync(0xffffffffu, v0 < v1);
         if (lane == h) word = b;
     }
@@ -762,6 +828,9 @@ struct kfs_orb {
     float lscale[KFS_MAX_LEVELS];
     long long lfs[KFS_MAX_LEVELS];
     uint8_t *pyr[KFS_MAX_LEVELS];   // internal level buffers (level 0 included)
+    uint8_t *bpyr[KFS_MAX_LEVELS];  // blurred levels (a1.9)
+    uint32_t *blur_tab = nullptr;   // blur tile -> level<<24 | tiy<<12 | tix
+    int blur_tiles = 0;
     uint8_t *mpyr[KFS_MAX_LEVELS];  // mask pyramid
     uint32_t *xtab[KFS_MAX_LEVELS], *ytab[KFS_MAX_LEVELS];
     uint4 *xtab4[KFS_MAX_LEVELS];   // per 4-pixel group tables of the fast resize path
@@ -781,6 +850,8 @@ struct kfs_orb {
     int *h_counts = nullptr; // pinned staging for n_out
     // host-buffer pipeline (kfs_orb_detect_and_compute_batch): H2D / kernels / D2H of frame chunks on three streams
     cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaStream_t s_blur = nullptr;  // side stream of the blur (fork after the pyramid, join before k_describe)
+    cudaEvent_t ev_pyr = nullptr, ev_blur = nullptr;
     std::vector<cudaEvent_t> ev_in, ev_cmp;
     cudaEvent_t ev_start = nullptr;
     int pipeline_chunk = 0;       // frames per chunk; 0 = auto
@@ -845,10 +916,11 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     // arena layout
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t r = off; off = kfs_align_up(off + bytes, 256); return r; };
-    size_t o_pyr[KFS_MAX_LEVELS], o_mpyr[KFS_MAX_LEVELS], o_xt[KFS_MAX_LEVELS], o_xt4[KFS_MAX_LEVELS], o_yt[KFS_MAX_LEVELS];
+    size_t o_pyr[KFS_MAX_LEVELS], o_bpyr[KFS_MAX_LEVELS], o_mpyr[KFS_MAX_LEVELS], o_xt[KFS_MAX_LEVELS], o_xt4[KFS_MAX_LEVELS], o_yt[KFS_MAX_LEVELS];
     int list_off[KFS_MAX_LEVELS], list_cap[KFS_MAX_LEVELS], list_fs = 0;
     for (int l = 0; l < L; l++) {
         o_pyr[l] = take((size_t)o->lfs[l] * batch + 256);
+        o_bpyr[l] = take((size_t)o->lfs[l] * batch + 256);
         o_mpyr[l] = need_mask ? take((size_t)o->lfs[l] * batch + 256) : 0;
         o_xt[l] = take(kfs_align_up((size_t)o->lw[l], 4) * 4);
         o_xt4[l] = take(kfs_align_up((size_t)o->lw[l], 4) * 8);
@@ -866,6 +938,10 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     for (int l = 0; l < L; l++)
         if (list_cap[l] > 0) n_tiles_total += kfs_div_up(o->lw[l] - KFS_BORDER - FAST_X0, FT_W) * kfs_div_up(o->lh[l] - 2 * KFS_BORDER, FT_H);
     const size_t o_tt = take((size_t)(n_tiles_total + 1) * 4);
+    int n_blur_tiles = 0;
+    for (int l = 0; l < L; l++)
+        if (list_cap[l] > 0) n_blur_tiles += kfs_div_up(o->lw[l], BT_W) * kfs_div_up(o->lh[l] - 2 * BT_Y0, BT_H);
+    const size_t o_bt = take((size_t)(n_blur_tiles + 1) * 4);
     const size_t outs = (size_t)batch * o->cap_out;
     const size_t o_kp = take(outs * sizeof(kfs_keypoint)), o_desc = take(outs * 32), o_rot = take(outs * sizeof(float2)), o_meta = take(outs * 4);
     KFS_CUDA_TRY(cudaMalloc(&o->arena, off));
@@ -882,10 +958,12 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     g.kept_count = g.cand_count + (size_t)batch * KFS_MAX_LEVELS; g.n_out = g.kept_count + (size_t)batch * KFS_MAX_LEVELS;
     g.kp = (kfs_keypoint *)(base + o_kp); g.desc = base + o_desc; g.rot = (float2 *)(base + o_rot); g.slot_meta = (uint32_t *)(base + o_meta);
     int tile_base = 0;
-    std::vector<uint32_t> tab, ttab;
+    std::vector<uint32_t> tab, ttab, btab;
     o->tile_tab = (uint32_t *)(base + o_tt);
+    o->blur_tab = (uint32_t *)(base + o_bt);
     for (int l = 0; l < L; l++) {
         o->pyr[l] = base + o_pyr[l];
+        o->bpyr[l] = base + o_bpyr[l];
         o->mpyr[l] = need_mask ? base + o_mpyr[l] : nullptr;
         o->xtab[l] = (uint32_t *)(base + o_xt[l]);
         o->xtab4[l] = (uint4 *)(base + o_xt4[l]);
@@ -894,12 +972,16 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
         LevelDev &D = g.lv[l];
         D.img = o->pyr[l]; D.img_fs = o->lfs[l]; D.pitch = o->lpitch[l];
         D.mask = nullptr; D.mask_fs = o->lfs[l]; D.mask_pitch = o->lpitch[l];
+        D.blur = o->bpyr[l]; D.img_fs_blur = o->lfs[l]; D.pitch_blur = o->lpitch[l];
         D.w = o->lw[l]; D.h = o->lh[l]; D.quota = o->quota[l]; D.scale = o->lscale[l];
         D.list_off = list_off[l]; D.list_cap = list_cap[l];
         if (list_cap[l] > 0) {
             D.tiles_x = kfs_div_up(D.w - KFS_BORDER - FAST_X0, FT_W);
             D.tiles_y = kfs_div_up(D.h - 2 * KFS_BORDER, FT_H);
         } else { D.tiles_x = 0; D.tiles_y = 0; }
+        if (list_cap[l] > 0) // levels too small to hold a keypoint are never sampled
+            for (int ty = 0; ty < kfs_div_up(D.h - 2 * BT_Y0, BT_H); ty++)
+                for (int tx = 0; tx < kfs_div_up(D.w, BT_W); tx++) btab.push_back(((uint32_t)l << 24) | ((uint32_t)ty << 12) | (uint32_t)tx);
         D.tile_base = tile_base;
         tile_base += D.tiles_x * D.tiles_y;
         for (int ty = 0; ty < D.tiles_y; ty++)
@@ -939,6 +1021,11 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     g.total_tiles = tile_base;
     if (!ttab.empty()) {
         KFS_CUDA_TRY(cudaMemcpyAsync(o->tile_tab, ttab.data(), ttab.size() * 4, cudaMemcpyHostToDevice, o->stream));
+        KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    }
+    o->blur_tiles = (int)btab.size();
+    if (!btab.empty()) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(o->blur_tab, btab.data(), btab.size() * 4, cudaMemcpyHostToDevice, o->stream));
         KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
     }
     if (o->h_counts) { cudaFreeHost(o->h_counts); o->h_counts = nullptr; }
@@ -1014,6 +1101,21 @@ static kfs_status kfs_orb_run(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_
             }
         }
     }
+    // the blur needs only the pyramid: outside profiling it runs on a side stream, concurrently with the
+    // FAST -> select -> Harris -> select chain (whose small latency-bound kernels leave most SMs idle)
+    const bool fork_blur = !o->profiling && o->blur_tiles > 0;
+    if (fork_blur) {
+        if (!o->s_blur) {
+            KFS_CUDA_TRY(cudaStreamCreateWithFlags(&o->s_blur, cudaStreamNonBlocking));
+            KFS_CUDA_TRY(cudaEventCreateWithFlags(&o->ev_pyr, cudaEventDisableTiming));
+            KFS_CUDA_TRY(cudaEventCreateWithFlags(&o->ev_blur, cudaEventDisableTiming));
+        }
+        KFS_CUDA_TRY(cudaEventRecord(o->ev_pyr, st));
+        KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_blur, o->ev_pyr, 0));
+        k_blur7<<<dim3(o->blur_tiles, nb), BT_THREADS, 0, o->s_blur>>>(g, o->blur_tab);
+        KFS_LAUNCH_CHECK(o);
+        KFS_CUDA_TRY(cudaEventRecord(o->ev_blur, o->s_blur));
+    }
     if (kfs_stage_mark(o, KFS_STAGE_FAST)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
         k_fast<<<dim3(g.total_tiles, nb), FAST_THREADS, 0, st>>>(g, o->tile_tab);
@@ -1040,7 +1142,13 @@ static kfs_status kfs_orb_run(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_
         k_select_sort<<<dim3(L, nb), SORT_THREADS, dyn, st>>>(g, smem_n);
         KFS_LAUNCH_CHECK(o);
     }
-    if (kfs_stage_mark(o, KFS_STAGE_ORIENT)) return KFS_ERR_CUDA;
+    if (kfs_stage_mark(o, KFS_STAGE_BLUR)) return KFS_ERR_CUDA;
+    if (fork_blur) {
+        KFS_CUDA_TRY(cudaStreamWaitEvent(st, o->ev_blur, 0));
+    } else if (o->blur_tiles > 0) {
+        k_blur7<<<dim3(o->blur_tiles, nb), BT_THREADS, 0, st>>>(g, o->blur_tab);
+        KFS_LAUNCH_CHECK(o);
+    }
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
     k_describe<<<dim3(kfs_div_up(g.cap_out, DK), nb), 32 * DK, 0, st>>>(g);
     KFS_LAUNCH_CHECK(o);
@@ -1113,6 +1221,9 @@ void kfs_orb_destroy(kfs_orb *o)
     for (cudaEvent_t e : o->ev_cmp) cudaEventDestroy(e);
     if (o->ev_start) cudaEventDestroy(o->ev_start);
     if (o->mask_stage) cudaFree(o->mask_stage);
+    if (o->ev_pyr) cudaEventDestroy(o->ev_pyr);
+    if (o->ev_blur) cudaEventDestroy(o->ev_blur);
+    if (o->s_blur) cudaStreamDestroy(o->s_blur);
     if (o->s_in) cudaStreamDestroy(o->s_in);
     if (o->s_out) cudaStreamDestroy(o->s_out);
     if (o->own_stream) cudaStreamDestroy(o->own_stream);
