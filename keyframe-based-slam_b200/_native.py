@@ -7,7 +7,8 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libkfslam_frontend.so")
+# KFS_LIB selects another build of the same library (kernel-variant experiments); the default is the in-tree product
+LIB_PATH = os.environ.get("KFS_LIB") or os.path.join(HERE, "libkfslam_frontend.so")
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
                      ("octave", "<i4"), ("class_id", "<i4")])

@@ -14,6 +14,12 @@
 #include <vector>
 #include <new>
 
+#ifndef KFS_DK
+#define KFS_DK 2
+#endif
+#ifndef KFS_KPW
+#define KFS_KPW 8
+#endif
 #define KFS_MAX_LEVELS 16
 #define KFS_BORDER 31
 
@@ -675,141 +681,232 @@ k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
 // ======================================================================================================
 // a1.7 / a1.8 / a1.10  orientation + keypoint record + rotated BRIEF: one WARP per keypoint
 // ======================================================================================================
-// grid (ceil(cap_out/DK), frame), DK warps per CTA, warp = output slot.
-//   1. slot -> (level, rank) through the per-level kept counts (warp prefix), read (x, y, response)
-//   2. intensity-centroid moments on the un-blurred level (lane = disc column u, |v| <= umax[|u|]);
+// grid (ceil(cap_out/(DK*KPW)), frame), DK warps per CTA; a warp walks KPW keypoints (slots), software-pipelined:
+//   0. the windows of keypoint i+1 (31 x 48 B un-blurred rows for the IC disc, 37 x 64 B of the blurred level for
+//      BRIEF) travel HBM -> shared memory with cp.async (LDGSTS, 16-byte aligned chunks, zero-fill past the pitch)
+//      while keypoint i is computed: no register staging, no exposed DRAM latency; lane = (row, 16-byte chunk) so
+//      one warp instruction touches 8 rows
+//   1. slot -> (level, rank) through the per-level kept counts (warp prefix), read (x, y, response) two rounds ahead
+//   2. intensity-centroid moments: lane = (disc row v, chunk): 2 x 4 IDP.4A per 16 bytes against a weight table indexed
+//      by (alignment shift, |v|, word): bytes = u (signed) for m10 and 0/1 for the row sum (m01 = v * row sum); the disc
+//      mask |u| <= umax[|v|] is baked into the table.  Two REDUX.SUM finish the warp sums.
 //      kfs_fast_atan2 (OpenCV's polynomial, no FMA)
-//   3. fp64 sincos of the DK keypoints of the CTA by DK lanes (dense) instead of once per warp; cv::KeyPoint record
-//   4. rotated BRIEF on the blurred level: lane = pair 32h + lane, 8 ballots give the 8 descriptor words; sample
-//      coordinates are rounded half-even with the magic add (kfs_rint), the float pattern table saves the I2Fs
-constexpr int DK = 8;
-constexpr int IW_P = 48, BW_P = 64; // window pitches: un-blurred (IC), blurred (BRIEF)
+//   3. fp64 sincos of the DK keypoints of the round by DK lanes; cv::KeyPoint record
+//   4. rotated BRIEF: lane = pair 32h + lane (its 8 pairs stay in registers for all KPW keypoints), 8 ballots give the
+//      8 descriptor words; sample coordinates are rounded half-even by a magic add whose constant already carries the
+//      window origin and the shared-memory address, so a sample costs 4 FMUL + 2 FADD + 2 FADD + IMAD + IADD + LDS.U8
+constexpr int DK = KFS_DK;    // warps (keypoints in flight) per CTA
+constexpr int KPW = KFS_KPW;  // keypoints per warp, one after the other (the lane's sample pairs stay in registers)
+constexpr int BW_P = 64;      // pitch of the blurred window
 __device__ __align__(16) const float d_patf[1024] = {
 #include "orb_pattern.inc"
 };
 
+// IC weight table [shift 0..15][|v| 0..15][word 0..11] for the 48 aligned bytes that cover one disc row:
+// wu = byte-wise u (signed) where |u| <= umax[|v|], else 0; w1 = byte-wise 1 under the same mask.
+struct IcTab { uint32_t wu[16 * 16 * 12], w1[16 * 16 * 12]; };
+constexpr IcTab kfs_make_ictab()
+{
+    IcTab t{};
+    const int umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+    for (int s = 0; s < 16; s++)
+        for (int a = 0; a < 16; a++)
+            for (int k = 0; k < 12; k++) {
+                uint32_t wu = 0, w1 = 0;
+                for (int j = 0; j < 4; j++) {
+                    const int p = 4 * k + j - s, u = p - 15;
+                    if (p < 0 || p > 30) continue;
+                    if ((u < 0 ? -u : u) > umax[a]) continue;
+                    wu |= (uint32_t)(u & 0xff) << (8 * j);
+                    w1 |= 1u << (8 * j);
+                }
+                t.wu[(s * 16 + a) * 12 + k] = wu;
+                t.w1[(s * 16 + a) * 12 + k] = w1;
+            }
+    return t;
+}
+__device__ __align__(16) const IcTab d_ictab = kfs_make_ictab();
+
+__device__ __forceinline__ int kfs_dp4a_us(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+__device__ __forceinline__ void kfs_cp_async16_zfill(void *smem, const void *gmem, bool pred)
+{
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+    const int n = pred ? 16 : 0; // src-size 0: nothing is read, the 16 bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(n) : "memory");
+}
+
+constexpr int IC_BYTES = 31 * 48, WB_BYTES = 37 * BW_P;
+
 __global__ void __launch_bounds__(32 * DK)
 k_describe(const __grid_constant__ OrbDev g)
 {
-    __shared__ __align__(16) uint8_t s_wi[DK][31 * IW_P];
-    __shared__ __align__(16) uint8_t s_wb[DK][37 * BW_P];
+    // per warp, double-buffered: the 31 x 48 B un-blurred rows of the IC disc and the 37 x 64 B blurred window
+    __shared__ __align__(16) uint8_t s_win[DK][2][IC_BYTES + WB_BYTES];
     __shared__ float s_angle[DK];
     __shared__ float2 s_rot[DK];
     const int f = blockIdx.y + g.frame0, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * DK + warp;
-    uint8_t *wi = s_wi[warp], *wb = s_wb[warp];
-    int shi = 0, shb = 0;
     // per-level kept counts -> prefix
     int cnt = 0;
     if (lane < g.nlevels) cnt = min(g.kept_count[f * KFS_MAX_LEVELS + lane], g.lv[lane].list_cap);
     int incl = cnt;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
+    for (int d = 1; d < KFS_MAX_LEVELS; d <<= 1) {
         const int v = __shfl_up_sync(0xffffffffu, incl, d);
         if (lane >= d) incl += v;
     }
-    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    const int total = __shfl_sync(0xffffffffu, incl, KFS_MAX_LEVELS - 1);
     if (blockIdx.x == 0 && threadIdx.x == 0) g.n_out[f] = total;
     const int nvalid = min(total, g.cap_out);
-    if (blockIdx.x * DK >= nvalid) return; // whole CTA beyond the last keypoint
-    const bool valid = slot < nvalid;
-    int x = 0, y = 0, level = 0;
-    float resp = 0.f, angle = 0.f;
-    if (valid) {
-        level = __popc(__ballot_sync(0xffffffffu, incl <= slot));
-        const int excl = __shfl_sync(0xffffffffu, incl - cnt, level);
-        const LevelDev &L = g.lv[level];
-        const long long li = (long long)f * g.list_fs + L.list_off + (slot - excl);
-        const uint32_t xy = g.kept_xy[li];
-        x = xy & 0xfff; y = (xy >> 12) & 0xfff;
-        resp = g.kept_resp[li];
-        // ---- windows -> shared memory with aligned 16-byte loads: un-blurred 31 rows x 48 B (IC disc), blurred
-        //      37 rows x 64 B (rotated BRIEF reach); the x origins are rounded down to 16, the remainders kept as shifts
-        {
-            const int ox = x - 15, ax = ox & ~15;
-            shi = ox & 15;
-            const uint8_t *src = L.img + (long long)f * L.img_fs + (long long)(y - 15) * L.pitch + ax;
-#pragma unroll 1
-            for (int i = lane; i < 31 * 3; i += 32) {
-                const int r = i / 3, q = i - 3 * r;
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (ax + 16 * q + 16 <= L.pitch) v = __ldg(reinterpret_cast<const uint4 *>(src + (long long)r * L.pitch + 16 * q));
-                *reinterpret_cast<uint4 *>(wi + r * IW_P + 16 * q) = v;
-            }
-            const int oxb = x - 18, axb = oxb & ~15;
-            shb = oxb & 15;
-            const uint8_t *srb = L.blur + (long long)f * L.img_fs_blur + (long long)(y - 18) * L.pitch_blur + axb;
-#pragma unroll 1
-            for (int i = lane; i < 37 * 4; i += 32) {
-                const int r = i >> 2, q = i & 3;
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (axb + 16 * q + 16 <= L.pitch_blur) v = __ldg(reinterpret_cast<const uint4 *>(srb + (long long)r * L.pitch_blur + 16 * q));
-                *reinterpret_cast<uint4 *>(wb + r * BW_P + 16 * q) = v;
-            }
-        }
-        __syncwarp();
-        // ---- IC moments: lane = column u
-        int m10 = 0, m01 = 0;
-        if (lane < 31) {
-            const int u = lane - 15, au = u < 0 ? -u : u;
-            const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * au)) & 15ull);
-            const uint8_t *c = wi + 15 * IW_P + shi + 15 + u;
-            int colsum = 0;
-#pragma unroll 4
-            for (int v = -d; v <= d; v++) {
-                const int I = c[v * IW_P];
-                colsum += I;
-                m01 += v * I;
-            }
-            m10 = u * colsum;
-        }
+    if (blockIdx.x * (DK * KPW) >= nvalid) return; // whole CTA beyond the last keypoint
+    // this lane's 8 sample pairs (pair 32h + lane), kept in registers for all KPW keypoints of the warp
+    float4 pat[8];
 #pragma unroll
-        for (int d = 16; d > 0; d >>= 1) {
-            m10 += __shfl_xor_sync(0xffffffffu, m10, d);
-            m01 += __shfl_xor_sync(0xffffffffu, m01, d);
+    for (int h = 0; h < 8; h++) pat[h] = __ldg(reinterpret_cast<const float4 *>(d_patf) + 32 * h + lane);
+    const int q = lane & 3, rq = lane >> 2;
+
+    // keypoint of round `it` of this warp: slot -> (level, rank) -> (x, y, response); xy = ~0 when there is none
+    auto load_meta = [&](int it, uint32_t &xy, float &resp, int &level) {
+        xy = 0xffffffffu; resp = 0.f; level = 0;
+        const int slot = (blockIdx.x * KPW + it) * DK + warp;
+        if (it < KPW && slot < nvalid) { // warp-uniform
+            level = __popc(__ballot_sync(0xffffffffu, incl <= slot) & ((1u << KFS_MAX_LEVELS) - 1u));
+            const int excl = __shfl_sync(0xffffffffu, incl - cnt, level);
+            const long long li = (long long)f * g.list_fs + g.lv[level].list_off + (slot - excl);
+            xy = g.kept_xy[li];
+            resp = g.kept_resp[li];
         }
-        angle = kfs_fast_atan2((float)m01, (float)m10);
-        if (lane == 0) s_angle[warp] = angle;
+    };
+    // asynchronous copies (LDGSTS) of both windows of one keypoint: lane = (row rq + 8 i, 16-byte chunk q), so a warp
+    // instruction touches 8 rows; the x origins are rounded down to 16 bytes, the remainders are kept as shifts
+    auto issue = [&](uint32_t xy, int level, int buf) {
+        if (xy != 0xffffffffu) {
+            const LevelDev &L = g.lv[level];
+            const int x = xy & 0xfff, y = (xy >> 12) & 0xfff;
+            uint8_t *ic = s_win[warp][buf], *wb = ic + IC_BYTES;
+            const int ax = (x - 15) & ~15;
+            const bool in_i = ax + 16 * q + 16 <= L.pitch;
+            const uint8_t *srci = L.img + (long long)f * L.img_fs + (long long)(y - 15 + rq) * L.pitch + ax + (in_i ? 16 * q : 0);
+            if (q < 3) {
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    if (rq + 8 * i < 31) kfs_cp_async16_zfill(ic + (rq + 8 * i) * 48 + 16 * q, srci + (long long)(8 * i) * L.pitch, in_i);
+            }
+            const int axb = (x - 18) & ~15;
+            const bool in_b = axb + 16 * q + 16 <= L.pitch_blur;
+            const uint8_t *srb = L.blur + (long long)f * L.img_fs_blur + (long long)(y - 18 + rq) * L.pitch_blur + axb + (in_b ? 16 * q : 0);
+#pragma unroll
+            for (int i = 0; i < 5; i++)
+                if (rq + 8 * i < 37) kfs_cp_async16_zfill(wb + (rq + 8 * i) * BW_P + 16 * q, srb + (long long)(8 * i) * L.pitch_blur, in_b);
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+
+    uint32_t xy_c, xy_n, xy_nn;
+    float resp_c, resp_n, resp_nn;
+    int level_c, level_n, level_nn;
+    load_meta(0, xy_c, resp_c, level_c);
+    issue(xy_c, level_c, 0);
+    load_meta(1, xy_n, resp_n, level_n);
+
+#pragma unroll 1
+    for (int it = 0; it < KPW; it++) {
+        const int slot0 = (blockIdx.x * KPW + it) * DK; // first slot of this round (block-uniform)
+        if (slot0 >= nvalid) break;
+        const int buf = it & 1;
+        issue(xy_n, level_n, buf ^ 1);           // next keypoint's windows fly while this one is computed
+        load_meta(it + 2, xy_nn, resp_nn, level_nn);
+        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        __syncwarp();
+        const bool valid = xy_c != 0xffffffffu;
+        const int slot = slot0 + warp;
+        const int x = xy_c & 0xfff, y = (xy_c >> 12) & 0xfff;
+        const uint8_t *ic = s_win[warp][buf], *wb = ic + IC_BYTES;
+        float angle = 0.f;
+        if (valid) {
+            // ---- IC moments (a1.7): 2 x 4 IDP.4A per 16-byte chunk against the (shift, |v|, word) weight table
+            const int shi = (x - 15) & 15;
+            int m10 = 0, m01 = 0;
+            const int qc = min(q, 2);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int r = rq + 8 * i, v = r - 15, a = min(v < 0 ? -v : v, 15);
+                uint4 px = make_uint4(0, 0, 0, 0);
+                if (q < 3 && r < 31) px = *reinterpret_cast<const uint4 *>(ic + r * 48 + 16 * q);
+                const int ti = (shi * 16 + a) * 12 + 4 * qc;
+                const uint4 tu = __ldg(reinterpret_cast<const uint4 *>(d_ictab.wu + ti));
+                const uint4 t1 = __ldg(reinterpret_cast<const uint4 *>(d_ictab.w1 + ti));
+                m10 = kfs_dp4a_us(px.x, tu.x, m10); m10 = kfs_dp4a_us(px.y, tu.y, m10);
+                m10 = kfs_dp4a_us(px.z, tu.z, m10); m10 = kfs_dp4a_us(px.w, tu.w, m10);
+                int rs = kfs_dp4a_us(px.x, t1.x, 0); rs = kfs_dp4a_us(px.y, t1.y, rs);
+                rs = kfs_dp4a_us(px.z, t1.z, rs); rs = kfs_dp4a_us(px.w, t1.w, rs);
+                m01 += v * rs; // lanes with q == 3 or row > 30 hold zero pixels
+            }
+            m10 = __reduce_add_sync(0xffffffffu, m10);
+            m01 = __reduce_add_sync(0xffffffffu, m01);
+            angle = kfs_fast_atan2((float)m01, (float)m10);
+            if (lane == 0) s_angle[warp] = angle;
+        }
+        __syncthreads();
+        if (threadIdx.x < DK && slot0 + (int)threadIdx.x < nvalid) {
+            const float rad = kfs_mul(s_angle[threadIdx.x], (float)(3.1415926535897932384626433832795 / 180.f));
+            double sn, cs;
+            sincos((double)rad, &sn, &cs);
+            s_rot[threadIdx.x] = make_float2((float)cs, (float)sn);
+        }
+        __syncthreads();
+        if (valid) {
+            const float2 ab = s_rot[warp];
+            const float sc = g.lv[level_c].scale;
+            const long long o = (long long)f * g.cap_out + slot;
+            if (lane == 0) {
+                kfs_keypoint kp;
+                kp.x = kfs_mul((float)x, sc);
+                kp.y = kfs_mul((float)y, sc);
+                kp.size = kfs_mul(31.f, sc);
+                kp.angle = angle;
+                kp.response = resp_c;
+                kp.octave = level_c;
+                kp.class_id = -1;
+                g.kp[o] = kp;
+            }
+            // OpenCV recomputes the integer centre from the scaled float point: cvRound(pt * (1.f/scale)).  (x*s)*(1/s)
+            // is within 1e-3 of x for x < 4096, so the rounded centre is (x, y) itself.
+            // Sample address = wb + (iy + 18) * 64 + (ix + 18 + shb).  rint(v) + c = bits(v + (1.5*2^23 + c)) - 0x4B400000
+            // for small even integer c, so the y magic carries +18, the x magic carries +18 + shb + the shared address of
+            // wb, and  by * 64 + bx = 65 * 0x4B400000 + address  (mod 2^32): one IMAD and one constant subtraction.
+            // (c must be even, or the tie rule of the magic add would flip to round-half-odd: the odd bit goes into kfold)
+            const int shb = (x - 18) & 15;
+            const int cx = 18 + shb + (int)__cvta_generic_to_shared(wb);
+            const float mx = 12582912.f + (float)(cx & ~1), my = 12582912.f + 18.f;
+            const uint32_t kfold = 0x4B400000u * 65u - (uint32_t)(cx & 1);
+            uint32_t word = 0;
+#pragma unroll
+            for (int h = 0; h < 8; h++) {
+                const float4 pt = pat[h];
+                const uint32_t bx0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.x, ab.x), __fmul_rn(pt.y, ab.y)), mx));
+                const uint32_t by0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.x, ab.y), __fmul_rn(pt.y, ab.x)), my));
+                const uint32_t bx1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.z, ab.x), __fmul_rn(pt.w, ab.y)), mx));
+                const uint32_t by1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.z, ab.y), __fmul_rn(pt.w, ab.x)), my));
+                uint32_t v0, v1;
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v0) : "r"(by0 * 64u + bx0 - kfold));
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v1) : "r"(by1 * 64u + bx1 - kfold));
+                const uint32_t b = __ballot_sync(0xffffffffu, v0 < v1);
+                if (lane == h) word = b;
+            }
+            if (lane < 8) reinterpret_cast<uint32_t *>(g.desc + o * 32)[lane] = word;
+        }
+        // buffer reuse: the windows of round it+2 are issued (by this warp, in program order) after the ballots above have
+        // consumed every read of this round's buffer; s_angle / s_rot reuse is ordered by the next round's two barriers
+        xy_c = xy_n; resp_c = resp_n; level_c = level_n;
+        xy_n = xy_nn; resp_n = resp_nn; level_n = level_nn;
     }
-    __syncthreads();
-    if (threadIdx.x < DK && blockIdx.x * DK + (int)threadIdx.x < nvalid) {
-        const float rad = kfs_mul(s_angle[threadIdx.x], (float)(3.1415926535897932384626433832795 / 180.f));
-        double sn, cs;
-        sincos((double)rad, &sn, &cs);
-        s_rot[threadIdx.x] = make_float2((float)cs, (float)sn);
-    }
-    __syncthreads();
-    if (!valid) return;
-    const float2 ab = s_rot[warp];
-    const LevelDev &L = g.lv[level];
-    const float sc = L.scale;
-    const long long o = (long long)f * g.cap_out + slot;
-    if (lane == 0) {
-        kfs_keypoint kp;
-        kp.x = kfs_mul((float)x, sc);
-        kp.y = kfs_mul((float)y, sc);
-        kp.size = kfs_mul(31.f, sc);
-        kp.angle = angle;
-        kp.response = resp;
-        kp.octave = level;
-        kp.class_id = -1;
-        g.kp[o] = kp;
-    }
-    // OpenCV recomputes the integer centre from the scaled float point: cvRound(pt * (1.f/scale)).  (x*s)*(1/s) is
-    // within 1e-3 of x for x < 4096, so the rounded centre is (x, y) itself.
-    const uint8_t *bl = wb + 18 * BW_P + shb + 18;
-    uint32_t word = 0;
-#pragma unroll 4
-    for (int h = 0; h < 8; h++) {
-        const float4 pt = __ldg(reinterpret_cast<const float4 *>(d_patf) + 32 * h + lane);
-        int ix0, iy0, ix1, iy1;
-        kfs_brief_rotf(pt.x, pt.y, ab.x, ab.y, &ix0, &iy0);
-        kfs_brief_rotf(pt.z, pt.w, ab.x, ab.y, &ix1, &iy1);
-        const int v0 = bl[iy0 * BW_P + ix0], v1 = bl[iy1 * BW_P + ix1];
-        const uint32_t b = __ballot_sync(0xffffffffu, v0 < v1);
-        if (lane == h) word = b;
-    }
-    if (lane < 8) reinterpret_cast<uint32_t *>(g.desc + o * 32)[lane] = word;
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory"); // nothing may still be landing in shared memory at exit
 }
 
 // ======================================================================================================
@@ -1150,7 +1247,7 @@ static kfs_status kfs_orb_run(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
-    k_describe<<<dim3(kfs_div_up(g.cap_out, DK), nb), 32 * DK, 0, st>>>(g);
+    k_describe<<<dim3(kfs_div_up(g.cap_out, DK * KPW), nb), 32 * DK, 0, st>>>(g);
     KFS_LAUNCH_CHECK(o);
     if (kfs_stage_mark(o, KFS_STAGE_COUNT)) return KFS_ERR_CUDA;
     o->last_batch = f0 + nb;
