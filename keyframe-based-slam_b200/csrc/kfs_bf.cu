@@ -14,6 +14,7 @@
 #include "kfs_common.cuh"
 #include <float.h>
 #include <string.h>
+#include <stdlib.h>
 #include <vector>
 #include <unordered_map>
 #include <new>
@@ -26,6 +27,8 @@ constexpr int BF_QTILE = BF_QWARPS * 32 * BF_QPT; // 128 queries per CTA
 constexpr int BF_CHUNK = 512;                   // train rows per smem stage (16 KB)
 constexpr int BF_SLICE = BF_CHUNK / BF_TSPLIT;  // rows one warp group scans per stage
 constexpr uint32_t BF_INF = 0xffffffffu;
+constexpr int BF_MAX_SPLIT = 8;                // train-row splits of one (pair, query tile) across CTAs
+static_assert(BF_QTILE <= BF_THREADS, "one thread per query in the merge epilogue");
 
 
 __device__ __forceinline__ void bf_cp_async16(void *smem, const void *gmem)
@@ -56,10 +59,14 @@ __device__ __forceinline__ void bf_top2_insert(uint32_t key, uint32_t &b1, uint3
     b2 = min(b2, hi);
 }
 
-// grid (ceil(max_nq / BF_QTILE), npairs)
-__global__ void __launch_bounds__(BF_THREADS)
-k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k)
+// grid (ceil(max_nq / BF_QTILE), npairs, S).  S > 1 splits the TRAIN rows of every (pair, query tile) over S CTAs so that
+// small batches still fill the 148 SMs and large ones end in many short waves instead of a few long ones; the
+// partial top-2 lists go through `scratch`, and the CTA that arrives last at the tile's counter merges them and
+// writes the cv::DMatch rows (the counter is left at zero for the next launch).
+__global__ void __launch_bounds__(BF_THREADS, 3)
+k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ scratch, int *__restrict__ counters)
 {
+    __shared__ int s_last;
     __shared__ __align__(16) uint4 s_train[2][BF_CHUNK * 2]; // 2 stages x 512 rows x 32 B
     const BfPairDev P = pairs[blockIdx.y];
     int nq = P.nq, nt = P.nt;
@@ -83,10 +90,14 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k)
         b1[r] = BF_INF; b2[r] = BF_INF;
     }
 
-    const int nchunks = (nt + BF_CHUNK - 1) / BF_CHUNK;
+    // this CTA's train rows [t0, t1)
+    const int S = gridDim.z, split = blockIdx.z;
+    const int seg = S > 1 ? ((nt + BF_CHUNK - 1) / BF_CHUNK + S - 1) / S * BF_CHUNK : nt; // whole stages per split
+    const int t0 = min(split * seg, nt), t1 = min(t0 + seg, nt);
+    const int nchunks = (t1 - t0 + BF_CHUNK - 1) / BF_CHUNK;
     auto issue = [&](int chunk, int stage) {
-        const int base = chunk * BF_CHUNK;
-        const int rows = min(BF_CHUNK, nt - base);
+        const int base = t0 + chunk * BF_CHUNK;
+        const int rows = min(BF_CHUNK, t1 - base);
         const uint4 *src = reinterpret_cast<const uint4 *>(P.train + (size_t)base * 32);
         for (int i = tid; i < rows * 2; i += BF_THREADS) bf_cp_async16(&s_train[stage][i], src + i);
         bf_cp_commit();
@@ -97,8 +108,8 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k)
         if (c + 1 < nchunks) { issue(c + 1, stage ^ 1); bf_cp_wait<1>(); }
         else bf_cp_wait<0>();
         __syncthreads();
-        const int base = c * BF_CHUNK + tsplit * BF_SLICE;
-        const int rows = min(BF_SLICE, nt - base); // may be <= 0 for the last chunk
+        const int base = t0 + c * BF_CHUNK + tsplit * BF_SLICE;
+        const int rows = min(BF_SLICE, t1 - base); // may be <= 0 for the last chunk
         const uint4 *tp = &s_train[stage][tsplit * BF_SLICE * 2];
 #pragma unroll 2
         for (int j = 0; j < rows; j++) {
@@ -133,15 +144,36 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k)
         s_m[(tsplit * BF_QTILE + ql) * 2 + 1] = b2[r];
     }
     __syncthreads();
-    for (int ql = tid; ql < BF_QTILE; ql += BF_THREADS) {
-        const int qi = q0 + ql;
-        if (qi >= nq) continue;
-        uint32_t m1 = BF_INF, m2 = BF_INF;
+    uint32_t m1 = BF_INF, m2 = BF_INF; // thread ql < BF_QTILE: merged top-2 of query q0 + ql over this CTA's rows
+    if (tid < BF_QTILE) {
 #pragma unroll
         for (int s = 0; s < BF_TSPLIT; s++) {
-            bf_top2_insert(s_m[(s * BF_QTILE + ql) * 2 + 0], m1, m2);
-            bf_top2_insert(s_m[(s * BF_QTILE + ql) * 2 + 1], m1, m2);
+            bf_top2_insert(s_m[(s * BF_QTILE + tid) * 2 + 0], m1, m2);
+            bf_top2_insert(s_m[(s * BF_QTILE + tid) * 2 + 1], m1, m2);
         }
+    }
+    if (S > 1) {
+        const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+        uint2 *part = scratch + (size_t)tile * S * BF_QTILE;
+        if (tid < BF_QTILE) __stcg(part + split * BF_QTILE + tid, make_uint2(m1, m2));
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) s_last = atomicAdd(counters + tile, 1) == S - 1;
+        __syncthreads();
+        if (!s_last) return;
+        if (tid == 0) counters[tile] = 0;
+        __threadfence();
+        if (tid < BF_QTILE) {
+            m1 = m2 = BF_INF;
+            for (int s = 0; s < S; s++) {
+                const uint2 v = __ldcg(part + s * BF_QTILE + tid);
+                bf_top2_insert(v.x, m1, m2);
+                bf_top2_insert(v.y, m1, m2);
+            }
+        }
+    }
+    const int qi = q0 + tid;
+    if (tid < BF_QTILE && qi < nq) {
         kfs_dmatch r0, r1;
         r0.queryIdx = qi; r1.queryIdx = qi;
         int cnt = 0;
@@ -217,7 +249,67 @@ struct kfs_bf {
     uint8_t *d_buf = nullptr;     // staging for the host-buffer entry points
     size_t d_buf_bytes = 0;
     int launches = 0;
+    int sm_count = 0;
+    uint2 *d_scratch = nullptr;   // [tiles][S][BF_QTILE] partial top-2 lists of split launches
+    int *d_counters = nullptr;    // [tiles] arrival counters (zero between launches)
+    size_t scratch_tiles = 0, scratch_elems = 0;
+    int force_split = 0;          // KFS_BF_SPLIT (tests / experiments): 0 = automatic
 };
+
+// Number of train splits.  A batch with >= 4 query tiles per SM is throughput-bound as it is (S = 1).  Smaller launches
+// (one 2000 x 2000 pair is 16 tiles on 148 SMs) split the train rows over up to BF_MAX_SPLIT CTAs per tile, in whole
+// BF_CHUNK stages so that the 8 warp groups of every CTA stay evenly loaded.
+static int bf_choose_split(const kfs_bf *b, int tiles, int max_nt)
+{
+    const int nchunks = kfs_div_up(max_nt > 0 ? max_nt : 1, BF_CHUNK);
+    int s;
+    if (b->force_split > 0) s = b->force_split;
+    else {
+        const int want = 4 * (b->sm_count > 0 ? b->sm_count : 148);
+        s = tiles >= want ? 1 : kfs_div_up(want, tiles);
+    }
+    if (s > BF_MAX_SPLIT) s = BF_MAX_SPLIT;
+    if (s > nchunks) s = nchunks;
+    if (s < 1) s = 1;
+    return kfs_div_up(nchunks, kfs_div_up(nchunks, s)); // drop splits that would get no chunk
+}
+
+static kfs_status bf_reserve_split(kfs_bf *b, size_t tiles, int S)
+{
+    if (S <= 1) return KFS_OK;
+    const size_t elems = tiles * (size_t)S * BF_QTILE;
+    if (tiles > b->scratch_tiles) {
+        KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
+        if (b->d_counters) cudaFree(b->d_counters);
+        b->d_counters = nullptr; b->scratch_tiles = 0;
+        const size_t cap = tiles + tiles / 2 + 64;
+        KFS_CUDA_TRY(cudaMalloc(&b->d_counters, cap * sizeof(int)));
+        KFS_CUDA_TRY(cudaMemset(b->d_counters, 0, cap * sizeof(int)));
+        b->scratch_tiles = cap;
+    }
+    if (elems > b->scratch_elems) {
+        KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
+        if (b->d_scratch) cudaFree(b->d_scratch);
+        b->d_scratch = nullptr; b->scratch_elems = 0;
+        const size_t cap = elems + elems / 2;
+        KFS_CUDA_TRY(cudaMalloc(&b->d_scratch, cap * sizeof(uint2)));
+        b->scratch_elems = cap;
+    }
+    return KFS_OK;
+}
+
+static kfs_status bf_launch_kernel(kfs_bf *b, const BfPairDev *d_table, int npairs, int max_nq, int max_nt, int k, cudaStream_t st)
+{
+    const int qtiles = kfs_div_up(max_nq, BF_QTILE);
+    const int S = bf_choose_split(b, qtiles * npairs, max_nt);
+    kfs_status s = bf_reserve_split(b, (size_t)qtiles * npairs, S);
+    if (s) return s;
+    k_hamming_knn2<<<dim3(qtiles, npairs, S), BF_THREADS, 0, st>>>(d_table, k, b->d_scratch, b->d_counters);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_hamming_knn2 launch: %s", cudaGetErrorString(e));
+    b->launches++;
+    return KFS_OK;
+}
 
 static kfs_status bf_reserve_pairs(kfs_bf *b, int n)
 {
@@ -262,8 +354,11 @@ static kfs_status bf_check_pairs(const kfs_bf_pair *pairs, int npairs, int k, bo
 
 static kfs_status bf_launch(kfs_bf *b, const BfPairDev *h, int npairs, int k)
 {
-    int max_nq = 0;
-    for (int i = 0; i < npairs; i++) max_nq = h[i].nq > max_nq ? h[i].nq : max_nq;
+    int max_nq = 0, max_nt = 0;
+    for (int i = 0; i < npairs; i++) {
+        max_nq = h[i].nq > max_nq ? h[i].nq : max_nq;
+        max_nt = h[i].nt > max_nt ? h[i].nt : max_nt;
+    }
     if (npairs == 0 || max_nq == 0) return KFS_OK;
     kfs_status s = bf_reserve_pairs(b, npairs);
     if (s) return s;
@@ -274,11 +369,7 @@ static kfs_status bf_launch(kfs_bf *b, const BfPairDev *h, int npairs, int k)
         KFS_CUDA_TRY(cudaMemcpyAsync(b->d_pairs, b->h_stage, sizeof(BfPairDev) * (size_t)npairs, cudaMemcpyHostToDevice, b->stream));
         b->h_pairs_last.assign(h, h + npairs);
     }
-    k_hamming_knn2<<<dim3(kfs_div_up(max_nq, BF_QTILE), npairs), BF_THREADS, 0, b->stream>>>(b->d_pairs, k);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_hamming_knn2 launch: %s", cudaGetErrorString(e));
-    b->launches++;
-    return KFS_OK;
+    return bf_launch_kernel(b, b->d_pairs, npairs, max_nq, max_nt, k, b->stream);
 }
 
 // ---- library-internal hooks for kfs_replay.cu (not exported) ------------------------------------------
@@ -286,11 +377,7 @@ static kfs_status bf_launch(kfs_bf *b, const BfPairDev *h, int npairs, int k)
 kfs_status kfs_bf_launch_table(kfs_bf *b, const BfPairDev *d_table, int npairs, int max_nq, int k, cudaStream_t st)
 {
     if (npairs == 0 || max_nq == 0) return KFS_OK;
-    k_hamming_knn2<<<dim3(kfs_div_up(max_nq, BF_QTILE), npairs), BF_THREADS, 0, st>>>(d_table, k);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_hamming_knn2 launch: %s", cudaGetErrorString(e));
-    b->launches++;
-    return KFS_OK;
+    return bf_launch_kernel(b, d_table, npairs, max_nq, max_nq, k, st); // replay: query and train share the capacity
 }
 // Ratio test of every pair of the table: good_base[pair * good_stride ..], n_good[pair].
 kfs_status kfs_bf_launch_ratio_table(kfs_bf *b, const BfPairDev *d_table, int npairs, float ratio, kfs_dmatch *good_base, long long good_stride,
@@ -321,6 +408,8 @@ kfs_status kfs_bf_create(int norm_type, int cross_check, int device, kfs_bf **ou
     KfsDeviceGuard guard(device);
     cudaError_t e = cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { delete b; KFS_FAIL(KFS_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+    cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (const char *fs = getenv("KFS_BF_SPLIT")) b->force_split = atoi(fs);
     b->stream = b->own_stream;
     *out = b;
     return KFS_OK;
@@ -334,6 +423,8 @@ void kfs_bf_destroy(kfs_bf *b)
     if (b->d_pairs) cudaFree(b->d_pairs);
     if (b->h_stage) cudaFreeHost(b->h_stage);
     if (b->d_buf) cudaFree(b->d_buf);
+    if (b->d_scratch) cudaFree(b->d_scratch);
+    if (b->d_counters) cudaFree(b->d_counters);
     if (b->own_stream) cudaStreamDestroy(b->own_stream);
     delete b;
 }
