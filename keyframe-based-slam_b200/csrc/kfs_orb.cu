@@ -587,19 +587,54 @@ k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
 // ======================================================================================================
 // a1.9  7x7 sigma=2 blur of every level (OpenCV's sepFilter2D float path, exact FMA order: kfs_blur_row / _col)
 // ======================================================================================================
-// One CTA = one 128 x 32 tile of one level of one frame (tile table like k_fast's), 128 threads.
-//   source tile 160 x 38 bytes (origin (x0-16, y0-3): rows are 16-byte aligned -> LDG.128)
-//   row pass   : item = (row, 16-pixel segment): 22 source bytes -> I2F.U8 with byte select -> 16 x 7 FFMA (immediate
-//                form) -> 4 x STS.128 into the 38 x 128 float tile
-//   column pass: thread = (4 adjacent columns, 8-row segment): LDS.128 down the column block, sliding 7-row window
-//                in registers, round-half-even by the 1.5*2^23 magic add (no F2I), 4 pixels packed -> one STG.32;
-//                a warp writes 128 contiguous bytes per row
+// One CTA = one 128 x 58 tile of one level of one frame (tile table like k_fast's), 256 threads.
+//   source tile 160 x 64 bytes (origin (x0-16, y0-3): rows are 16-byte aligned -> LDG.128)
+//   row pass   : thread = (row PAIR, 16-pixel segment): 2 x 22 source bytes -> I2F.U8 with byte select; the two rows ride
+//                in the two halves of packed fp32x2 registers, so the 16 x 7 taps are 112 FFMA2 (fma.rn.f32x2: two exact
+//                IEEE FMAs per issue slot — the kernel is issue-bound, the FMA pipe itself is not) -> 2 x 4 STS.128
+//                into the 64 x 128 float tile
+//   column pass: thread = (4 adjacent columns, 7..8-row segment): LDS.128 down the column block = two packed column
+//                pairs, sliding 7-row window in registers, the symmetric taps as ADD2 + FMA2, round-half-even by the
+//                1.5*2^23 magic add (no F2I), 4 pixels packed -> one STG.32; a warp writes 128 contiguous bytes per row
+// Every lane of a packed operation evaluates exactly kfs_blur_row / kfs_blur_col_bits (kfs_math.cuh, checked on the CPU
+// against the oracle): same operands, same order, same rounding.
 // Borders: source rows/columns outside the image are clamped / zero-filled instead of REFLECT_101: a descriptor
 // sample lies >= 31-19 = 12 px inside the level and its 7x7 support >= 9 px inside, so those pixels of the blurred
 // level are never read (rotated BRIEF reaches <= 18.4 px from a keypoint that is >= 31 px inside).
-constexpr int BT_W = 128, BT_H = 26, BT_THREADS = 128; // 26 + 6 halo rows = 32 -> the row pass is exactly 2 rounds of 128 items
+constexpr int BT_W = 128, BT_H = 58, BT_THREADS = 256; // 58 + 6 halo rows = 64 = 32 row pairs x 8 segments = 256 row-pass items
 constexpr int BT_Y0 = 12;                               // first blurred row / rows [12, H-12) are the only ones ever sampled
 constexpr int BS_P = 160, BS_H = BT_H + 6;
+static_assert(BS_H == 64 && BT_THREADS == 256, "one row-pass item per thread");
+
+typedef unsigned long long kfs_f2; // two fp32 lanes in one 64-bit register pair
+__device__ __forceinline__ kfs_f2 kfs_pk2(float lo, float hi) { kfs_f2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void kfs_unpk2(kfs_f2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ kfs_f2 kfs_mul2(kfs_f2 a, kfs_f2 b) { kfs_f2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ kfs_f2 kfs_add2(kfs_f2 a, kfs_f2 b) { kfs_f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ kfs_f2 kfs_fma2(kfs_f2 a, kfs_f2 b, kfs_f2 c) { kfs_f2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+// kfs_blur_row on both lanes
+__device__ __forceinline__ kfs_f2 kfs_blur_row2(kfs_f2 g0, kfs_f2 g1, kfs_f2 g2, kfs_f2 g3, kfs_f2 p0, kfs_f2 p1, kfs_f2 p2, kfs_f2 p3,
+                                                kfs_f2 p4, kfs_f2 p5, kfs_f2 p6)
+{
+    kfs_f2 r = kfs_mul2(g0, p0);
+    r = kfs_fma2(g1, p1, r);
+    r = kfs_fma2(g2, p2, r);
+    r = kfs_fma2(g3, p3, r);
+    r = kfs_fma2(g2, p4, r);
+    r = kfs_fma2(g1, p5, r);
+    r = kfs_fma2(g0, p6, r);
+    return r;
+}
+// kfs_blur_col_bits on both lanes: the bits of (s + 1.5*2^23), byte 0 of each half is the rounded pixel
+__device__ __forceinline__ kfs_f2 kfs_blur_col2(kfs_f2 g0, kfs_f2 g1, kfs_f2 g2, kfs_f2 g3, kfs_f2 magic, kfs_f2 rm3, kfs_f2 rm2, kfs_f2 rm1,
+                                                kfs_f2 r0, kfs_f2 rp1, kfs_f2 rp2, kfs_f2 rp3)
+{
+    kfs_f2 s = kfs_mul2(g3, r0);
+    s = kfs_fma2(g2, kfs_add2(rp1, rm1), s);
+    s = kfs_fma2(g1, kfs_add2(rp2, rm2), s);
+    s = kfs_fma2(g0, kfs_add2(rp3, rm3), s);
+    return kfs_add2(s, magic);
+}
 
 __global__ void __launch_bounds__(BT_THREADS)
 k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
@@ -621,58 +656,59 @@ k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
         if (gx >= 0 && gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
         *reinterpret_cast<uint4 *>(s_src + r * BS_P + 16 * c) = v;
     }
+    const kfs_f2 G0 = kfs_pk2(KFS_G0, KFS_G0), G1 = kfs_pk2(KFS_G1, KFS_G1), G2 = kfs_pk2(KFS_G2, KFS_G2), G3 = kfs_pk2(KFS_G3, KFS_G3);
     __syncthreads();
-    // ---- row pass
-#pragma unroll 1
-    for (int item = tid; item < BS_H * 8; item += BT_THREADS) {
-        const int r = item >> 3, sg = item & 7;
-        const uint8_t *base = s_src + r * BS_P + 16 + 16 * sg;
-        const uint32_t wl = *reinterpret_cast<const uint32_t *>(base - 4);
-        const uint4 wm = *reinterpret_cast<const uint4 *>(base);
-        const uint32_t wr = *reinterpret_cast<const uint32_t *>(base + 16);
-        float p[22];
-        p[0] = (float)((wl >> 8) & 0xffu); p[1] = (float)((wl >> 16) & 0xffu); p[2] = (float)(wl >> 24);
-        const uint32_t w4[4] = {wm.x, wm.y, wm.z, wm.w};
+    // ---- row pass: rows 2m (low lanes) and 2m+1 (high lanes), pixels [16 sg, 16 sg + 16)
+    {
+        const int m = tid >> 3, sg = tid & 7;
+        const uint8_t *ba = s_src + (2 * m) * BS_P + 16 + 16 * sg, *bb = ba + BS_P;
+        const uint32_t al = *reinterpret_cast<const uint32_t *>(ba - 4), ar = *reinterpret_cast<const uint32_t *>(ba + 16);
+        const uint32_t bl = *reinterpret_cast<const uint32_t *>(bb - 4), br = *reinterpret_cast<const uint32_t *>(bb + 16);
+        const uint4 am = *reinterpret_cast<const uint4 *>(ba), bm = *reinterpret_cast<const uint4 *>(bb);
+        const uint32_t aw[6] = {al, am.x, am.y, am.z, am.w, ar}, bw[6] = {bl, bm.x, bm.y, bm.z, bm.w, br};
+        kfs_f2 p[22]; // p[i] = pixel x - 3 + i of both rows = byte i + 1 of the 24-byte window
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            p[3 + 4 * k] = (float)(w4[k] & 0xffu); p[4 + 4 * k] = (float)((w4[k] >> 8) & 0xffu);
-            p[5 + 4 * k] = (float)((w4[k] >> 16) & 0xffu); p[6 + 4 * k] = (float)(w4[k] >> 24);
+        for (int i = 0; i < 22; i++) {
+            const int wi = (i + 1) >> 2, sh = 8 * ((i + 1) & 3);
+            p[i] = kfs_pk2((float)((aw[wi] >> sh) & 0xffu), (float)((bw[wi] >> sh) & 0xffu));
         }
-        p[19] = (float)(wr & 0xffu); p[20] = (float)((wr >> 8) & 0xffu); p[21] = (float)((wr >> 16) & 0xffu);
-        // float4 slot c4 of a row lives at physical slot c4 ^ ((c4 >> 3) & 3): the 8 lanes of a quarter warp (sg = 0..7,
-        // same k) then hit 8 distinct 16-byte bank groups instead of 2; the column pass reads a permutation of a full row
-        float4 *out = reinterpret_cast<float4 *>(s_row + r * BT_W);
+        // float4 slot c4 of a row lives at physical slot c4 ^ (c4 >> 3): the 8 lanes of a quarter warp (sg = 0..7, same k)
+        // then hit 8 distinct 16-byte bank groups instead of 2; the column pass reads a permutation of a full row
+        float4 *oa = reinterpret_cast<float4 *>(s_row + (2 * m) * BT_W), *ob = oa + BT_W / 4;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            float4 o;
-            o.x = kfs_blur_row(p[4 * k + 0], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6]);
-            o.y = kfs_blur_row(p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7]);
-            o.z = kfs_blur_row(p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8]);
-            o.w = kfs_blur_row(p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8], p[4 * k + 9]);
-            out[(4 * sg + k) ^ (sg >> 1)] = o;
+            float4 va, vb;
+            kfs_unpk2(kfs_blur_row2(G0, G1, G2, G3, p[4 * k + 0], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6]), va.x, vb.x);
+            kfs_unpk2(kfs_blur_row2(G0, G1, G2, G3, p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7]), va.y, vb.y);
+            kfs_unpk2(kfs_blur_row2(G0, G1, G2, G3, p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8]), va.z, vb.z);
+            kfs_unpk2(kfs_blur_row2(G0, G1, G2, G3, p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8], p[4 * k + 9]), va.w, vb.w);
+            const int slot = (4 * sg + k) ^ (sg >> 1);
+            oa[slot] = va;
+            ob[slot] = vb;
         }
     }
     __syncthreads();
-    // ---- column pass
+    // ---- column pass: warp w owns output rows [r0, r0 + n): 8, 8, 7, 7, 7, 7, 7, 7; lane = 4 adjacent columns
     {
-        const int cg = tid & 31, rs = tid >> 5;           // warp rs owns output rows [r0, r0 + n): 7, 7, 6, 6
-        const int r0 = rs < 2 ? 7 * rs : 14 + 6 * (rs - 2), n = rs < 2 ? 7 : 6;
-        const float4 *col = reinterpret_cast<const float4 *>(s_row + r0 * BT_W) + (cg ^ ((cg >> 3) & 3));
-        float4 q0 = col[0], q1 = col[BT_W / 4], q2 = col[2 * (BT_W / 4)], q3 = col[3 * (BT_W / 4)], q4 = col[4 * (BT_W / 4)],
-               q5 = col[5 * (BT_W / 4)];
+        const int cg = tid & 31, w = tid >> 5;
+        const int r0 = w < 2 ? 8 * w : 16 + 7 * (w - 2), n = w < 2 ? 8 : 7;
+        const ulonglong2 *col = reinterpret_cast<const ulonglong2 *>(s_row + r0 * BT_W) + (cg ^ ((cg >> 3) & 3));
+        const kfs_f2 magic = kfs_pk2(12582912.f, 12582912.f);
+        ulonglong2 q0 = col[0], q1 = col[BT_W / 4], q2 = col[2 * (BT_W / 4)], q3 = col[3 * (BT_W / 4)], q4 = col[4 * (BT_W / 4)],
+                   q5 = col[5 * (BT_W / 4)];
         uint8_t *dst = L.blur + (long long)f * L.img_fs_blur + (long long)(y0 + r0) * L.pitch_blur + x0 + 4 * cg;
-        const int ylim = H - BT_Y0;
+        const int nrows = min(n, H - BT_Y0 - (y0 + r0)); // rows at or below H - 12 are never sampled
+        const long long dp = L.pitch_blur;
 #pragma unroll
-        for (int k = 0; k < 7; k++) {
-            if (k >= n) break;
-            const float4 q6 = col[(k + 6) * (BT_W / 4)];
-            const uint32_t a = kfs_blur_col_bits(q0.x, q1.x, q2.x, q3.x, q4.x, q5.x, q6.x);
-            const uint32_t b = kfs_blur_col_bits(q0.y, q1.y, q2.y, q3.y, q4.y, q5.y, q6.y);
-            const uint32_t c = kfs_blur_col_bits(q0.z, q1.z, q2.z, q3.z, q4.z, q5.z, q6.z);
-            const uint32_t d = kfs_blur_col_bits(q0.w, q1.w, q2.w, q3.w, q4.w, q5.w, q6.w);
+        for (int k = 0; k < 8; k++) {
+            if (k >= nrows) break;
+            const ulonglong2 q6 = col[(k + 6) * (BT_W / 4)];
+            const kfs_f2 ab = kfs_blur_col2(G0, G1, G2, G3, magic, q0.x, q1.x, q2.x, q3.x, q4.x, q5.x, q6.x);
+            const kfs_f2 cd = kfs_blur_col2(G0, G1, G2, G3, magic, q0.y, q1.y, q2.y, q3.y, q4.y, q5.y, q6.y);
             // byte 0 of each magic-rounded float is the pixel
-            const uint32_t w = __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
-            if (y0 + r0 + k < ylim) *reinterpret_cast<uint32_t *>(dst + (long long)k * L.pitch_blur) = w;
+            const uint32_t a = (uint32_t)ab, b = (uint32_t)(ab >> 32), c = (uint32_t)cd, d = (uint32_t)(cd >> 32);
+            *reinterpret_cast<uint32_t *>(dst) = __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
+            dst += dp;
             q0 = q1; q1 = q2; q2 = q3; q3 = q4; q4 = q5; q5 = q6;
         }
     }
@@ -928,6 +964,7 @@ struct kfs_orb {
     uint8_t *bpyr[KFS_MAX_LEVELS];  // blurred levels (a1.9)
     uint32_t *blur_tab = nullptr;   // blur tile -> level<<24 | tiy<<12 | tix
     int blur_tiles = 0;
+    int sm_count = 0;
     uint8_t *mpyr[KFS_MAX_LEVELS];  // mask pyramid
     uint32_t *xtab[KFS_MAX_LEVELS], *ytab[KFS_MAX_LEVELS];
     uint4 *xtab4[KFS_MAX_LEVELS];   // per 4-pixel group tables of the fast resize path
