@@ -571,7 +571,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--batch", type=int, default=64, help="frames per GPU per step")
+    ap.add_argument("--batch", type=int, default=128, help="frames per GPU per step")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--replay-chunk", type=int, default=0, help="frames per chunk inside one replay batch (0 = whole batch)")
     ap.add_argument("--e2e-chunk", type=int, default=0, help="frames per chunk of the host-buffer pipeline (0 = library default)")

@@ -13,6 +13,8 @@
 namespace cv {
 
 struct Point2f { float x = 0, y = 0; };
+struct Point2d { double x = 0, y = 0; Point2d() = default; Point2d(double x_, double y_) : x(x_), y(y_) {} Point2d(const Point2f &p) : x(p.x), y(p.y) {} };
+struct Point3d { double x = 0, y = 0, z = 0; Point3d() = default; Point3d(double x_, double y_, double z_) : x(x_), y(y_), z(z_) {} };
 
 struct KeyPoint {
     Point2f pt;
@@ -28,7 +30,7 @@ struct DMatch {
 static_assert(sizeof(KeyPoint) == 28, "cv::KeyPoint layout");
 static_assert(sizeof(DMatch) == 16, "cv::DMatch layout");
 
-enum { CV_8U = 0, CV_8UC1 = 0 };
+enum { CV_8U = 0, CV_8UC1 = 0, CV_16U = 2, CV_16UC1 = 2, CV_8UC3 = 16 };
 enum NormTypes { NORM_L2 = 4, NORM_HAMMING = 6 };
 
 class Exception : public std::runtime_error {
@@ -37,30 +39,34 @@ public:
     Exception(int c, const std::string &m) : std::runtime_error(m), code(c) {}
 };
 
-// Minimal row-major 8-bit matrix: owns its buffer or wraps external memory (like cv::Mat(rows, cols, type, data, step)).
+// Minimal row-major matrix for the element types the path uses (CV_8UC1 gray / mask / descriptors, CV_8UC3 colour,
+// CV_16UC1 depth): owns its buffer or wraps external memory (like cv::Mat(rows, cols, type, data, step)).  step in bytes.
 class Mat {
 public:
     int rows = 0, cols = 0;
     size_t step = 0;
     uint8_t *data = nullptr;
     Mat() = default;
-    Mat(int r, int c, int /*type*/) { create(r, c, CV_8U); }
-    Mat(int r, int c, int /*type*/, void *ext, size_t st = 0) : rows(r), cols(c), step(st ? st : (size_t)c), data((uint8_t *)ext) {}
-    void create(int r, int c, int /*type*/)
+    Mat(int r, int c, int type) { create(r, c, type); }
+    Mat(int r, int c, int type, void *ext, size_t st = 0) : rows(r), cols(c), step(st ? st : (size_t)c * esz(type)), data((uint8_t *)ext), type_(type) {}
+    void create(int r, int c, int type)
     {
-        if (r == rows && c == cols && own_) return;
-        own_ = std::shared_ptr<uint8_t>(new uint8_t[(size_t)r * c + 1], std::default_delete<uint8_t[]>());
-        rows = r; cols = c; step = (size_t)c; data = own_.get();
+        if (r == rows && c == cols && type == type_ && own_) return;
+        own_ = std::shared_ptr<uint8_t>(new uint8_t[(size_t)r * c * esz(type) + 1], std::default_delete<uint8_t[]>());
+        rows = r; cols = c; type_ = type; step = (size_t)c * esz(type); data = own_.get();
     }
     void release() { own_.reset(); rows = cols = 0; step = 0; data = nullptr; }
     bool empty() const { return rows == 0 || cols == 0 || data == nullptr; }
-    bool isContinuous() const { return step == (size_t)cols; }
-    int type() const { return CV_8U; }
-    int channels() const { return 1; }
+    bool isContinuous() const { return step == (size_t)cols * elemSize(); }
+    int type() const { return type_; }
+    int channels() const { return type_ == CV_8UC3 ? 3 : 1; }
+    size_t elemSize() const { return esz(type_); }
     uint8_t *ptr(int r = 0) { return data + (size_t)r * step; }
     const uint8_t *ptr(int r = 0) const { return data + (size_t)r * step; }
 private:
+    static size_t esz(int type) { return type == CV_8UC3 ? 3 : (type == CV_16UC1 ? 2 : 1); }
     std::shared_ptr<uint8_t> own_;
+    int type_ = CV_8UC1;
 };
 
 using InputArray = const Mat &;

@@ -231,6 +231,46 @@ KFS_API kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, con
 KFS_API kfs_status kfs_replay_wait(kfs_replay *r, int ticket);
 KFS_API int kfs_replay_last_launches(const kfs_replay *r);      /* kernels launched by the last submit */
 
+/* ---- tracker front-end: VisualOdometry::ExtractFeatures + MatchFeatures as the reference calls them --------
+ * (the callers either side of the two drop-in calls.)
+ *   ExtractFeatures  /root/reference/src/lib/VisualOdometry.cpp:21-33   cvtColor(RGB2BGR), cvtColor(BGR2GRAY) when the
+ *                    image has 3 channels, then detectAndCompute(gray, mask)
+ *   MatchFeatures    /root/reference/src/lib/VisualOdometry.cpp:35-62   knnMatch(keyframe, current, 2), ratio test
+ *                    d0 < 0.6f*d1 (:46), depth look-up and pin-hole back-projection of the KEYFRAME keypoint (:52-54),
+ *                    2-D point of the current keypoint (:57)
+ *   KeyFrame         /root/reference/include/lib/KeyFrame.hpp:35-39     descriptors, keypoints and the uint16 depth
+ *                    image of the last keyframe: cached on the device, uploaded once per keyframe
+ * One handle owns an ORB extractor, a matcher, the colour/gray staging and the keyframe cache; one stream. */
+typedef struct kfs_frontend kfs_frontend;
+KFS_API kfs_status kfs_frontend_create(const kfs_orb_params *params, int device, kfs_frontend **out);
+KFS_API void kfs_frontend_destroy(kfs_frontend *fe);
+KFS_API int kfs_frontend_capacity(const kfs_frontend *fe);   /* rows kp_out / desc_out / the match outputs should have */
+
+/* ExtractFeatures(rgb, mask): image = h rows of w pixels x `channels` bytes (1 = already gray, 3 = R,G,B byte order as the
+ * reference receives it), rows `step` bytes apart, host memory.  Gray = (R*9798 + G*19235 + B*3735 + 16384) >> 15, which
+ * is what OpenCV's RGB2BGR + BGR2GRAY pair computes, evaluated on the device.  Outputs as kfs_orb_detect_and_compute;
+ * the descriptors and keypoints also stay on the device as "the current frame" for the calls below. */
+KFS_API kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t *image, size_t step, int w, int h, int channels,
+                                                 const uint8_t *mask, size_t mask_step,
+                                                 kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out);
+/* The current frame becomes the keyframe (device-to-device copy of its descriptors and keypoints) and `depth`
+ * (h x w uint16 millimetres, rows depth_step BYTES apart, host) is uploaded next to them. */
+KFS_API kfs_status kfs_frontend_promote_keyframe(kfs_frontend *fe, const uint16_t *depth, size_t depth_step);
+/* Same, from host copies of a keyframe (n rows of descriptors and keypoints, a w x h depth image). */
+KFS_API kfs_status kfs_frontend_set_keyframe(kfs_frontend *fe, const uint8_t *desc, const kfs_keypoint *kp, int n,
+                                             const uint16_t *depth, size_t depth_step, int w, int h);
+/* MatchFeatures: query = the cached keyframe, train = the current frame (cur_desc / cur_kp host rows, or both NULL to use
+ * the device-resident result of the last kfs_frontend_extract_features).  intrinsics = {fx, fy, cx, cy} (K(0,0), K(1,1),
+ * K(0,2), K(1,2)).  Survivors of d0 < ratio*d1 come out in query order: matches_out[i] (the best cv::DMatch),
+ * points3d_out[3*i..] = (x, y, z) and points2d_out[2*i..] = current keypoint pt, all as the reference's doubles
+ * (computed through the same float intermediates).  *n_out = survivors (may exceed capacity: then only `capacity` rows
+ * were written and the status is KFS_ERR_CAPACITY). */
+KFS_API kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc, const kfs_keypoint *cur_kp, int n_cur,
+                                               const double *intrinsics, float ratio,
+                                               kfs_dmatch *matches_out, double *points3d_out, double *points2d_out,
+                                               int capacity, int *n_out);
+KFS_API int kfs_frontend_last_launches(const kfs_frontend *fe);
+
 /* ---- microbenchmarks used by bench.py for the integer-pipe roofline -------------------- */
 /* Dependency-free POPC.32 (what=0) or LOP3.32 (what=1) issue-rate probe on `device`; returns 1e9 ops/s. */
 KFS_API kfs_status kfs_pipe_peak(int device, int what, double *gops);

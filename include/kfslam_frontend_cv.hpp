@@ -21,8 +21,10 @@
 #define KFS_HAVE_OPENCV 0
 #endif
 #include "kfslam_frontend.h"
+#include <cstring>
 #include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace kfs {
@@ -177,6 +179,97 @@ private:
     kfs_bf *h_;
     std::vector<cv::DMatch> flat_;
     std::vector<int> counts_;
+};
+
+// The tracker's two methods around the drop-in calls, with the reference's own signatures:
+//   std::pair<std::vector<cv::KeyPoint>, cv::Mat> VisualOdometry::ExtractFeatures(cv::Mat rgb, cv::Mat mask)        (VisualOdometry.cpp:21-33)
+//   std::pair<std::vector<cv::Point3d>, std::vector<cv::Point2d>>
+//       VisualOdometry::MatchFeatures(cv::Mat dpCurrImg, std::vector<cv::KeyPoint> kpCurrImg, std::vector<cv::DMatch>& matches)   (:35-62)
+// The keyframe the reference fetches with map->GetLastKeyFrame() (:36; descriptors, keypoints, depth — KeyFrame.hpp:35-39)
+// lives in the handle's device cache: SetKeyFrame / PromoteKeyFrame replace the KeyFrame construction at :105-123.
+class TrackerFrontEnd {
+public:
+    static cv::Ptr<TrackerFrontEnd> create(int nfeatures = 3000, float scaleFactor = 1.2f, int nlevels = 8, int fastThreshold = 20, int device = 0)
+    {
+        kfs_orb_params p;
+        kfs_orb_default_params(&p);
+        p.nfeatures = nfeatures; p.scale_factor = scaleFactor; p.nlevels = nlevels; p.fast_threshold = fastThreshold;
+        kfs_frontend *h = nullptr;
+        const kfs_status st = kfs_frontend_create(&p, device, &h);
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::create");
+        return cv::Ptr<TrackerFrontEnd>(new TrackerFrontEnd(h));
+    }
+    ~TrackerFrontEnd() { kfs_frontend_destroy(h_); }
+    TrackerFrontEnd(const TrackerFrontEnd &) = delete;
+    TrackerFrontEnd &operator=(const TrackerFrontEnd &) = delete;
+
+    // K(0,0), K(1,1), K(0,2), K(1,2) of the reference's camera matrix (VisualOdometry.cpp:53-54)
+    void setIntrinsics(double fx, double fy, double cx, double cy) { k_[0] = fx; k_[1] = fy; k_[2] = cx; k_[3] = cy; }
+    void setRatio(float r) { ratio_ = r; } // 0.6f in the reference (:46)
+
+    std::pair<std::vector<cv::KeyPoint>, cv::Mat> ExtractFeatures(const cv::Mat &rgb, const cv::Mat &mask)
+    {
+        std::vector<cv::KeyPoint> kp;
+        cv::Mat desc;
+        const int cap = kfs_frontend_capacity(h_);
+        kp.resize((size_t)cap);
+        std::vector<uint8_t> d((size_t)cap * 32);
+        int n = 0;
+        const kfs_status st = kfs_frontend_extract_features(h_, rgb.data, (size_t)rgb.step, rgb.cols, rgb.rows, rgb.channels(),
+                                                            mask.empty() ? nullptr : mask.data, mask.empty() ? 0 : (size_t)mask.step,
+                                                            reinterpret_cast<kfs_keypoint *>(kp.data()), d.data(), cap, &n);
+        if (st != KFS_OK && st != KFS_ERR_CAPACITY) detail::raise(st, "kfs::TrackerFrontEnd::ExtractFeatures");
+        if (n > cap) n = cap;
+        kp.resize((size_t)n);
+        detail::make_desc(desc, n);
+        if (n) {
+            for (int i = 0; i < n; i++) std::memcpy(desc.ptr(i), d.data() + (size_t)i * 32, 32);
+        }
+        return {kp, desc};
+    }
+    // the frame just extracted becomes the keyframe; depth = CV_16UC1 millimetres (KeyFrame::matDepth)
+    void PromoteKeyFrame(const cv::Mat &depth)
+    {
+        const kfs_status st = kfs_frontend_promote_keyframe(h_, reinterpret_cast<const uint16_t *>(depth.data), (size_t)depth.step);
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::PromoteKeyFrame");
+    }
+    void SetKeyFrame(const cv::Mat &descriptors, const std::vector<cv::KeyPoint> &keypoints, const cv::Mat &depth)
+    {
+        std::vector<uint8_t> d((size_t)descriptors.rows * 32);
+        for (int i = 0; i < descriptors.rows; i++) std::memcpy(d.data() + (size_t)i * 32, descriptors.ptr(i), 32);
+        const kfs_status st = kfs_frontend_set_keyframe(h_, d.data(), reinterpret_cast<const kfs_keypoint *>(keypoints.data()), (int)keypoints.size(),
+                                                        reinterpret_cast<const uint16_t *>(depth.data), (size_t)depth.step, depth.cols, depth.rows);
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::SetKeyFrame");
+    }
+    std::pair<std::vector<cv::Point3d>, std::vector<cv::Point2d>> MatchFeatures(const cv::Mat &dpCurrImg, const std::vector<cv::KeyPoint> &kpCurrImg,
+                                                                               std::vector<cv::DMatch> &matches)
+    {
+        const int cap = kfs_frontend_capacity(h_);
+        std::vector<cv::DMatch> m((size_t)cap);
+        std::vector<double> p3((size_t)cap * 3), p2((size_t)cap * 2);
+        std::vector<uint8_t> d((size_t)dpCurrImg.rows * 32);
+        for (int i = 0; i < dpCurrImg.rows; i++) std::memcpy(d.data() + (size_t)i * 32, dpCurrImg.ptr(i), 32);
+        int n = 0;
+        const bool resident = dpCurrImg.empty() && kpCurrImg.empty(); // match the frame ExtractFeatures left on the device
+        const kfs_status st = kfs_frontend_match_features(h_, resident ? nullptr : d.data(),
+                                                          resident ? nullptr : reinterpret_cast<const kfs_keypoint *>(kpCurrImg.data()),
+                                                          (int)kpCurrImg.size(), k_, ratio_, reinterpret_cast<kfs_dmatch *>(m.data()), p3.data(), p2.data(), cap, &n);
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::MatchFeatures");
+        std::vector<cv::Point3d> points3D;
+        std::vector<cv::Point2d> points2D;
+        for (int i = 0; i < n; i++) {
+            matches.push_back(m[(size_t)i]);                                                                  // :48
+            points3D.push_back(cv::Point3d(p3[3 * (size_t)i], p3[3 * (size_t)i + 1], p3[3 * (size_t)i + 2])); // :56
+            points2D.push_back(cv::Point2d(p2[2 * (size_t)i], p2[2 * (size_t)i + 1]));                        // :57
+        }
+        return {points3D, points2D};
+    }
+
+private:
+    explicit TrackerFrontEnd(kfs_frontend *h) : h_(h) {}
+    kfs_frontend *h_;
+    double k_[4] = {1, 1, 0, 0};
+    float ratio_ = 0.6f;
 };
 
 } // namespace kfs

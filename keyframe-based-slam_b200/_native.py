@@ -95,6 +95,14 @@ SIGNATURES = {
     "kfs_replay_submit": (_i, [_vp, C.POINTER(ReplayIO), C.POINTER(ReplayFrame), _i, _ip]),
     "kfs_replay_wait": (_i, [_vp, _i]),
     "kfs_replay_last_launches": (_i, [_vp]),
+    "kfs_frontend_create": (_i, [C.POINTER(OrbParams), _i, C.POINTER(_vp)]),
+    "kfs_frontend_destroy": (None, [_vp]),
+    "kfs_frontend_capacity": (_i, [_vp]),
+    "kfs_frontend_extract_features": (_i, [_vp, _vp, _sz, _i, _i, _i, _vp, _sz, _vp, _vp, _i, _ip]),
+    "kfs_frontend_promote_keyframe": (_i, [_vp, _vp, _sz]),
+    "kfs_frontend_set_keyframe": (_i, [_vp, _vp, _vp, _i, _vp, _sz, _i, _i]),
+    "kfs_frontend_match_features": (_i, [_vp, _vp, _vp, _i, C.POINTER(C.c_double), _f, _vp, _vp, _vp, _i, _ip]),
+    "kfs_frontend_last_launches": (_i, [_vp]),
     "kfs_pipe_peak": (_i, [_i, _i, C.POINTER(C.c_double)]),
 }
 

@@ -1,0 +1,381 @@
+// kfs_track.cu — the callers either side of the two drop-in calls:
+//     VisualOdometry::ExtractFeatures   /root/reference/src/lib/VisualOdometry.cpp:21-33
+//     VisualOdometry::MatchFeatures     /root/reference/src/lib/VisualOdometry.cpp:35-62
+//     KeyFrame (descriptors, keypoints, depth of the last keyframe)   /root/reference/include/lib/KeyFrame.hpp:35-39
+// built on the ORB and matcher handles of this library: colour -> gray on the device, a device-resident keyframe cache,
+// and ONE kernel after the kNN that does the ratio test, the depth look-up, the pin-hole back-projection and the ordered
+// compaction into the 3-D / 2-D correspondence lists solvePnPRansac consumes (:72).
+#include "kfs_common.cuh"
+#include <new>
+#include <string.h>
+
+// ---- ExtractFeatures :25-28 ----------------------------------------------------------------------------------
+// cvtColor(rgb, rgb, RGB2BGR) then cvtColor(rgb, gray, BGR2GRAY): OpenCV's 8-bit path is the 15-bit fixed point
+//   gray = (B*3735 + G*19235 + R*9798 + 16384) >> 15      with R = byte 0 of the image the reference receives
+// [probe, SURVEY Appendix A "gray probe": bit-exact vs cv2 4.13].  One thread = 4 output pixels = 12 source bytes
+// (three aligned 32-bit loads when the row allows it), one 32-bit store; pad bytes of the row replicate the last pixel.
+__device__ __forceinline__ uint32_t kfs_gray15(uint32_t r, uint32_t g, uint32_t b) { return (r * 9798u + g * 19235u + b * 3735u + 16384u) >> 15; }
+
+__global__ void __launch_bounds__(256)
+k_rgb2gray(const uint8_t *__restrict__ src, long long sstep, uint8_t *__restrict__ dst, int dpitch, int w, int h, int aligned)
+{
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 8 + threadIdx.y;
+    if (x4 >= dpitch || y >= h) return;
+    const uint8_t *row = src + (long long)y * sstep;
+    uint32_t out = 0;
+    if (aligned && x4 + 4 <= w) {
+        const uint32_t *p = reinterpret_cast<const uint32_t *>(row + 3 * x4);
+        const uint32_t a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2); // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+        out = kfs_gray15(a & 0xff, (a >> 8) & 0xff, (a >> 16) & 0xff) |
+              kfs_gray15(a >> 24, b & 0xff, (b >> 8) & 0xff) << 8 |
+              kfs_gray15((b >> 16) & 0xff, b >> 24, c & 0xff) << 16 |
+              kfs_gray15((c >> 8) & 0xff, (c >> 16) & 0xff, c >> 24) << 24;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int x = min(x4 + j, w - 1);
+            out |= kfs_gray15(__ldg(row + 3 * x), __ldg(row + 3 * x + 1), __ldg(row + 3 * x + 2)) << (8 * j);
+        }
+    }
+    *reinterpret_cast<uint32_t *>(dst + (long long)y * dpitch + x4) = out;
+}
+
+// ---- MatchFeatures :45-59 --------------------------------------------------------------------------------------
+// One CTA walks the keyframe's kNN rows in query order (the reference's loop order), 1024 rows per round:
+//   keep  <=> both neighbours exist and d0 < ratio * d1                                     (:46, fp32)
+//   z = (float)(depth(cvRound(pt.y), cvRound(pt.x)) * 0.001)                                (:52, int -> double -> float)
+//   y = (float)((pt.y - K(1,2)) * z / K(1,1)),  x likewise with K(0,2), K(0,0)              (:53-54, double -> float)
+//   points3D.push_back(Point3d(x, y, z)); points2D.push_back(kpCurr.pt)                     (:56-57, float -> double)
+// with IEEE double multiply / divide / subtract (no contraction), so every output equals the CPU's bit for bit.
+// A block scan over the keep flags gives each survivor its slot: the lists come out exactly as the reference's
+// push_back sequence.
+struct TrackArgs {
+    const kfs_dmatch *knn;        // [nq][2]
+    const kfs_keypoint *kf_kp;    // keyframe keypoints (query side)
+    const kfs_keypoint *cur_kp;   // current keypoints (train side)
+    const int *d_ncur;            // device count of the current frame (nullptr: n_cur is exact)
+    const uint16_t *depth;        // keyframe depth, rows depth_pitch ELEMENTS apart
+    long long depth_pitch;
+    int depth_w, depth_h;
+    double fx, fy, cx, cy;
+    float ratio;
+    int nq, n_cur, capacity;
+    kfs_dmatch *matches;          // [capacity]
+    double *p3d, *p2d;            // [capacity][3], [capacity][2]
+    int *n_out;                   // total survivors
+};
+
+__global__ void __launch_bounds__(1024)
+k_ratio_backproject(const TrackArgs A)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    int ncur = A.n_cur;
+    if (A.d_ncur) ncur = min(ncur, *A.d_ncur);
+    for (int q0 = 0; q0 < A.nq; q0 += 1024) {
+        const int q = q0 + tid;
+        bool keep = false;
+        kfs_dmatch m0 = {0, 0, 0, 0.f};
+        if (q < A.nq) {
+            const uint4 r0 = *reinterpret_cast<const uint4 *>(A.knn + 2 * (size_t)q), r1 = *reinterpret_cast<const uint4 *>(A.knn + 2 * (size_t)q + 1);
+            m0 = *reinterpret_cast<const kfs_dmatch *>(&r0);
+            const kfs_dmatch m1 = *reinterpret_cast<const kfs_dmatch *>(&r1);
+            // rows with fewer than 2 neighbours (fewer than 2 current keypoints) can never pass; the reference would index
+            // knnMatches[i][1] out of bounds there (:46)
+            keep = m0.trainIdx >= 0 && m1.trainIdx >= 0 && m0.trainIdx < ncur && m0.distance < __fmul_rn(A.ratio, m1.distance);
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        int wsum = s_warp[lane]; // 32 warps
+        int incl = wsum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        const int wbase = __shfl_sync(0xffffffffu, incl - wsum, warp);
+        const int slot = s_base + wbase + __popc(bal & ((1u << lane) - 1u));
+        if (keep && slot < A.capacity) {
+            const kfs_keypoint kp = A.kf_kp[m0.queryIdx];
+            const kfs_keypoint kc = A.cur_kp[m0.trainIdx];
+            const int ix = min(max(__float2int_rn(kp.x), 0), A.depth_w - 1), iy = min(max(__float2int_rn(kp.y), 0), A.depth_h - 1);
+            const int d = (int)A.depth[(long long)iy * A.depth_pitch + ix];
+            const float z = __double2float_rn(__dmul_rn((double)d, 0.001));
+            const float y = __double2float_rn(__ddiv_rn(__dmul_rn(__dsub_rn((double)kp.y, A.cy), (double)z), A.fy));
+            const float x = __double2float_rn(__ddiv_rn(__dmul_rn(__dsub_rn((double)kp.x, A.cx), (double)z), A.fx));
+            A.matches[slot] = m0;
+            A.p3d[3 * (size_t)slot + 0] = (double)x;
+            A.p3d[3 * (size_t)slot + 1] = (double)y;
+            A.p3d[3 * (size_t)slot + 2] = (double)z;
+            A.p2d[2 * (size_t)slot + 0] = (double)kc.x;
+            A.p2d[2 * (size_t)slot + 1] = (double)kc.y;
+        }
+        __syncthreads();
+        if (tid == 0) s_base += total;
+        __syncthreads();
+    }
+    if (tid == 0) *A.n_out = s_base;
+}
+
+// ---- handle ------------------------------------------------------------------------------------------------------
+struct kfs_frontend {
+    int device = 0;
+    kfs_orb *orb = nullptr;
+    kfs_bf *bf = nullptr;
+    cudaStream_t stream = nullptr; // the ORB handle's stream; the matcher is moved onto it
+    int cap = 0;                   // keypoint rows per frame (kfs_orb_capacity)
+    // colour / gray / mask staging of ExtractFeatures
+    uint8_t *d_img = nullptr, *d_gray = nullptr, *d_mask = nullptr;
+    size_t img_bytes = 0, gray_bytes = 0, mask_bytes = 0;
+    // current frame: device views of the last extraction, or uploads of the caller's rows
+    const kfs_keypoint *d_cur_kp = nullptr;
+    const uint8_t *d_cur_desc = nullptr;
+    const int *d_cur_count = nullptr;
+    int cur_n = -1, cur_w = 0, cur_h = 0;
+    uint8_t *d_up_desc = nullptr;
+    kfs_keypoint *d_up_kp = nullptr;
+    // keyframe cache (KeyFrame.hpp:35-39)
+    uint8_t *d_kf_desc = nullptr;
+    kfs_keypoint *d_kf_kp = nullptr;
+    uint16_t *d_kf_depth = nullptr;
+    size_t kf_depth_elems = 0;
+    int kf_n = -1, kf_w = 0, kf_h = 0;
+    // match outputs
+    kfs_dmatch *d_knn = nullptr, *d_good = nullptr;
+    double *d_p3d = nullptr, *d_p2d = nullptr;
+    int *d_nout = nullptr;
+    int *h_nout = nullptr; // pinned
+    int launches = 0;
+};
+
+static kfs_status fe_reserve(uint8_t **p, size_t *have, size_t need)
+{
+    if (need <= *have) return KFS_OK;
+    if (*p) { cudaFree(*p); *p = nullptr; *have = 0; }
+    const size_t cap = kfs_align_up(need + need / 4, 1 << 16);
+    KFS_CUDA_TRY(cudaMalloc(p, cap));
+    *have = cap;
+    return KFS_OK;
+}
+
+extern "C" {
+
+void kfs_frontend_destroy(kfs_frontend *fe)
+{
+    if (!fe) return;
+    KfsDeviceGuard guard(fe->device);
+    if (fe->stream) cudaStreamSynchronize(fe->stream);
+    if (fe->bf) kfs_bf_destroy(fe->bf);
+    if (fe->orb) kfs_orb_destroy(fe->orb);
+    void *bufs[] = {fe->d_img, fe->d_gray, fe->d_mask, fe->d_up_desc, fe->d_up_kp, fe->d_kf_desc, fe->d_kf_kp, fe->d_kf_depth,
+                    fe->d_knn, fe->d_good, fe->d_p3d, fe->d_p2d, fe->d_nout};
+    for (void *b : bufs) if (b) cudaFree(b);
+    if (fe->h_nout) cudaFreeHost(fe->h_nout);
+    delete fe;
+}
+
+kfs_status kfs_frontend_create(const kfs_orb_params *params, int device, kfs_frontend **out)
+{
+    if (!out) KFS_FAIL(KFS_ERR_INVALID_ARG, "out is NULL");
+    *out = nullptr;
+    kfs_frontend *fe = new (std::nothrow) kfs_frontend();
+    if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "out of host memory");
+    fe->device = device;
+    kfs_status s = kfs_orb_create(params, device, &fe->orb);
+    if (!s) s = kfs_bf_create(KFS_NORM_HAMMING, 0, device, &fe->bf);
+    if (s) { kfs_frontend_destroy(fe); return s; }
+    KfsDeviceGuard guard(device);
+    fe->stream = (cudaStream_t)kfs_orb_get_stream(fe->orb);
+    kfs_bf_set_stream(fe->bf, (void *)fe->stream);
+    fe->cap = kfs_orb_capacity(fe->orb);
+    const size_t n = (size_t)fe->cap;
+    cudaError_t e = cudaSuccess;
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_up_desc, n * 32);
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_up_kp, n * sizeof(kfs_keypoint));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_kf_desc, n * 32);
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_kf_kp, n * sizeof(kfs_keypoint));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_knn, n * 2 * sizeof(kfs_dmatch));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_good, n * sizeof(kfs_dmatch));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_p3d, n * 3 * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_p2d, n * 2 * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_nout, sizeof(int));
+    if (e == cudaSuccess) e = cudaMallocHost(&fe->h_nout, sizeof(int));
+    if (e != cudaSuccess) {
+        kfs_frontend_destroy(fe);
+        KFS_FAIL(KFS_ERR_CUDA, "kfs_frontend_create: %s", cudaGetErrorString(e));
+    }
+    *out = fe;
+    return KFS_OK;
+}
+
+int kfs_frontend_capacity(const kfs_frontend *fe) { return fe ? fe->cap : 0; }
+int kfs_frontend_last_launches(const kfs_frontend *fe) { return fe ? fe->launches : 0; }
+
+kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t *image, size_t step, int w, int h, int channels,
+                                         const uint8_t *mask, size_t mask_step,
+                                         kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out)
+{
+    if (!fe || !n_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle or n_out is NULL");
+    *n_out = 0;
+    if (channels != 1 && channels != 3) KFS_FAIL(KFS_ERR_UNSUPPORTED, "ExtractFeatures: %d channels (the reference handles 1 or 3, VisualOdometry.cpp:27)", channels);
+    if (w < 0 || h < 0 || capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "negative size");
+    if (w == 0 || h == 0) { fe->cur_n = 0; return KFS_OK; }
+    if (!image || step < (size_t)w * channels) KFS_FAIL(KFS_ERR_INVALID_ARG, "image is NULL or step < w*channels");
+    if (mask && mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < w");
+    if (capacity > 0 && (!kp_out || !desc_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
+    KfsDeviceGuard guard(fe->device);
+    cudaStream_t st = fe->stream;
+    const size_t gpitch = kfs_align_up((size_t)w, 128);
+    kfs_status s = fe_reserve(&fe->d_gray, &fe->gray_bytes, gpitch * h);
+    if (s) return s;
+    fe->launches = 0;
+    if (channels == 3) {
+        const size_t ipitch = kfs_align_up((size_t)w * 3, 16);
+        s = fe_reserve(&fe->d_img, &fe->img_bytes, ipitch * h);
+        if (s) return s;
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(fe->d_img, ipitch, image, step, (size_t)w * 3, h, cudaMemcpyHostToDevice, st));
+        k_rgb2gray<<<dim3(kfs_div_up((int)gpitch, 128), kfs_div_up(h, 8)), dim3(32, 8), 0, st>>>(fe->d_img, (long long)ipitch, fe->d_gray, (int)gpitch, w, h, 1);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_rgb2gray launch: %s", cudaGetErrorString(e));
+        fe->launches++;
+    } else {
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(fe->d_gray, gpitch, image, step, (size_t)w, h, cudaMemcpyHostToDevice, st));
+    }
+    const uint8_t *d_mask = nullptr;
+    if (mask) {
+        s = fe_reserve(&fe->d_mask, &fe->mask_bytes, gpitch * h);
+        if (s) return s;
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(fe->d_mask, gpitch, mask, mask_step, (size_t)w, h, cudaMemcpyHostToDevice, st));
+        d_mask = fe->d_mask;
+    }
+    s = kfs_orb_extract_device(fe->orb, fe->d_gray, gpitch, gpitch * h, w, h, 1, d_mask, gpitch, gpitch * h);
+    if (s) return s;
+    fe->launches += kfs_orb_last_launches(fe->orb);
+    int dcap = 0, nb = 0;
+    s = kfs_orb_device_results(fe->orb, &fe->d_cur_kp, &fe->d_cur_desc, &fe->d_cur_count, &dcap, &nb);
+    if (s) return s;
+    s = kfs_orb_fetch_results(fe->orb, kp_out, desc_out, capacity, n_out);
+    fe->cur_n = *n_out < dcap ? *n_out : dcap;
+    fe->cur_w = w; fe->cur_h = h;
+    return s;
+}
+
+static kfs_status fe_upload_depth(kfs_frontend *fe, const uint16_t *depth, size_t depth_step, int w, int h)
+{
+    if (!depth || w <= 0 || h <= 0 || depth_step < (size_t)w * 2) KFS_FAIL(KFS_ERR_INVALID_ARG, "depth is NULL, empty or depth_step < 2*w");
+    const size_t elems = (size_t)w * h;
+    if (elems > fe->kf_depth_elems) {
+        if (fe->d_kf_depth) { KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream)); cudaFree(fe->d_kf_depth); fe->d_kf_depth = nullptr; fe->kf_depth_elems = 0; }
+        KFS_CUDA_TRY(cudaMalloc(&fe->d_kf_depth, elems * 2));
+        fe->kf_depth_elems = elems;
+    }
+    KFS_CUDA_TRY(cudaMemcpy2DAsync(fe->d_kf_depth, (size_t)w * 2, depth, depth_step, (size_t)w * 2, h, cudaMemcpyHostToDevice, fe->stream));
+    fe->kf_w = w; fe->kf_h = h;
+    return KFS_OK;
+}
+
+kfs_status kfs_frontend_promote_keyframe(kfs_frontend *fe, const uint16_t *depth, size_t depth_step)
+{
+    if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
+    if (fe->cur_n < 0 || !fe->d_cur_desc) KFS_FAIL(KFS_ERR_INVALID_ARG, "promote_keyframe: no frame has been extracted on this handle yet");
+    KfsDeviceGuard guard(fe->device);
+    kfs_status s = fe_upload_depth(fe, depth, depth_step, fe->cur_w, fe->cur_h);
+    if (s) return s;
+    if (fe->cur_n > 0) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_kf_desc, fe->d_cur_desc, (size_t)fe->cur_n * 32, cudaMemcpyDeviceToDevice, fe->stream));
+        KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_kf_kp, fe->d_cur_kp, (size_t)fe->cur_n * sizeof(kfs_keypoint), cudaMemcpyDeviceToDevice, fe->stream));
+    }
+    fe->kf_n = fe->cur_n;
+    return KFS_OK;
+}
+
+kfs_status kfs_frontend_set_keyframe(kfs_frontend *fe, const uint8_t *desc, const kfs_keypoint *kp, int n,
+                                     const uint16_t *depth, size_t depth_step, int w, int h)
+{
+    if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
+    if (n < 0 || n > fe->cap) KFS_FAIL(KFS_ERR_CAPACITY, "set_keyframe: %d rows, handle capacity %d", n, fe->cap);
+    if (n > 0 && (!desc || !kp)) KFS_FAIL(KFS_ERR_INVALID_ARG, "desc or kp is NULL");
+    KfsDeviceGuard guard(fe->device);
+    kfs_status s = fe_upload_depth(fe, depth, depth_step, w, h);
+    if (s) return s;
+    if (n > 0) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_kf_desc, desc, (size_t)n * 32, cudaMemcpyHostToDevice, fe->stream));
+        KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_kf_kp, kp, (size_t)n * sizeof(kfs_keypoint), cudaMemcpyHostToDevice, fe->stream));
+    }
+    KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream)); // the caller may reuse its (pageable) buffers right away
+    fe->kf_n = n;
+    return KFS_OK;
+}
+
+kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc, const kfs_keypoint *cur_kp, int n_cur,
+                                       const double *intrinsics, float ratio,
+                                       kfs_dmatch *matches_out, double *points3d_out, double *points2d_out,
+                                       int capacity, int *n_out)
+{
+    if (!fe || !n_out || !intrinsics) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle, intrinsics or n_out is NULL");
+    *n_out = 0;
+    if (fe->kf_n < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_features: no keyframe cached (promote_keyframe / set_keyframe first)");
+    if (capacity < 0 || (capacity > 0 && (!matches_out || !points3d_out || !points2d_out))) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers");
+    if (intrinsics[0] == 0.0 || intrinsics[1] == 0.0) KFS_FAIL(KFS_ERR_INVALID_ARG, "fx or fy is zero");
+    KfsDeviceGuard guard(fe->device);
+    cudaStream_t st = fe->stream;
+    const kfs_keypoint *d_kp;
+    const uint8_t *d_desc;
+    const int *d_cnt = nullptr;
+    int nt;
+    if (cur_desc || cur_kp) {
+        if (!cur_desc || !cur_kp || n_cur < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "cur_desc / cur_kp must both be given with n_cur >= 0");
+        if (n_cur > fe->cap) KFS_FAIL(KFS_ERR_CAPACITY, "match_features: %d current rows, handle capacity %d", n_cur, fe->cap);
+        if (n_cur > 0) {
+            KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_up_desc, cur_desc, (size_t)n_cur * 32, cudaMemcpyHostToDevice, st));
+            KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_up_kp, cur_kp, (size_t)n_cur * sizeof(kfs_keypoint), cudaMemcpyHostToDevice, st));
+        }
+        d_kp = fe->d_up_kp; d_desc = fe->d_up_desc; nt = n_cur;
+    } else {
+        if (fe->cur_n < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_features: no current frame on the device (extract_features first)");
+        d_kp = fe->d_cur_kp; d_desc = fe->d_cur_desc; d_cnt = fe->d_cur_count; nt = fe->cur_n;
+    }
+    fe->launches = 0;
+    if (fe->kf_n == 0) return KFS_OK; // knnMatch of an empty query: no rows
+    // the reference indexes knnMatches[i][1] unguarded (:46): with fewer than 2 current keypoints it is undefined there;
+    // here such rows simply never pass
+    kfs_bf_pair pair;
+    pair.query = fe->d_kf_desc; pair.nq = fe->kf_n; pair.d_nq = nullptr;
+    pair.train = d_desc; pair.nt = nt; pair.d_nt = nullptr;
+    pair.out = fe->d_knn; pair.counts = nullptr;
+    kfs_status s = kfs_bf_knn_match_pairs_device(fe->bf, &pair, 1, 2);
+    if (s) return s;
+    fe->launches += kfs_bf_last_launches(fe->bf) > 0 ? 1 : 0;
+    TrackArgs A;
+    A.knn = fe->d_knn; A.kf_kp = fe->d_kf_kp; A.cur_kp = d_kp; A.d_ncur = d_cnt;
+    A.depth = fe->d_kf_depth; A.depth_pitch = fe->kf_w; A.depth_w = fe->kf_w; A.depth_h = fe->kf_h;
+    A.fx = intrinsics[0]; A.fy = intrinsics[1]; A.cx = intrinsics[2]; A.cy = intrinsics[3];
+    A.ratio = ratio; A.nq = fe->kf_n; A.n_cur = nt;
+    A.capacity = capacity < fe->cap ? capacity : fe->cap;
+    A.matches = fe->d_good; A.p3d = fe->d_p3d; A.p2d = fe->d_p2d; A.n_out = fe->d_nout;
+    k_ratio_backproject<<<1, 1024, 0, st>>>(A);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_ratio_backproject launch: %s", cudaGetErrorString(e));
+    fe->launches++;
+    KFS_CUDA_TRY(cudaMemcpyAsync(fe->h_nout, fe->d_nout, sizeof(int), cudaMemcpyDeviceToHost, st));
+    KFS_CUDA_TRY(cudaStreamSynchronize(st));
+    const int n = *fe->h_nout;
+    *n_out = n;
+    const int m = n < A.capacity ? n : A.capacity;
+    if (m > 0) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(matches_out, fe->d_good, (size_t)m * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, st));
+        KFS_CUDA_TRY(cudaMemcpyAsync(points3d_out, fe->d_p3d, (size_t)m * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        KFS_CUDA_TRY(cudaMemcpyAsync(points2d_out, fe->d_p2d, (size_t)m * 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        KFS_CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    if (n > capacity) KFS_FAIL(KFS_ERR_CAPACITY, "match_features: %d survivors, output capacity %d", n, capacity);
+    return KFS_OK;
+}
+
+} // extern "C"

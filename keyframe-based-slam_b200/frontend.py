@@ -298,3 +298,82 @@ class Replay:
         st = N.check(N.lib().kfs_replay_wait(self._h, ticket), allow=(N.KFS_ERR_CAPACITY,))
         self._keep.pop(ticket, None)
         return st
+
+
+class TrackerFrontEnd:
+    """VisualOdometry::ExtractFeatures / MatchFeatures as the reference's tracker calls them
+    (/root/reference/src/lib/VisualOdometry.cpp:21-33, :35-62) over kfs_frontend_*: colour -> gray on the device, the last
+    keyframe (descriptors, keypoints, depth; KeyFrame.hpp:35-39) cached on the device, and kNN + ratio test + depth
+    look-up + pin-hole back-projection returning the (points3D, points2D, matches) the PnP stage consumes."""
+
+    def __init__(self, nfeatures=3000, scaleFactor=1.2, nlevels=8, fastThreshold=20, device=0):
+        self._h = C.c_void_p()
+        p = N.OrbParams()
+        N.lib().kfs_orb_default_params(C.byref(p))
+        p.nfeatures, p.scale_factor, p.nlevels, p.fast_threshold = nfeatures, scaleFactor, nlevels, fastThreshold
+        N.check(N.lib().kfs_frontend_create(C.byref(p), device, C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            N.lib().kfs_frontend_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    @property
+    def capacity(self):
+        return N.lib().kfs_frontend_capacity(self._h)
+
+    @property
+    def last_launches(self):
+        return N.lib().kfs_frontend_last_launches(self._h)
+
+    def extractFeatures(self, rgb, mask=None):
+        """rgb: uint8 [H,W,3] (R,G,B byte order, as the reference receives it) or [H,W] gray -> (keypoints, descriptors)."""
+        rgb = np.asarray(rgb)
+        assert rgb.dtype == np.uint8 and rgb.ndim in (2, 3) and rgb.strides[-1] == 1
+        ch = 1 if rgb.ndim == 2 else rgb.shape[2]
+        if rgb.ndim == 3 and rgb.strides[1] != ch:
+            rgb = np.ascontiguousarray(rgb)
+        h, w = rgb.shape[:2]
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, dtype=np.uint8)
+        cap = self.capacity
+        kp = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int()
+        N.check(N.lib().kfs_frontend_extract_features(self._h, rgb.ctypes.data, rgb.strides[0], w, h, ch, _ptr(mask),
+                                                      mask.strides[0] if mask is not None else 0, kp.ctypes.data, desc.ctypes.data, cap, C.byref(n)),
+                allow=(N.KFS_ERR_CAPACITY,))
+        m = min(n.value, cap)
+        return kp[:m].copy(), desc[:m].copy()
+
+    def promoteKeyframe(self, depth):
+        depth = np.ascontiguousarray(depth, dtype=np.uint16)
+        N.check(N.lib().kfs_frontend_promote_keyframe(self._h, depth.ctypes.data, depth.strides[0]))
+
+    def setKeyframe(self, desc, kp, depth):
+        desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        kp = np.ascontiguousarray(kp, dtype=KP_DTYPE)
+        depth = np.ascontiguousarray(depth, dtype=np.uint16)
+        N.check(N.lib().kfs_frontend_set_keyframe(self._h, desc.ctypes.data, kp.ctypes.data, len(kp), depth.ctypes.data, depth.strides[0],
+                                                  depth.shape[1], depth.shape[0]))
+
+    def matchFeatures(self, K, dpCurrImg=None, kpCurrImg=None, ratio=0.6):
+        """K: 3x3 camera matrix.  -> (points3D float64 [n,3], points2D float64 [n,2], matches DM_DTYPE [n]) in the order of the
+        reference's loop over the keyframe's descriptors.  With dpCurrImg/kpCurrImg None the device-resident result of the
+        last extractFeatures is matched."""
+        K = np.asarray(K, dtype=np.float64)
+        intr = (C.c_double * 4)(K[0, 0], K[1, 1], K[0, 2], K[1, 2])
+        cap = self.capacity
+        m = np.zeros(cap, DM_DTYPE)
+        p3 = np.zeros((cap, 3), np.float64)
+        p2 = np.zeros((cap, 2), np.float64)
+        n = C.c_int()
+        if dpCurrImg is not None:
+            dpCurrImg = np.ascontiguousarray(dpCurrImg, dtype=np.uint8).reshape(-1, 32)
+            kpCurrImg = np.ascontiguousarray(kpCurrImg, dtype=KP_DTYPE)
+            assert len(dpCurrImg) == len(kpCurrImg)
+        N.check(N.lib().kfs_frontend_match_features(self._h, _ptr(dpCurrImg), _ptr(kpCurrImg), 0 if dpCurrImg is None else len(dpCurrImg),
+                                                    intr, ratio, m.ctypes.data, p3.ctypes.data, p2.ctypes.data, cap, C.byref(n)))
+        return p3[:n.value].copy(), p2[:n.value].copy(), m[:n.value].copy()

@@ -25,7 +25,7 @@ class OrbParams(C.Structure):
 
 def build(force=False):
     so = os.path.join(_HERE, "libkforacle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.c", "knn_oracle.c", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.c", "knn_oracle.c", "track_oracle.c", "Makefile")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     return so
@@ -58,6 +58,10 @@ def lib():
                                                     C.POINTER(C.c_int), C.POINTER(u8p), C.c_int]
         L.kfo_knn_match.argtypes = [u8p, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int)]
         L.kfo_ratio_test.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float, C.c_void_p]
+        L.kfo_rgb2gray.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, u8p, C.c_size_t]
+        L.kfo_match_features.restype = C.c_int
+        L.kfo_match_features.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_double), C.c_float,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         _LIB = L
     return _LIB
 
@@ -180,3 +184,29 @@ def ratio_test(matches, counts, ratio=0.6):
     good = np.zeros(nq, DM_DTYPE)
     n = lib().kfo_ratio_test(matches.ctypes.data, counts.ctypes.data_as(C.POINTER(C.c_int)), nq, k, ratio, good.ctypes.data)
     return good[:n].copy()
+
+
+def rgb2gray(rgb):
+    """VisualOdometry.cpp:25-28 (RGB2BGR + BGR2GRAY): uint8 [H,W,3] (R,G,B) -> uint8 [H,W]."""
+    rgb = np.ascontiguousarray(rgb, dtype=np.uint8)
+    h, w, _ = rgb.shape
+    out = np.zeros((h, w), np.uint8)
+    lib().kfo_rgb2gray(_u8(rgb), rgb.strides[0], w, h, _u8(out), out.strides[0])
+    return out
+
+
+def match_features(knn, kf_kp, cur_kp, depth, K, ratio=0.6):
+    """VisualOdometry.cpp:45-59 on kNN rows (nq,2): -> (points3D [n,3] f64, points2D [n,2] f64, matches DM_DTYPE [n])."""
+    knn = np.ascontiguousarray(knn, dtype=DM_DTYPE).reshape(-1, 2)
+    kf_kp = np.ascontiguousarray(kf_kp, dtype=KP_DTYPE)
+    cur_kp = np.ascontiguousarray(cur_kp, dtype=KP_DTYPE)
+    depth = np.ascontiguousarray(depth, dtype=np.uint16)
+    K = np.asarray(K, dtype=np.float64)
+    intr = (C.c_double * 4)(K[0, 0], K[1, 1], K[0, 2], K[1, 2])
+    nq = knn.shape[0]
+    m = np.zeros(nq, DM_DTYPE)
+    p3 = np.zeros((nq, 3), np.float64)
+    p2 = np.zeros((nq, 2), np.float64)
+    n = lib().kfo_match_features(knn.ctypes.data, nq, kf_kp.ctypes.data, cur_kp.ctypes.data, depth.ctypes.data, depth.strides[0], intr, ratio,
+                                 m.ctypes.data, p3.ctypes.data, p2.ctypes.data, nq)
+    return p3[:n].copy(), p2[:n].copy(), m[:n].copy()

@@ -27,6 +27,37 @@ int main(int argc, char **argv)
         }
         return 0;
     }
+    if (argc == 10 && !std::strcmp(argv[1], "--track")) {
+        // adapter_test --track <w> <h> <nfeatures> <rgbA.raw> <rgbB.raw> <depthA.raw> <out.bin> <fx,fy,cx,cy>
+        // the reference's Track() front half: ExtractFeatures(keyframe), KeyFrame creation, ExtractFeatures(current),
+        // MatchFeatures (VisualOdometry.cpp:138, :105-123, :144) through kfs::TrackerFrontEnd
+        const int w = std::atoi(argv[2]), h = std::atoi(argv[3]), nf = std::atoi(argv[4]);
+        auto a = slurp(argv[5]), b = slurp(argv[6]), dep = slurp(argv[7]);
+        if ((int)a.size() != w * h * 3 || (int)b.size() != w * h * 3 || (int)dep.size() != w * h * 2) { std::fprintf(stderr, "bad sizes\n"); return 65; }
+        double k[4];
+        if (std::sscanf(argv[9], "%lf,%lf,%lf,%lf", &k[0], &k[1], &k[2], &k[3]) != 4) return 66;
+        cv::Ptr<kfs::TrackerFrontEnd> fe = kfs::TrackerFrontEnd::create(nf);
+        fe->setIntrinsics(k[0], k[1], k[2], k[3]);
+        cv::Mat rgbA(h, w, cv::CV_8UC3, a.data()), rgbB(h, w, cv::CV_8UC3, b.data()), depth(h, w, cv::CV_16UC1, dep.data()), mask;
+        auto fa = fe->ExtractFeatures(rgbA, mask);
+        fe->PromoteKeyFrame(depth);
+        auto fb = fe->ExtractFeatures(rgbB, mask);
+        std::vector<cv::DMatch> matches;
+        auto pts = fe->MatchFeatures(fb.second, fb.first, matches);          // host rows, like the reference passes them
+        std::vector<cv::DMatch> matches2;
+        auto pts2 = fe->MatchFeatures(cv::Mat(), {}, matches2);              // device-resident current frame
+        const bool same = matches.size() == matches2.size() && pts.first.size() == pts2.first.size() &&
+                          !std::memcmp(pts.first.data(), pts2.first.data(), pts.first.size() * sizeof(cv::Point3d)) &&
+                          !std::memcmp(matches.data(), matches2.data(), matches.size() * sizeof(cv::DMatch));
+        std::ofstream o(argv[8], std::ios::binary);
+        const int hdr[4] = {(int)fa.first.size(), (int)fb.first.size(), (int)matches.size(), same ? 1 : 0};
+        o.write((const char *)hdr, sizeof(hdr));
+        o.write((const char *)fb.first.data(), fb.first.size() * sizeof(cv::KeyPoint));
+        o.write((const char *)matches.data(), matches.size() * sizeof(cv::DMatch));
+        o.write((const char *)pts.first.data(), pts.first.size() * sizeof(cv::Point3d));
+        o.write((const char *)pts.second.data(), pts.second.size() * sizeof(cv::Point2d));
+        return 0;
+    }
     if (argc != 7) { std::fprintf(stderr, "usage\n"); return 64; }
     const int w = std::atoi(argv[1]), h = std::atoi(argv[2]), nf = std::atoi(argv[3]);
     auto a = slurp(argv[4]), b = slurp(argv[5]);

@@ -59,3 +59,27 @@ def test_adapter_reference_call_sequence(tmp_path):
     good = np.frombuffer(buf, DM, ngood, off)
     ref = [(i, int(gk["idx"][i, 0])) for i in range(nknn) if gk["dist"][i, 0] < np.float32(0.6) * gk["dist"][i, 1]]
     assert [(int(g["queryIdx"]), int(g["trainIdx"])) for g in good] == ref
+
+
+@pytest.mark.gpu
+def test_adapter_tracker_front_half(tmp_path, oracle):
+    """kfs::TrackerFrontEnd (ExtractFeatures / PromoteKeyFrame / MatchFeatures with the reference's signatures) vs the oracle."""
+    from _track_util import make_depth, make_rgb
+    exe = _build()
+    a, b, depth = make_rgb(480, 640, 21), make_rgb(480, 640, 21, shift=3), make_depth(480, 640, 5)
+    fa, fb, fd, fo = tmp_path / "a.rgb", tmp_path / "b.rgb", tmp_path / "d.u16", tmp_path / "out.bin"
+    a.tofile(fa); b.tofile(fb); depth.tofile(fd)
+    r = subprocess.run([exe, "--track", "640", "480", "1000", str(fa), str(fb), str(fd), str(fo), "525.3,524.9,319.7,239.2"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    buf = open(fo, "rb").read()
+    na, nb, nm, same = struct.unpack_from("<4i", buf, 0)
+    off = 16
+    kpb = np.frombuffer(buf, KP, nb, off); off += nb * 28
+    m = np.frombuffer(buf, DM, nm, off); off += nm * 16
+    p3 = np.frombuffer(buf, np.float64, nm * 3, off).reshape(nm, 3); off += nm * 24
+    p2 = np.frombuffer(buf, np.float64, nm * 2, off).reshape(nm, 2)
+    g = golden("track_cfg1")
+    K = np.array([[525.3, 0, 319.7], [0, 524.9, 239.2], [0, 0, 1]])
+    r3, r2, rm = oracle.match_features(g["knn"], g["kf_kp"], g["cur_kp"], depth, K, 0.6)
+    assert na == len(g["kf_kp"]) and np.array_equal(kpb, g["cur_kp"]) and same == 1
+    assert nm == len(rm) > 50 and np.array_equal(m, rm) and np.array_equal(p3, r3) and np.array_equal(p2, r2)
