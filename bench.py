@@ -480,6 +480,42 @@ def run_ours(args):
     except Exception as ex:  # latency is informative only
         lat = {"error": str(ex)[:200]}
 
+    # ---- window matching (configs[3]: current frame vs the 10 keyframes of a local-BA window = 10 pairs of 2000 x 2000 per
+    #      frame; kfs_frontend_match_window issues exactly this launch): (a) one frame per call, (b) every frame of the batch
+    win = None
+    try:
+        WIN = 10
+        wout = torch.empty((B * WIN, cap, 2, 16), dtype=torch.uint8, device=dev)
+
+        def wpairs(frames):
+            pp = []
+            for i in frames:
+                for j in range(WIN):
+                    k = (i + 1 + j) % B     # ten other frames of the batch stand in for the window's keyframes
+                    pp.append(dict(query=d_desc + k * cap * 32, nq=cap, d_nq=d_cnt + 4 * k, train=d_desc + i * cap * 32, nt=cap,
+                                   d_nt=d_cnt + 4 * i, out=wout[len(pp)].data_ptr(), counts=None))
+            return pp
+        one_f, all_f = wpairs([0]), wpairs(range(B))
+        res = {}
+        with torch.cuda.stream(stream):
+            for name, pp, reps_w in (("one_frame", one_f, 20), ("batch", all_f, 3)):
+                bf.knnMatchPairsDevice(pp, 2)
+                torch.cuda.synchronize(dev)
+                a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream)
+                for _ in range(reps_w):
+                    bf.knnMatchPairsDevice(pp, 2)
+                b_.record(stream)
+                torch.cuda.synchronize(dev)
+                nfr = len(pp) // WIN
+                cmp_ = float(sum(counts[(i + 1 + j) % B] * counts[i] for i in range(nfr) for j in range(WIN)))
+                ms_w = a.elapsed_time(b_) / reps_w
+                res[name] = {"frames": nfr, "pairs": len(pp), "us_per_frame": round(ms_w * 1e3 / nfr, 2), "gcmp_s": round(cmp_ / (ms_w * 1e-3) / 1e9, 1)}
+        win = {"workload": "cfg4: 2000 x (10 x 2000) per frame, k=2", "window": WIN, **res}
+        del wout
+    except Exception as ex:  # informative only
+        win = {"error": str(ex)[:200]}
+
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -557,7 +593,7 @@ def run_ours(args):
                     "drop_in_calls": dropin},
             "gpu_launches": int(launches),
             "roofline": roofline, "roofline_popc": roofline_popc, "kernels": kernels, "stream_latency": lat,
-            "cpu_baseline": cpu}
+            "window_matching": win, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()

@@ -269,6 +269,32 @@ KFS_API kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *
                                                const double *intrinsics, float ratio,
                                                kfs_dmatch *matches_out, double *points3d_out, double *points2d_out,
                                                int capacity, int *n_out);
+/* ---- keyframe window --------------------------------------------------------
+ *   Map::GetNKeyFrames(win)   /root/reference/src/lib/Map.cpp:72-78    the last `win` keyframes, oldest first, or all of
+ *                             them while fewer exist
+ *   LocalBundleAdjustment     /root/reference/include/lib/Optimizers.hpp:70 (window 5), src/lib/Optimizers.cpp:59
+ *   Map::CreateMapPoints      /root/reference/src/lib/Map.cpp:16-65    consumes (keyframe, keyframe) DMatch lists
+ * The handle keeps the last `window` keyframes (descriptors, keypoints, depth) in a device ring; promote_keyframe /
+ * set_keyframe push into it, match_features keeps using the newest one (Map::GetLastKeyFrame, Map.cpp:68-70).
+ * kfs_frontend_set_window drops every cached keyframe.  1 <= window <= KFS_MAX_WINDOW; a new handle has window 1. */
+#define KFS_MAX_WINDOW 64
+KFS_API kfs_status kfs_frontend_set_window(kfs_frontend *fe, int window);
+KFS_API int kfs_frontend_window(const kfs_frontend *fe);         /* ring size                                         */
+KFS_API int kfs_frontend_window_count(const kfs_frontend *fe);   /* keyframes held = min(keyframes pushed, window)   */
+/* Current frame against every keyframe of the window in ONE kNN launch (one (keyframe, frame) pair per keyframe, as
+ * configs 4 and 5 of BASELINE.json shape it) plus one ratio-test launch.  For keyframe i of GetNKeyFrames' order
+ * (i = 0 oldest): knnMatch(keyframe_i descriptors (query), current descriptors (train), 2) exactly as
+ * VisualOdometry.cpp:39, then d0 < ratio*d1 (:46) with ordered compaction.
+ *   cur_desc / n_cur   host rows of the current frame, or NULL to use the device-resident result of the last
+ *                      kfs_frontend_extract_features
+ *   kf_rows_out[i]     query rows of keyframe i                                         (KFS_MAX_WINDOW ints or NULL)
+ *   knn_out            [n_kf][knn_rows][2] raw kNN rows (unused entries {q,-1,-1,FLT_MAX})   (NULL: not wanted)
+ *   good_out           [n_kf][capacity] survivors in query order; n_good_out[i] = survivors of keyframe i
+ * Returns KFS_ERR_CAPACITY (outputs truncated) when a keyframe has more rows than knn_rows or more survivors than
+ * capacity.  *n_kf_out = keyframes matched (0 with an empty ring: no error, like an empty vecKeyFrames). */
+KFS_API kfs_status kfs_frontend_match_window(kfs_frontend *fe, const uint8_t *cur_desc, int n_cur, float ratio,
+                                             int *kf_rows_out, kfs_dmatch *knn_out, int knn_rows,
+                                             kfs_dmatch *good_out, int *n_good_out, int capacity, int *n_kf_out);
 KFS_API int kfs_frontend_last_launches(const kfs_frontend *fe);
 
 /* ---- microbenchmarks used by bench.py for the integer-pipe roofline -------------------- */

@@ -265,6 +265,30 @@ public:
         return {points3D, points2D};
     }
 
+    // ---- keyframe window: Map::GetNKeyFrames (src/lib/Map.cpp:72-78; window 5 at include/lib/Optimizers.hpp:70) ----
+    void SetWindow(int window)
+    {
+        const kfs_status st = kfs_frontend_set_window(h_, window);
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::SetWindow");
+    }
+    int WindowCount() const { return kfs_frontend_window_count(h_); }
+    // dpCurrImg (empty: the frame ExtractFeatures left on the device) against every cached keyframe, oldest first:
+    // result[i] = ratio-test survivors of knnMatch(keyframe_i, current, 2), the DMatch lists Map::CreateMapPoints consumes
+    std::vector<std::vector<cv::DMatch>> MatchWindow(const cv::Mat &dpCurrImg)
+    {
+        const int cap = kfs_frontend_capacity(h_), cnt = kfs_frontend_window_count(h_);
+        std::vector<cv::DMatch> good((size_t)cap * (size_t)(cnt > 0 ? cnt : 1));
+        std::vector<uint8_t> d((size_t)dpCurrImg.rows * 32);
+        for (int i = 0; i < dpCurrImg.rows; i++) std::memcpy(d.data() + (size_t)i * 32, dpCurrImg.ptr(i), 32);
+        int n_good[KFS_MAX_WINDOW], nkf = 0;
+        const kfs_status st = kfs_frontend_match_window(h_, dpCurrImg.empty() ? nullptr : d.data(), dpCurrImg.rows, ratio_, nullptr, nullptr, 0,
+                                                        reinterpret_cast<kfs_dmatch *>(good.data()), n_good, cap, &nkf);
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::MatchWindow");
+        std::vector<std::vector<cv::DMatch>> out((size_t)nkf);
+        for (int i = 0; i < nkf; i++) out[(size_t)i].assign(good.begin() + (size_t)i * cap, good.begin() + (size_t)i * cap + n_good[i]);
+        return out;
+    }
+
 private:
     explicit TrackerFrontEnd(kfs_frontend *h) : h_(h) {}
     kfs_frontend *h_;

@@ -16,6 +16,7 @@ DM_DTYPE = np.dtype([("queryIdx", "<i4"), ("trainIdx", "<i4"), ("imgIdx", "<i4")
 assert KP_DTYPE.itemsize == 28 and DM_DTYPE.itemsize == 16
 
 KFS_OK, KFS_ERR_INVALID_ARG, KFS_ERR_UNSUPPORTED, KFS_ERR_CAPACITY, KFS_ERR_CUDA, KFS_ERR_NO_DEVICE = range(6)
+KFS_MAX_WINDOW = 64  # include/kfslam_frontend.h
 STATUS_NAMES = ["KFS_OK", "KFS_ERR_INVALID_ARG", "KFS_ERR_UNSUPPORTED", "KFS_ERR_CAPACITY", "KFS_ERR_CUDA", "KFS_ERR_NO_DEVICE"]
 STAGE_NAMES = ["ingest", "pyramid", "fast", "select_harris", "select_sort", "blur", "describe"]
 NORM_HAMMING = 6
@@ -102,6 +103,10 @@ SIGNATURES = {
     "kfs_frontend_promote_keyframe": (_i, [_vp, _vp, _sz]),
     "kfs_frontend_set_keyframe": (_i, [_vp, _vp, _vp, _i, _vp, _sz, _i, _i]),
     "kfs_frontend_match_features": (_i, [_vp, _vp, _vp, _i, C.POINTER(C.c_double), _f, _vp, _vp, _vp, _i, _ip]),
+    "kfs_frontend_set_window": (_i, [_vp, _i]),
+    "kfs_frontend_window": (_i, [_vp]),
+    "kfs_frontend_window_count": (_i, [_vp]),
+    "kfs_frontend_match_window": (_i, [_vp, _vp, _i, _f, _ip, _vp, _i, _vp, _ip, _i, _ip]),
     "kfs_frontend_last_launches": (_i, [_vp]),
     "kfs_pipe_peak": (_i, [_i, _i, C.POINTER(C.c_double)]),
 }

@@ -379,6 +379,7 @@ kfs_status kfs_bf_launch_table(kfs_bf *b, const BfPairDev *d_table, int npairs, 
     if (npairs == 0 || max_nq == 0) return KFS_OK;
     return bf_launch_kernel(b, d_table, npairs, max_nq, max_nq, k, st); // replay: query and train share the capacity
 }
+const BfPairDev *kfs_bf_device_table(const kfs_bf *b) { return b->d_pairs; }
 // Ratio test of every pair of the table: good_base[pair * good_stride ..], n_good[pair].
 kfs_status kfs_bf_launch_ratio_table(kfs_bf *b, const BfPairDev *d_table, int npairs, float ratio, kfs_dmatch *good_base, long long good_stride,
                                      int *n_good, cudaStream_t st)

@@ -56,5 +56,6 @@ kfs_status kfs_orb_finish_host_batch(kfs_orb *o, int batch, int *n_out);
 void kfs_orb_internal_streams(kfs_orb *o, cudaStream_t *s_in, cudaStream_t *s_out);
 void kfs_orb_internal_start_fence(kfs_orb *o, bool on);
 kfs_status kfs_bf_launch_table(kfs_bf *b, const BfPairDev *d_table, int npairs, int max_nq, int k, cudaStream_t st);
+const BfPairDev *kfs_bf_device_table(const kfs_bf *b); // device copy of the pair table of the last kfs_bf_knn_match_pairs_device
 kfs_status kfs_bf_launch_ratio_table(kfs_bf *b, const BfPairDev *d_table, int npairs, float ratio, kfs_dmatch *good_base, long long good_stride,
                                      int *n_good, cudaStream_t st);

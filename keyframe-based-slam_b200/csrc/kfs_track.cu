@@ -8,6 +8,7 @@
 #include "kfs_common.cuh"
 #include <new>
 #include <string.h>
+#include <vector>
 
 // ---- ExtractFeatures :25-28 ----------------------------------------------------------------------------------
 // cvtColor(rgb, rgb, RGB2BGR) then cvtColor(rgb, gray, BGR2GRAY): OpenCV's 8-bit path is the 15-bit fixed point
@@ -124,6 +125,14 @@ k_ratio_backproject(const TrackArgs A)
 }
 
 // ---- handle ------------------------------------------------------------------------------------------------------
+struct KfSlot { // one cached keyframe
+    uint8_t *desc = nullptr;
+    kfs_keypoint *kp = nullptr;
+    uint16_t *depth = nullptr;
+    size_t depth_elems = 0;
+    int n = -1, w = 0, h = 0;
+};
+
 struct kfs_frontend {
     int device = 0;
     kfs_orb *orb = nullptr;
@@ -140,12 +149,14 @@ struct kfs_frontend {
     int cur_n = -1, cur_w = 0, cur_h = 0;
     uint8_t *d_up_desc = nullptr;
     kfs_keypoint *d_up_kp = nullptr;
-    // keyframe cache (KeyFrame.hpp:35-39)
-    uint8_t *d_kf_desc = nullptr;
-    kfs_keypoint *d_kf_kp = nullptr;
-    uint16_t *d_kf_depth = nullptr;
-    size_t kf_depth_elems = 0;
-    int kf_n = -1, kf_w = 0, kf_h = 0;
+    // keyframe cache (KeyFrame.hpp:35-39): a ring of the last `window` keyframes (Map::GetNKeyFrames, Map.cpp:72-78);
+    // ring[head] is the newest one (Map::GetLastKeyFrame, Map.cpp:68-70)
+    std::vector<KfSlot> ring;
+    int window = 1, head = -1, count = 0;
+    // window-matching outputs: [window][cap][2] kNN rows, [window][cap] survivors, [window] counts
+    kfs_dmatch *d_wknn = nullptr, *d_wgood = nullptr;
+    int *d_wn = nullptr;
+    int *h_wn = nullptr; // pinned
     // match outputs
     kfs_dmatch *d_knn = nullptr, *d_good = nullptr;
     double *d_p3d = nullptr, *d_p2d = nullptr;
@@ -164,6 +175,57 @@ static kfs_status fe_reserve(uint8_t **p, size_t *have, size_t need)
     return KFS_OK;
 }
 
+static void fe_free_ring(kfs_frontend *fe)
+{
+    for (KfSlot &k : fe->ring) {
+        if (k.desc) cudaFree(k.desc);
+        if (k.kp) cudaFree(k.kp);
+        if (k.depth) cudaFree(k.depth);
+    }
+    fe->ring.clear();
+    if (fe->d_wknn) cudaFree(fe->d_wknn);
+    if (fe->d_wgood) cudaFree(fe->d_wgood);
+    if (fe->d_wn) cudaFree(fe->d_wn);
+    fe->d_wknn = fe->d_wgood = nullptr;
+    fe->d_wn = nullptr;
+    fe->head = -1;
+    fe->count = 0;
+}
+
+// (Re)builds the ring for `window` keyframes; every cached keyframe is dropped.
+static kfs_status fe_alloc_ring(kfs_frontend *fe, int window)
+{
+    fe_free_ring(fe);
+    fe->window = window;
+    fe->ring.resize((size_t)window);
+    const size_t n = (size_t)fe->cap;
+    cudaError_t e = cudaSuccess;
+    for (KfSlot &k : fe->ring) {
+        if (e == cudaSuccess) e = cudaMalloc(&k.desc, n * 32);
+        if (e == cudaSuccess) e = cudaMalloc(&k.kp, n * sizeof(kfs_keypoint));
+    }
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_wknn, (size_t)window * n * 2 * sizeof(kfs_dmatch));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_wgood, (size_t)window * n * sizeof(kfs_dmatch));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_wn, (size_t)window * sizeof(int));
+    if (e != cudaSuccess) {
+        fe_free_ring(fe);
+        fe->window = 0;
+        KFS_FAIL(KFS_ERR_CUDA, "keyframe ring of %d: %s", window, cudaGetErrorString(e));
+    }
+    return KFS_OK;
+}
+
+// Slot the next keyframe goes into (committed by fe_commit_slot once its uploads are enqueued).
+static KfSlot *fe_next_slot(kfs_frontend *fe) { return fe->window > 0 ? &fe->ring[(size_t)((fe->head + 1) % fe->window)] : nullptr; }
+static void fe_commit_slot(kfs_frontend *fe)
+{
+    fe->head = (fe->head + 1) % fe->window;
+    if (fe->count < fe->window) fe->count++;
+}
+static KfSlot *fe_newest(kfs_frontend *fe) { return fe->count > 0 ? &fe->ring[(size_t)fe->head] : nullptr; }
+// i-th keyframe of Map::GetNKeyFrames' order (0 = oldest held)
+static KfSlot *fe_window_slot(kfs_frontend *fe, int i) { return &fe->ring[(size_t)((fe->head - fe->count + 1 + i + 2 * fe->window) % fe->window)]; }
+
 extern "C" {
 
 void kfs_frontend_destroy(kfs_frontend *fe)
@@ -173,10 +235,11 @@ void kfs_frontend_destroy(kfs_frontend *fe)
     if (fe->stream) cudaStreamSynchronize(fe->stream);
     if (fe->bf) kfs_bf_destroy(fe->bf);
     if (fe->orb) kfs_orb_destroy(fe->orb);
-    void *bufs[] = {fe->d_img, fe->d_gray, fe->d_mask, fe->d_up_desc, fe->d_up_kp, fe->d_kf_desc, fe->d_kf_kp, fe->d_kf_depth,
-                    fe->d_knn, fe->d_good, fe->d_p3d, fe->d_p2d, fe->d_nout};
+    void *bufs[] = {fe->d_img, fe->d_gray, fe->d_mask, fe->d_up_desc, fe->d_up_kp, fe->d_knn, fe->d_good, fe->d_p3d, fe->d_p2d, fe->d_nout};
     for (void *b : bufs) if (b) cudaFree(b);
+    fe_free_ring(fe);
     if (fe->h_nout) cudaFreeHost(fe->h_nout);
+    if (fe->h_wn) cudaFreeHost(fe->h_wn);
     delete fe;
 }
 
@@ -198,18 +261,19 @@ kfs_status kfs_frontend_create(const kfs_orb_params *params, int device, kfs_fro
     cudaError_t e = cudaSuccess;
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_up_desc, n * 32);
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_up_kp, n * sizeof(kfs_keypoint));
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_kf_desc, n * 32);
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_kf_kp, n * sizeof(kfs_keypoint));
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_knn, n * 2 * sizeof(kfs_dmatch));
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_good, n * sizeof(kfs_dmatch));
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_p3d, n * 3 * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_p2d, n * 2 * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_nout, sizeof(int));
     if (e == cudaSuccess) e = cudaMallocHost(&fe->h_nout, sizeof(int));
+    if (e == cudaSuccess) e = cudaMallocHost(&fe->h_wn, KFS_MAX_WINDOW * sizeof(int));
     if (e != cudaSuccess) {
         kfs_frontend_destroy(fe);
         KFS_FAIL(KFS_ERR_CUDA, "kfs_frontend_create: %s", cudaGetErrorString(e));
     }
+    s = fe_alloc_ring(fe, 1);
+    if (s) { kfs_frontend_destroy(fe); return s; }
     *out = fe;
     return KFS_OK;
 }
@@ -266,17 +330,17 @@ kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t *image,
     return s;
 }
 
-static kfs_status fe_upload_depth(kfs_frontend *fe, const uint16_t *depth, size_t depth_step, int w, int h)
+static kfs_status fe_upload_depth(kfs_frontend *fe, KfSlot *k, const uint16_t *depth, size_t depth_step, int w, int h)
 {
     if (!depth || w <= 0 || h <= 0 || depth_step < (size_t)w * 2) KFS_FAIL(KFS_ERR_INVALID_ARG, "depth is NULL, empty or depth_step < 2*w");
     const size_t elems = (size_t)w * h;
-    if (elems > fe->kf_depth_elems) {
-        if (fe->d_kf_depth) { KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream)); cudaFree(fe->d_kf_depth); fe->d_kf_depth = nullptr; fe->kf_depth_elems = 0; }
-        KFS_CUDA_TRY(cudaMalloc(&fe->d_kf_depth, elems * 2));
-        fe->kf_depth_elems = elems;
+    if (elems > k->depth_elems) {
+        if (k->depth) { KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream)); cudaFree(k->depth); k->depth = nullptr; k->depth_elems = 0; }
+        KFS_CUDA_TRY(cudaMalloc(&k->depth, elems * 2));
+        k->depth_elems = elems;
     }
-    KFS_CUDA_TRY(cudaMemcpy2DAsync(fe->d_kf_depth, (size_t)w * 2, depth, depth_step, (size_t)w * 2, h, cudaMemcpyHostToDevice, fe->stream));
-    fe->kf_w = w; fe->kf_h = h;
+    KFS_CUDA_TRY(cudaMemcpy2DAsync(k->depth, (size_t)w * 2, depth, depth_step, (size_t)w * 2, h, cudaMemcpyHostToDevice, fe->stream));
+    k->w = w; k->h = h;
     return KFS_OK;
 }
 
@@ -285,13 +349,15 @@ kfs_status kfs_frontend_promote_keyframe(kfs_frontend *fe, const uint16_t *depth
     if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
     if (fe->cur_n < 0 || !fe->d_cur_desc) KFS_FAIL(KFS_ERR_INVALID_ARG, "promote_keyframe: no frame has been extracted on this handle yet");
     KfsDeviceGuard guard(fe->device);
-    kfs_status s = fe_upload_depth(fe, depth, depth_step, fe->cur_w, fe->cur_h);
+    KfSlot *k = fe_next_slot(fe);
+    kfs_status s = fe_upload_depth(fe, k, depth, depth_step, fe->cur_w, fe->cur_h);
     if (s) return s;
     if (fe->cur_n > 0) {
-        KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_kf_desc, fe->d_cur_desc, (size_t)fe->cur_n * 32, cudaMemcpyDeviceToDevice, fe->stream));
-        KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_kf_kp, fe->d_cur_kp, (size_t)fe->cur_n * sizeof(kfs_keypoint), cudaMemcpyDeviceToDevice, fe->stream));
+        KFS_CUDA_TRY(cudaMemcpyAsync(k->desc, fe->d_cur_desc, (size_t)fe->cur_n * 32, cudaMemcpyDeviceToDevice, fe->stream));
+        KFS_CUDA_TRY(cudaMemcpyAsync(k->kp, fe->d_cur_kp, (size_t)fe->cur_n * sizeof(kfs_keypoint), cudaMemcpyDeviceToDevice, fe->stream));
     }
-    fe->kf_n = fe->cur_n;
+    k->n = fe->cur_n;
+    fe_commit_slot(fe);
     return KFS_OK;
 }
 
@@ -302,14 +368,16 @@ kfs_status kfs_frontend_set_keyframe(kfs_frontend *fe, const uint8_t *desc, cons
     if (n < 0 || n > fe->cap) KFS_FAIL(KFS_ERR_CAPACITY, "set_keyframe: %d rows, handle capacity %d", n, fe->cap);
     if (n > 0 && (!desc || !kp)) KFS_FAIL(KFS_ERR_INVALID_ARG, "desc or kp is NULL");
     KfsDeviceGuard guard(fe->device);
-    kfs_status s = fe_upload_depth(fe, depth, depth_step, w, h);
+    KfSlot *k = fe_next_slot(fe);
+    kfs_status s = fe_upload_depth(fe, k, depth, depth_step, w, h);
     if (s) return s;
     if (n > 0) {
-        KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_kf_desc, desc, (size_t)n * 32, cudaMemcpyHostToDevice, fe->stream));
-        KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_kf_kp, kp, (size_t)n * sizeof(kfs_keypoint), cudaMemcpyHostToDevice, fe->stream));
+        KFS_CUDA_TRY(cudaMemcpyAsync(k->desc, desc, (size_t)n * 32, cudaMemcpyHostToDevice, fe->stream));
+        KFS_CUDA_TRY(cudaMemcpyAsync(k->kp, kp, (size_t)n * sizeof(kfs_keypoint), cudaMemcpyHostToDevice, fe->stream));
     }
     KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream)); // the caller may reuse its (pageable) buffers right away
-    fe->kf_n = n;
+    k->n = n;
+    fe_commit_slot(fe);
     return KFS_OK;
 }
 
@@ -320,7 +388,8 @@ kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc
 {
     if (!fe || !n_out || !intrinsics) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle, intrinsics or n_out is NULL");
     *n_out = 0;
-    if (fe->kf_n < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_features: no keyframe cached (promote_keyframe / set_keyframe first)");
+    KfSlot *kf = fe_newest(fe);
+    if (!kf) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_features: no keyframe cached (promote_keyframe / set_keyframe first)");
     if (capacity < 0 || (capacity > 0 && (!matches_out || !points3d_out || !points2d_out))) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers");
     if (intrinsics[0] == 0.0 || intrinsics[1] == 0.0) KFS_FAIL(KFS_ERR_INVALID_ARG, "fx or fy is zero");
     KfsDeviceGuard guard(fe->device);
@@ -342,21 +411,21 @@ kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc
         d_kp = fe->d_cur_kp; d_desc = fe->d_cur_desc; d_cnt = fe->d_cur_count; nt = fe->cur_n;
     }
     fe->launches = 0;
-    if (fe->kf_n == 0) return KFS_OK; // knnMatch of an empty query: no rows
+    if (kf->n == 0) return KFS_OK; // knnMatch of an empty query: no rows
     // the reference indexes knnMatches[i][1] unguarded (:46): with fewer than 2 current keypoints it is undefined there;
     // here such rows simply never pass
     kfs_bf_pair pair;
-    pair.query = fe->d_kf_desc; pair.nq = fe->kf_n; pair.d_nq = nullptr;
+    pair.query = kf->desc; pair.nq = kf->n; pair.d_nq = nullptr;
     pair.train = d_desc; pair.nt = nt; pair.d_nt = nullptr;
     pair.out = fe->d_knn; pair.counts = nullptr;
     kfs_status s = kfs_bf_knn_match_pairs_device(fe->bf, &pair, 1, 2);
     if (s) return s;
     fe->launches += kfs_bf_last_launches(fe->bf) > 0 ? 1 : 0;
     TrackArgs A;
-    A.knn = fe->d_knn; A.kf_kp = fe->d_kf_kp; A.cur_kp = d_kp; A.d_ncur = d_cnt;
-    A.depth = fe->d_kf_depth; A.depth_pitch = fe->kf_w; A.depth_w = fe->kf_w; A.depth_h = fe->kf_h;
+    A.knn = fe->d_knn; A.kf_kp = kf->kp; A.cur_kp = d_kp; A.d_ncur = d_cnt;
+    A.depth = kf->depth; A.depth_pitch = kf->w; A.depth_w = kf->w; A.depth_h = kf->h;
     A.fx = intrinsics[0]; A.fy = intrinsics[1]; A.cx = intrinsics[2]; A.cy = intrinsics[3];
-    A.ratio = ratio; A.nq = fe->kf_n; A.n_cur = nt;
+    A.ratio = ratio; A.nq = kf->n; A.n_cur = nt;
     A.capacity = capacity < fe->cap ? capacity : fe->cap;
     A.matches = fe->d_good; A.p3d = fe->d_p3d; A.p2d = fe->d_p2d; A.n_out = fe->d_nout;
     k_ratio_backproject<<<1, 1024, 0, st>>>(A);
@@ -375,6 +444,88 @@ kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc
         KFS_CUDA_TRY(cudaStreamSynchronize(st));
     }
     if (n > capacity) KFS_FAIL(KFS_ERR_CAPACITY, "match_features: %d survivors, output capacity %d", n, capacity);
+    return KFS_OK;
+}
+
+// ---- keyframe window: Map::GetNKeyFrames (Map.cpp:72-78) -----------------------------------------------------------
+kfs_status kfs_frontend_set_window(kfs_frontend *fe, int window)
+{
+    if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
+    if (window < 1 || window > KFS_MAX_WINDOW) KFS_FAIL(KFS_ERR_INVALID_ARG, "set_window: %d not in [1, %d]", window, KFS_MAX_WINDOW);
+    KfsDeviceGuard guard(fe->device);
+    KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream));
+    return fe_alloc_ring(fe, window);
+}
+int kfs_frontend_window(const kfs_frontend *fe) { return fe ? fe->window : 0; }
+int kfs_frontend_window_count(const kfs_frontend *fe) { return fe ? fe->count : 0; }
+
+kfs_status kfs_frontend_match_window(kfs_frontend *fe, const uint8_t *cur_desc, int n_cur, float ratio,
+                                     int *kf_rows_out, kfs_dmatch *knn_out, int knn_rows,
+                                     kfs_dmatch *good_out, int *n_good_out, int capacity, int *n_kf_out)
+{
+    if (!fe || !n_kf_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle or n_kf_out is NULL");
+    *n_kf_out = 0;
+    if (capacity < 0 || knn_rows < 0 || (capacity > 0 && !good_out) || !n_good_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_window: output buffers");
+    KfsDeviceGuard guard(fe->device);
+    cudaStream_t st = fe->stream;
+    const uint8_t *d_desc;
+    const int *d_cnt = nullptr;
+    int nt;
+    if (cur_desc) {
+        if (n_cur < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_window: n_cur < 0");
+        if (n_cur > fe->cap) KFS_FAIL(KFS_ERR_CAPACITY, "match_window: %d current rows, handle capacity %d", n_cur, fe->cap);
+        if (n_cur > 0) KFS_CUDA_TRY(cudaMemcpyAsync(fe->d_up_desc, cur_desc, (size_t)n_cur * 32, cudaMemcpyHostToDevice, st));
+        d_desc = fe->d_up_desc; nt = n_cur;
+    } else {
+        if (fe->cur_n < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_window: no current frame on the device (extract_features first)");
+        d_desc = fe->d_cur_desc; d_cnt = fe->d_cur_count; nt = fe->cur_n;
+    }
+    fe->launches = 0;
+    const int nkf = fe->count;
+    *n_kf_out = nkf;
+    if (nkf == 0) return KFS_OK;
+    const size_t cap = (size_t)fe->cap;
+    kfs_bf_pair pairs[KFS_MAX_WINDOW];
+    int max_rows = 0;
+    for (int i = 0; i < nkf; i++) {
+        const KfSlot *k = fe_window_slot(fe, i);
+        pairs[i].query = k->desc; pairs[i].nq = k->n; pairs[i].d_nq = nullptr;
+        pairs[i].train = d_desc; pairs[i].nt = nt; pairs[i].d_nt = d_cnt;
+        pairs[i].out = fe->d_wknn + (size_t)i * cap * 2; pairs[i].counts = nullptr;
+        if (kf_rows_out) kf_rows_out[i] = k->n;
+        n_good_out[i] = 0;
+        max_rows = k->n > max_rows ? k->n : max_rows;
+    }
+    if (max_rows == 0) return KFS_OK; // every keyframe is empty: knnMatch of an empty query has no rows
+    kfs_status s = kfs_bf_knn_match_pairs_device(fe->bf, pairs, nkf, 2);
+    if (s) return s;
+    fe->launches += kfs_bf_last_launches(fe->bf);
+    s = kfs_bf_launch_ratio_table(fe->bf, kfs_bf_device_table(fe->bf), nkf, ratio, fe->d_wgood, (long long)cap, fe->d_wn, st);
+    if (s) return s;
+    fe->launches++;
+    KFS_CUDA_TRY(cudaMemcpyAsync(fe->h_wn, fe->d_wn, (size_t)nkf * sizeof(int), cudaMemcpyDeviceToHost, st));
+    bool truncated = false;
+    if (knn_out && knn_rows > 0) {
+        const int rows = max_rows < knn_rows ? max_rows : knn_rows;
+        truncated |= max_rows > knn_rows;
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(knn_out, (size_t)knn_rows * 2 * sizeof(kfs_dmatch), fe->d_wknn, cap * 2 * sizeof(kfs_dmatch),
+                                       (size_t)rows * 2 * sizeof(kfs_dmatch), (size_t)nkf, cudaMemcpyDeviceToHost, st));
+    }
+    KFS_CUDA_TRY(cudaStreamSynchronize(st));
+    int max_good = 0;
+    for (int i = 0; i < nkf; i++) {
+        n_good_out[i] = fe->h_wn[i];
+        max_good = fe->h_wn[i] > max_good ? fe->h_wn[i] : max_good;
+    }
+    truncated |= max_good > capacity;
+    const int m = max_good < capacity ? max_good : capacity;
+    if (m > 0) {
+        KFS_CUDA_TRY(cudaMemcpy2DAsync(good_out, (size_t)capacity * sizeof(kfs_dmatch), fe->d_wgood, cap * sizeof(kfs_dmatch),
+                                       (size_t)m * sizeof(kfs_dmatch), (size_t)nkf, cudaMemcpyDeviceToHost, st));
+        KFS_CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    if (truncated) KFS_FAIL(KFS_ERR_CAPACITY, "match_window: outputs truncated (max keyframe rows %d vs knn_rows %d, max survivors %d vs capacity %d)",
+                            max_rows, knn_rows, max_good, capacity);
     return KFS_OK;
 }
 

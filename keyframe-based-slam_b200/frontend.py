@@ -377,3 +377,37 @@ class TrackerFrontEnd:
         N.check(N.lib().kfs_frontend_match_features(self._h, _ptr(dpCurrImg), _ptr(kpCurrImg), 0 if dpCurrImg is None else len(dpCurrImg),
                                                     intr, ratio, m.ctypes.data, p3.ctypes.data, p2.ctypes.data, cap, C.byref(n)))
         return p3[:n.value].copy(), p2[:n.value].copy(), m[:n.value].copy()
+
+    # ---- keyframe window (Map::GetNKeyFrames, /root/reference/src/lib/Map.cpp:72-78) ----
+    def setWindow(self, window):
+        """Keep the last `window` keyframes on the device (drops the cached ones)."""
+        N.check(N.lib().kfs_frontend_set_window(self._h, window))
+
+    @property
+    def window(self):
+        return N.lib().kfs_frontend_window(self._h)
+
+    @property
+    def windowCount(self):
+        return N.lib().kfs_frontend_window_count(self._h)
+
+    def matchWindow(self, dpCurrImg=None, ratio=0.6, want_knn=False):
+        """Current frame against every cached keyframe, oldest first (GetNKeyFrames' order), one kNN launch.
+        -> list of per-keyframe survivor arrays (DM_DTYPE, query = keyframe row, train = current row); with want_knn also
+        the raw kNN rows [rows_i, 2] per keyframe."""
+        cap = self.capacity
+        W = N.KFS_MAX_WINDOW
+        rows = (C.c_int * W)()
+        ngood = (C.c_int * W)()
+        nkf = C.c_int()
+        cnt = self.windowCount
+        good = np.zeros((max(cnt, 1), cap), DM_DTYPE)
+        knn = np.zeros((max(cnt, 1), cap, 2), DM_DTYPE) if want_knn else None
+        if dpCurrImg is not None:
+            dpCurrImg = np.ascontiguousarray(dpCurrImg, dtype=np.uint8).reshape(-1, 32)
+        N.check(N.lib().kfs_frontend_match_window(self._h, _ptr(dpCurrImg), 0 if dpCurrImg is None else len(dpCurrImg), ratio,
+                                                  rows, _ptr(knn), cap if want_knn else 0, good.ctypes.data, ngood, cap, C.byref(nkf)))
+        out = [good[i, :ngood[i]].copy() for i in range(nkf.value)]
+        if want_knn:
+            return out, [knn[i, :rows[i]].copy() for i in range(nkf.value)]
+        return out

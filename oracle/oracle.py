@@ -62,6 +62,9 @@ def lib():
         L.kfo_match_features.restype = C.c_int
         L.kfo_match_features.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_double), C.c_float,
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.kfo_match_window.restype = C.c_int
+        L.kfo_match_window.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int, C.c_int, u8p, C.c_int, C.c_float,
+                                       C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int]
         _LIB = L
     return _LIB
 
@@ -210,3 +213,24 @@ def match_features(knn, kf_kp, cur_kp, depth, K, ratio=0.6):
     n = lib().kfo_match_features(knn.ctypes.data, nq, kf_kp.ctypes.data, cur_kp.ctypes.data, depth.ctypes.data, depth.strides[0], intr, ratio,
                                  m.ctypes.data, p3.ctypes.data, p2.ctypes.data, nq)
     return p3[:n].copy(), p2[:n].copy(), m[:n].copy()
+
+
+def match_window(kf_descs, cur_desc, win, ratio=0.6):
+    """Map::GetNKeyFrames(win) (Map.cpp:72-78) x knnMatch (:39) x ratio test (:46): kf_descs = descriptors of every keyframe
+    of the map in creation order -> (list of k=2 rows per window keyframe, list of survivor arrays), oldest first."""
+    kfs = [np.ascontiguousarray(d, dtype=np.uint8).reshape(-1, 32) for d in kf_descs]
+    cur = np.ascontiguousarray(cur_desc, dtype=np.uint8).reshape(-1, 32)
+    n = len(kfs)
+    stride = max([len(d) for d in kfs] + [1])
+    ptrs = (C.c_void_p * max(n, 1))(*[d.ctypes.data for d in kfs])
+    rows = (C.c_int * max(n, 1))(*[len(d) for d in kfs])
+    nw = min(n, win)
+    knn = np.zeros((max(nw, 1), stride, 2), DM_DTYPE)
+    good = np.zeros((max(nw, 1), stride), DM_DTYPE)
+    ngood = (C.c_int * max(nw, 1))()
+    scratch = (C.c_int * stride)()
+    got = lib().kfo_match_window(ptrs, rows, n, win, _u8(cur), len(cur), ratio, knn.ctypes.data, good.ctypes.data, ngood, scratch, stride)
+    if got < 0:
+        raise ValueError("bad kNN arguments")
+    first = n - got
+    return [knn[i, :len(kfs[first + i])].copy() for i in range(got)], [good[i, :ngood[i]].copy() for i in range(got)]

@@ -10,6 +10,10 @@
  *                       this part is pinned by construction only: the same C float / double expressions, in the same
  *                       order, compiled with -ffp-contract=off ("parity unpinned" for lines 52-57; the kNN rows that
  *                       feed it are pinned against cv2 by knn_oracle.c's goldens).
+ *   kfo_match_window    /root/reference/src/lib/Map.cpp:72-78 (Map::GetNKeyFrames: the last `win` keyframes, oldest first,
+ *                       or all of them while fewer exist) composed with VisualOdometry.cpp:39 (knnMatch(keyframe, current,
+ *                       2)) and :46 (ratio test) per keyframe — the (frame, keyframe) pairs of BASELINE.json configs 4/5.
+ *                       Pinned against cv2 4.13 by tests/golden/window_cfg4.npz (tools/make_golden_window.py).
  */
 #include <math.h>
 #include <stddef.h>
@@ -61,4 +65,25 @@ int kfo_match_features(const kfo_dmatch *knn, int nq, const kfo_keypoint *kf_kp,
         }
     }
     return n;
+}
+
+/* knn_oracle.c */
+int kfo_knn_match(const uint8_t *query, int nq, const uint8_t *train, int nt, int desc_bytes, int k, kfo_dmatch *out, int *counts);
+int kfo_ratio_test(const kfo_dmatch *knn, const int *counts, int nq, int k, float ratio, kfo_dmatch *good);
+
+/* Map.cpp:72-78 + VisualOdometry.cpp:39,46.  kf_desc[j] / kf_rows[j]: descriptors of ALL n_kf keyframes of the map in
+ * creation order (Map::vecKeyFrames); the window is its last `win` entries (all of them if n_kf < win).  For window entry i
+ * (0 = oldest): knn_out + i*row_stride*2 receives the k=2 rows, good_out + i*row_stride the survivors, n_good[i] their count;
+ * counts_scratch holds row_stride ints.  Returns the number of keyframes in the window, or -1 on bad kNN arguments. */
+int kfo_match_window(const uint8_t *const *kf_desc, const int *kf_rows, int n_kf, int win, const uint8_t *cur_desc, int n_cur, float ratio,
+                     kfo_dmatch *knn_out, kfo_dmatch *good_out, int *n_good, int *counts_scratch, int row_stride)
+{
+    const int first = n_kf >= win ? n_kf - win : 0;                                        /* Map.cpp:73-77 */
+    int w = 0;
+    for (int j = first; j < n_kf; j++, w++) {
+        kfo_dmatch *knn = knn_out + (size_t)w * row_stride * 2;
+        if (kfo_knn_match(kf_desc[j], kf_rows[j], cur_desc, n_cur, 32, 2, knn, counts_scratch)) return -1;   /* :39 */
+        n_good[w] = kfo_ratio_test(knn, counts_scratch, kf_rows[j], 2, ratio, good_out + (size_t)w * row_stride);   /* :46 */
+    }
+    return w;
 }

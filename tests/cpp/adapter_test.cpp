@@ -38,6 +38,7 @@ int main(int argc, char **argv)
         if (std::sscanf(argv[9], "%lf,%lf,%lf,%lf", &k[0], &k[1], &k[2], &k[3]) != 4) return 66;
         cv::Ptr<kfs::TrackerFrontEnd> fe = kfs::TrackerFrontEnd::create(nf);
         fe->setIntrinsics(k[0], k[1], k[2], k[3]);
+        fe->SetWindow(5);                                                    // Optimizers.hpp:70
         cv::Mat rgbA(h, w, cv::CV_8UC3, a.data()), rgbB(h, w, cv::CV_8UC3, b.data()), depth(h, w, cv::CV_16UC1, dep.data()), mask;
         auto fa = fe->ExtractFeatures(rgbA, mask);
         fe->PromoteKeyFrame(depth);
@@ -46,7 +47,13 @@ int main(int argc, char **argv)
         auto pts = fe->MatchFeatures(fb.second, fb.first, matches);          // host rows, like the reference passes them
         std::vector<cv::DMatch> matches2;
         auto pts2 = fe->MatchFeatures(cv::Mat(), {}, matches2);              // device-resident current frame
-        const bool same = matches.size() == matches2.size() && pts.first.size() == pts2.first.size() &&
+        // keyframe window (Map::GetNKeyFrames): with one keyframe cached the window's only list is MatchFeatures' list
+        auto win = fe->MatchWindow(cv::Mat());
+        auto win2 = fe->MatchWindow(fb.second);
+        const bool win_ok = fe->WindowCount() == 1 && win.size() == 1 && win2.size() == 1 && win[0].size() == matches.size() &&
+                            win2[0].size() == matches.size() && !std::memcmp(win[0].data(), matches.data(), matches.size() * sizeof(cv::DMatch)) &&
+                            !std::memcmp(win2[0].data(), matches.data(), matches.size() * sizeof(cv::DMatch));
+        const bool same = win_ok && matches.size() == matches2.size() && pts.first.size() == pts2.first.size() &&
                           !std::memcmp(pts.first.data(), pts2.first.data(), pts.first.size() * sizeof(cv::Point3d)) &&
                           !std::memcmp(matches.data(), matches2.data(), matches.size() * sizeof(cv::DMatch));
         std::ofstream o(argv[8], std::ios::binary);
