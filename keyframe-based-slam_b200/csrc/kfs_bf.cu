@@ -52,6 +52,14 @@ __device__ __forceinline__ uint32_t bf_maj(uint32_t a, uint32_t b, uint32_t c)
     return r;
 }
 
+// carry of a full adder from two addends and the SUM: maj(a, b, a ^ b ^ s)
+__device__ __forceinline__ uint32_t bf_carry(uint32_t a, uint32_t b, uint32_t s)
+{
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xd4;" : "=r"(r) : "r"(a), "r"(b), "r"(s));
+    return r;
+}
+
 __device__ __forceinline__ void bf_top2_insert(uint32_t key, uint32_t &b1, uint32_t &b2)
 {
     const uint32_t hi = max(key, b1);
@@ -77,7 +85,8 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int qgroup = warp % BF_QWARPS, tsplit = warp / BF_QWARPS;
 
-    // query descriptors -> registers (clamped index for the ragged tail; results of clamped rows are dropped)
+    // query descriptors -> registers (clamped index for the ragged tail; results of clamped rows are dropped).
+    // Kept per query: words 0, 1, 3, 4, 7 and the three XOR-linear combinations the carry-save sums need (see the loop).
     uint32_t q[BF_QPT][8];
     uint32_t b1[BF_QPT], b2[BF_QPT];
 #pragma unroll
@@ -85,8 +94,10 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
         const int qi = min(q0 + qgroup * (32 * BF_QPT) + r * 32 + lane, nq - 1);
         const uint4 *src = reinterpret_cast<const uint4 *>(P.query + (size_t)qi * 32);
         const uint4 a = __ldg(src), b = __ldg(src + 1);
-        q[r][0] = a.x; q[r][1] = a.y; q[r][2] = a.z; q[r][3] = a.w;
-        q[r][4] = b.x; q[r][5] = b.y; q[r][6] = b.z; q[r][7] = b.w;
+        q[r][0] = a.x; q[r][1] = a.y; q[r][3] = a.w; q[r][4] = b.x; q[r][7] = b.w;
+        q[r][2] = bf_xor3(a.x, a.y, a.z);            // Q012
+        q[r][5] = bf_xor3(a.w, b.x, b.y);            // Q345
+        q[r][6] = bf_xor3(q[r][2], q[r][5], b.z);    // Q0..6
         b1[r] = BF_INF; b2[r] = BF_INF;
     }
 
@@ -115,17 +126,21 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
         for (int j = 0; j < rows; j++) {
             const uint4 ta = tp[2 * j], tb = tp[2 * j + 1];
             const uint32_t tkey = (uint32_t)(base + j);
+            // XOR-linear combinations of the train row, shared by this thread's BF_QPT queries
+            const uint32_t t012 = bf_xor3(ta.x, ta.y, ta.z), t345 = bf_xor3(ta.w, tb.x, tb.y), t06 = bf_xor3(t012, t345, tb.z);
 #pragma unroll
             for (int r = 0; r < BF_QPT; r++) {
-                // 256-bit Hamming distance with a carry-save (Harley-Seal) front end: 8 XOR words are compressed by
-                // three full adders (2 LOP3 each, ALU pipe) so that only 5 POPC (XU pipe, 16/clk/SM) are needed:
+                // 256-bit Hamming distance with a carry-save (Harley-Seal) front end: the 8 XOR words x_i = q_i ^ t_i are
+                // compressed by three full adders so that only 5 POPC are needed:
                 //   x0+x1+x2 = s0 + 2 c0;  x3+x4+x5 = s1 + 2 c1;  s0+s1+x6 = s2 + 2 c2
                 //   popc(all) = popc(s2) + popc(x7) + 2 (popc(c0) + popc(c1) + popc(c2))
-                const uint32_t x0 = q[r][0] ^ ta.x, x1 = q[r][1] ^ ta.y, x2 = q[r][2] ^ ta.z, x3 = q[r][3] ^ ta.w;
-                const uint32_t x4 = q[r][4] ^ tb.x, x5 = q[r][5] ^ tb.y, x6 = q[r][6] ^ tb.z, x7 = q[r][7] ^ tb.w;
-                const uint32_t s0 = bf_xor3(x0, x1, x2), c0 = bf_maj(x0, x1, x2);
-                const uint32_t s1 = bf_xor3(x3, x4, x5), c1 = bf_maj(x3, x4, x5);
-                const uint32_t s2 = bf_xor3(s0, s1, x6), c2 = bf_maj(s0, s1, x6);
+                // The SUM words are XOR-linear, so each is ONE xor of a precombined query word and a precombined train word
+                // (s0 = Q012 ^ T012, s1 = Q345 ^ T345, s2 = Q0..6 ^ T0..6), and a CARRY is a 3-input function of two addends
+                // and the sum (the third addend is their xor): c = maj(a, b, a^b^s) = LOP3 0xd4.  x2, x5, x6 are never
+                // formed: 11 LOP3 + 5 POPC per compare (+ 3 LOP3 per train row per thread) instead of 14 + 5.
+                const uint32_t s0 = q[r][2] ^ t012, s1 = q[r][5] ^ t345, s2 = q[r][6] ^ t06;
+                const uint32_t x0 = q[r][0] ^ ta.x, x1 = q[r][1] ^ ta.y, x3 = q[r][3] ^ ta.w, x4 = q[r][4] ^ tb.x, x7 = q[r][7] ^ tb.w;
+                const uint32_t c0 = bf_carry(x0, x1, s0), c1 = bf_carry(x3, x4, s1), c2 = bf_carry(s0, s1, s2);
                 const uint32_t ones = __popc(s2) + __popc(x7);
                 const uint32_t twos = __popc(c0) + __popc(c1) + __popc(c2);
                 const uint32_t d = ones + 2u * twos;

@@ -185,7 +185,7 @@ k_mask_binarise(const uint8_t *__restrict__ src, long long sfs, long long sstep,
 // phase 3: 3x3 NMS on the score tile, border/mask predicate; survivors are gathered in shared memory and
 //          appended to the (frame, level) list with ONE global atomic per tile
 constexpr int FT_W = 112, FT_H = 62;
-constexpr int FS_P = 128, FS_H = FT_H + 8;
+constexpr int FS_ROWB = 128, FS_P = 144, FS_H = FT_H + 8; // rows 144 B apart: vertically adjacent pixels sit 4 banks apart (byte gathers of phase 2)
 constexpr int SC_W = 128, SC_H = FT_H + 2;
 constexpr int FAST_X0 = 20; // interior x origin of tile column 0; source origin 16 (+112k) keeps rows 16B-aligned
 constexpr int FAST_THREADS = 256;
@@ -208,7 +208,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     __shared__ uint16_t s_q[SC_W * SC_H];
     __shared__ __align__(16) uint32_t s_mask[SC_H * 4];
     __shared__ int s_wsum[FAST_THREADS / 32];
-    __shared__ int s_nout, s_gbase;
+    __shared__ int s_nout, s_gbase, s_ncorner;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int f = blockIdx.y + g.frame0;
@@ -222,7 +222,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     const int thr = g.fast_thr;
 
     // ---- load the source tile (uint4 per thread), clear the score tile and the mask rows
-    for (int i = tid; i < FS_H * (FS_P / 16); i += FAST_THREADS) {
+    for (int i = tid; i < FS_H * (FS_ROWB / 16); i += FAST_THREADS) {
         const int r = i >> 3, c = i & 7;
         const int gy = min(max(sy0 + r, 0), H - 1), gx = ox + 16 * c;
         uint4 v = make_uint4(0, 0, 0, 0);
@@ -231,7 +231,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     }
     for (int i = tid; i < SC_W * SC_H / 16; i += FAST_THREADS) reinterpret_cast<uint4 *>(s_sc)[i] = make_uint4(0, 0, 0, 0);
     s_mask[tid] = 0;
-    if (tid == 0) s_nout = 0;
+    if (tid == 0) { s_nout = 0; s_ncorner = 0; }
     __syncthreads();
 
     // ---- phase 1: quick reject, one score row per warp-iteration, 4 pixels per lane
@@ -298,35 +298,57 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     }
     __syncthreads();
 
-    // ---- phase 2: exact score of queued pixels
-    for (int e = tid; e < nq; e += FAST_THREADS) {
-        const int pi = s_q[e];
-        const int sy = pi >> 7, sx = pi & (SC_W - 1);
-        const uint8_t *c = s_src + (sy + 3) * FS_P + sx;
-        const uint32_t cv = kfs_fast_cv(c[0]);
-        uint32_t ek[16];
-        ek[0] = kfs_fast_e(cv, c[3 * FS_P + 0]);   ek[1] = kfs_fast_e(cv, c[3 * FS_P + 1]);
-        ek[2] = kfs_fast_e(cv, c[2 * FS_P + 2]);   ek[3] = kfs_fast_e(cv, c[1 * FS_P + 3]);
-        ek[4] = kfs_fast_e(cv, c[3]);              ek[5] = kfs_fast_e(cv, c[-1 * FS_P + 3]);
-        ek[6] = kfs_fast_e(cv, c[-2 * FS_P + 2]);  ek[7] = kfs_fast_e(cv, c[-3 * FS_P + 1]);
-        ek[8] = kfs_fast_e(cv, c[-3 * FS_P + 0]);  ek[9] = kfs_fast_e(cv, c[-3 * FS_P - 1]);
-        ek[10] = kfs_fast_e(cv, c[-2 * FS_P - 2]); ek[11] = kfs_fast_e(cv, c[-1 * FS_P - 3]);
-        ek[12] = kfs_fast_e(cv, c[-3]);            ek[13] = kfs_fast_e(cv, c[1 * FS_P - 3]);
-        ek[14] = kfs_fast_e(cv, c[2 * FS_P - 2]);  ek[15] = kfs_fast_e(cv, c[3 * FS_P - 1]);
-        const int m = kfs_fast9_m(ek);
-        if (m > thr) s_sc[pi] = (uint8_t)(m - 1);
+    // ---- phase 2: exact score of queued pixels; the corners among them (about half) are appended to a second queue
+    //      (upper half of s_q; warp-aggregated shared atomic: the order inside a tile is free, the lists are re-ordered
+    //      by k_select_sort) so that phase 3 walks corners only.  Tiles with more than half of their pixels queued keep
+    //      the full queue for phase 3.
+    constexpr int CQ_OFF = SC_W * SC_H / 2;
+    const bool compact = nq <= CQ_OFF;
+    for (int e0 = 0; e0 < nq; e0 += FAST_THREADS) {
+        const int e = e0 + tid;
+        bool corner = false;
+        int pi = 0;
+        if (e < nq) {
+            pi = s_q[e];
+            const int sy = pi >> 7, sx = pi & (SC_W - 1);
+            const uint8_t *c = s_src + (sy + 3) * FS_P + sx;
+            const uint32_t cv = kfs_fast_cv(c[0]);
+            uint32_t ek[16];
+            ek[0] = kfs_fast_e(cv, c[3 * FS_P + 0]);   ek[1] = kfs_fast_e(cv, c[3 * FS_P + 1]);
+            ek[2] = kfs_fast_e(cv, c[2 * FS_P + 2]);   ek[3] = kfs_fast_e(cv, c[1 * FS_P + 3]);
+            ek[4] = kfs_fast_e(cv, c[3]);              ek[5] = kfs_fast_e(cv, c[-1 * FS_P + 3]);
+            ek[6] = kfs_fast_e(cv, c[-2 * FS_P + 2]);  ek[7] = kfs_fast_e(cv, c[-3 * FS_P + 1]);
+            ek[8] = kfs_fast_e(cv, c[-3 * FS_P + 0]);  ek[9] = kfs_fast_e(cv, c[-3 * FS_P - 1]);
+            ek[10] = kfs_fast_e(cv, c[-2 * FS_P - 2]); ek[11] = kfs_fast_e(cv, c[-1 * FS_P - 3]);
+            ek[12] = kfs_fast_e(cv, c[-3]);            ek[13] = kfs_fast_e(cv, c[1 * FS_P - 3]);
+            ek[14] = kfs_fast_e(cv, c[2 * FS_P - 2]);  ek[15] = kfs_fast_e(cv, c[3 * FS_P - 1]);
+            const int m = kfs_fast9_m(ek);
+            corner = m > thr;
+            if (corner) s_sc[pi] = (uint8_t)(m - 1);
+        }
+        if (compact) {
+            const uint32_t bc = __ballot_sync(0xffffffffu, corner);
+            if (bc) {
+                int base = 0;
+                if (lane == 0) base = kfs_atoms_add(&s_ncorner, __popc(bc));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (corner) s_q[CQ_OFF + base + __popc(bc & ((1u << lane) - 1u))] = (uint16_t)pi;
+            }
+        }
     }
     __syncthreads();
 
     // ---- phase 3: NMS + border/mask filter -> survivor list in shared memory (aliases the source tile)
     const uint8_t *mask = L.mask ? L.mask + (long long)f * L.mask_fs : nullptr;
     uint32_t *s_out = reinterpret_cast<uint32_t *>(s_src);
-    for (int e0 = 0; e0 < nq; e0 += FAST_THREADS) {
+    const uint16_t *s_list = compact ? s_q + CQ_OFF : s_q;
+    const int nlist = compact ? s_ncorner : nq;
+    for (int e0 = 0; e0 < nlist; e0 += FAST_THREADS) {
         const int e = e0 + tid;
         uint32_t packed = 0;
         bool keep = false;
-        if (e < nq) {
-            const int pi = s_q[e];
+        if (e < nlist) {
+            const int pi = s_list[e];
             const int s = s_sc[pi];
             const int sy = pi >> 7, sx = pi & (SC_W - 1);
             const int x = ox + sx, y = ty0 - 1 + sy;
