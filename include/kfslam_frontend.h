@@ -196,9 +196,10 @@ KFS_API int kfs_bf_last_launches(const kfs_bf *bf);
  * (:138 -> detectAndCompute :30), MatchFeatures against the last keyframe (:144 -> knnMatch :39, query = keyframe
  * descriptors, train = current frame) and the ratio test (:46).  Frames come from host memory; descriptors stay on
  * the device between extraction and matching, keyframes of earlier batches live in a device-resident cache
- * (KeyFrame::matDescriptors, KeyFrame.hpp:39), and two arenas double-buffer the batches: kfs_replay_submit only
+ * (KeyFrame::matDescriptors, KeyFrame.hpp:39), and three arenas (kfs_replay_arenas) rotate over the batches: kfs_replay_submit only
  * enqueues (H2D, kernels, D2H are stream-ordered), kfs_replay_wait blocks until that batch's results are in the
- * host buffers.  At most two batches are in flight; submitting a third first completes the oldest.
+ * host buffers.  At most kfs_replay_arenas() = 3 batches are in flight (upload | kernels | download); submitting one more first
+ * completes the oldest.
  * Use pinned host buffers (cudaHostAlloc / cudaHostRegister) for the copies to overlap with the kernels. */
 typedef struct kfs_replay kfs_replay;
 typedef struct kfs_replay_params {
@@ -227,6 +228,7 @@ KFS_API void kfs_replay_default_params(kfs_replay_params *p); /* ORB defaults, m
 KFS_API kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_replay **out);
 KFS_API void kfs_replay_destroy(kfs_replay *r);
 KFS_API int kfs_replay_capacity(const kfs_replay *r);           /* per-frame capacity the outputs should have */
+KFS_API int kfs_replay_arenas(const kfs_replay *r);             /* batches that can be in flight (submitted, not yet waited for) */
 KFS_API kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_replay_frame *plan, int batch, int *ticket);
 KFS_API kfs_status kfs_replay_wait(kfs_replay *r, int ticket);
 KFS_API int kfs_replay_last_launches(const kfs_replay *r);      /* kernels launched by the last submit */

@@ -96,6 +96,7 @@ SIGNATURES = {
     "kfs_replay_submit": (_i, [_vp, C.POINTER(ReplayIO), C.POINTER(ReplayFrame), _i, _ip]),
     "kfs_replay_wait": (_i, [_vp, _i]),
     "kfs_replay_last_launches": (_i, [_vp]),
+    "kfs_replay_arenas": (_i, [_vp]),
     "kfs_frontend_create": (_i, [C.POINTER(OrbParams), _i, C.POINTER(_vp)]),
     "kfs_frontend_destroy": (None, [_vp]),
     "kfs_frontend_capacity": (_i, [_vp]),

@@ -5,7 +5,8 @@
 // descriptors, train = current frame) -> ratio test (:46).  The reference does this one frame at a time through
 // host memory; here a batch of frames goes through
 //     H2D (chunked) | ORB kernel chain | Hamming kNN on the DEVICE-RESIDENT descriptors | ratio compaction | D2H
-// with two arenas (double buffering): batch i+1 is uploaded while batch i is still being matched and downloaded.
+// with three arenas: batch i+2 is uploaded while batch i+1 runs its kernels and batch i is downloaded (with two, an arena's
+// upload -> kernels -> download cycle is twice the batch period as soon as upload and kernels take equally long).
 // Keyframe descriptors never travel back to the device: a keyframe is either a frame of the same batch or an
 // entry of the device-resident keyframe cache (KeyFrame::matDescriptors, KeyFrame.hpp:39).
 // No host threads: everything is stream-ordered; kfs_replay_submit only enqueues, kfs_replay_wait blocks.
@@ -14,6 +15,8 @@
 #include <limits.h>
 #include <vector>
 #include <new>
+
+constexpr int RP_ARENAS = 3; // batches in flight: one uploading, one in the kernels, one downloading
 
 struct ReplaySlot {
     bool in_flight = false;
@@ -30,10 +33,10 @@ struct ReplaySlot {
 struct kfs_replay {
     kfs_replay_params p;
     int device = 0;
-    kfs_orb *orb[2] = {nullptr, nullptr};
+    kfs_orb *orb[RP_ARENAS] = {};
     kfs_bf *bf = nullptr;
     cudaStream_t compute = nullptr;
-    ReplaySlot slot[2];
+    ReplaySlot slot[RP_ARENAS];
     uint8_t *d_kf_desc = nullptr; // [slots][cap][32]
     int *d_kf_count = nullptr;    // [slots]
     int cap = 0;
@@ -83,7 +86,7 @@ void kfs_replay_destroy(kfs_replay *r)
     if (!r) return;
     KfsDeviceGuard guard(r->device);
     if (r->compute) cudaStreamSynchronize(r->compute);
-    for (int b = 0; b < 2; b++) {
+    for (int b = 0; b < RP_ARENAS; b++) {
         ReplaySlot &S = r->slot[b];
         if (S.ev_done) { if (S.in_flight) cudaEventSynchronize(S.ev_done); cudaEventDestroy(S.ev_done); }
         if (S.ev_knn) cudaEventDestroy(S.ev_knn);
@@ -113,7 +116,7 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
     r->p = *params;
     r->device = device;
     kfs_status s = KFS_OK;
-    for (int b = 0; b < 2 && !s; b++) s = kfs_orb_create(&params->orb, device, &r->orb[b]);
+    for (int b = 0; b < RP_ARENAS && !s; b++) s = kfs_orb_create(&params->orb, device, &r->orb[b]);
     if (!s) s = kfs_bf_create(KFS_NORM_HAMMING, 0, device, &r->bf);
     if (s) { kfs_replay_destroy(r); return s; }
     KfsDeviceGuard guard(device);
@@ -129,7 +132,7 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
         }                                                                                                  \
     } while (0)
     RP_TRY(cudaStreamCreateWithFlags(&r->compute, cudaStreamNonBlocking));
-    for (int b = 0; b < 2; b++) {
+    for (int b = 0; b < RP_ARENAS; b++) {
         ReplaySlot &S = r->slot[b];
         kfs_orb_set_stream(r->orb[b], (void *)r->compute);
         kfs_orb_internal_start_fence(r->orb[b], false); // arena reuse is ordered by replay_finish instead
@@ -152,6 +155,7 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
 }
 
 int kfs_replay_capacity(const kfs_replay *r) { return r ? r->cap : 0; }
+int kfs_replay_arenas(const kfs_replay *r) { return r ? RP_ARENAS : 0; }
 int kfs_replay_last_launches(const kfs_replay *r) { return r ? r->launches : 0; }
 
 kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_replay_frame *plan, int batch, int *ticket)
@@ -168,7 +172,7 @@ kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_r
             KFS_FAIL(KFS_ERR_INVALID_ARG, "plan[%d].store_slot = %d out of range", i, plan[i].store_slot);
     }
     KfsDeviceGuard guard(r->device);
-    const int b = r->seq & 1;
+    const int b = r->seq % RP_ARENAS;
     ReplaySlot &S = r->slot[b];
     kfs_status s = replay_finish(r, b); // the arena is reused: its previous batch must be complete (results already delivered)
     if (s && s != KFS_ERR_CAPACITY) return s;
@@ -252,7 +256,7 @@ kfs_status kfs_replay_wait(kfs_replay *r, int ticket)
 {
     if (!r) KFS_FAIL(KFS_ERR_INVALID_ARG, "replay handle is NULL");
     KfsDeviceGuard guard(r->device);
-    for (int b = 0; b < 2; b++)
+    for (int b = 0; b < RP_ARENAS; b++)
         if (r->slot[b].in_flight && r->slot[b].ticket == ticket) return replay_finish(r, b);
     if (ticket >= 0 && ticket < r->seq) return KFS_OK; // already delivered (its arena was reused, or waited before)
     KFS_FAIL(KFS_ERR_INVALID_ARG, "unknown ticket %d", ticket);

@@ -43,16 +43,16 @@ def _check_batch(oracle, out, B, ref, kf_desc_of, ratio=0.6):
 
 def test_replay_in_batch_keyframes_and_double_buffering(kfs, oracle):
     B, nf = 6, 500
-    frames = [np.ascontiguousarray(synth.make_stream(B, 240, 320, seed=30 + s)) for s in range(3)]
+    NB = 5
+    frames = [np.ascontiguousarray(synth.make_stream(B, 240, 320, seed=30 + s)) for s in range(NB)]
     rp = kfs.Replay(nfeatures=nf, max_batch=B, keyframe_slots=2, ratio=0.6)
+    assert kfs.lib().kfs_replay_arenas(rp._h) == 3
     plan = [(0, -1)] * B  # every frame (the keyframe itself included) against frame 0 of its batch
-    outs = [rp.alloc_outputs(B) for _ in range(3)]
-    t0 = rp.submit(frames[0], plan, outs[0])
-    t1 = rp.submit(frames[1], plan, outs[1])   # two batches in flight
-    t2 = rp.submit(frames[2], plan, outs[2])   # third submit completes the first internally
-    for t in (t0, t1, t2):
+    outs = [rp.alloc_outputs(B) for _ in range(NB)]
+    tickets = [rp.submit(frames[s], plan, outs[s]) for s in range(NB)]   # three batches in flight; the 4th and 5th submit
+    for t in tickets:                                                     # complete the oldest ones internally
         assert rp.wait(t) == 0
-    for s in range(3):
+    for s in range(NB):
         ref = _oracle_frames(oracle, frames[s], nf)
         _check_batch(oracle, outs[s], B, ref, lambda i: ref[0][1])
     assert rp.last_launches > 0
