@@ -206,7 +206,7 @@ def run_reference(args):
                              "sample": "%d frames/step (%d per worker x %d workers x 1 thread)" % (per * arm.cores, per, arm.cores)},
             "e2e": {"value": round(fps, 2), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit_line(line)
     return 0
 
 
@@ -223,6 +223,7 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device — the hot path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    affinity = bind_to_gpu_numa_node(local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world))) if world > 1 else None
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -584,7 +585,7 @@ def run_ours(args):
                        "l2": "inputs rotate over %d batches (%d MB > 126 MB L2); pyramid+lists per batch %d MB" % (nrot, nrot * B * W * H // 2**20, B * (sum(px) + 13 * 10**6) // 2**20),
                        "sharding": "frames sharded across ranks, no collective on the data path",
                        "keypoints_per_frame": round(nkp, 1), "ratio_survivors_per_frame": round(float(np.mean(good)), 1),
-                       "fast_corners_per_level_frame0": fast_counts, "synth_gen_s": round(gen_s, 2)},
+                       "fast_corners_per_level_frame0": fast_counts, "synth_gen_s": round(gen_s, 2), "rank0_cpu_affinity": affinity},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 1), "unit": "frames/s", "h2d_bytes_per_step": int(rep_h2d), "d2h_bytes_per_step": int(rep_d2h),
                     "steps": Kr, "api": "kfs_replay_submit/kfs_replay_wait (C ABI replay executor): pinned host frames in; keypoints, descriptors, "
@@ -595,11 +596,57 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "roofline": roofline, "roofline_popc": roofline_popc, "kernels": kernels, "stream_latency": lat,
             "window_matching": win, "cpu_baseline": cpu}
-    print(json.dumps(line), flush=True)
+    emit_line(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    """Only the JSON line may reach stdout: libraries that print there (NCCL's version banner, torchrun children) are sent to
+    stderr by pointing fd 1 at fd 2; emit_line() writes to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
+def bind_to_gpu_numa_node(gpu_index, local_world):
+    """Pin this rank (and the pinned host buffers it is about to allocate: first touch) to the CPUs next to its GPU, so that
+    8 ranks do not pull their frames across the socket interconnect.  Falls back to an even split of the visible cores."""
+    info = {}
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        near = [c for c in range(ncpu) if (int(words[c // 64]) >> (c % 64)) & 1]
+        allowed = sorted(os.sched_getaffinity(0))
+        near = [c for c in near if c in allowed] or allowed
+        # ranks that share a NUMA node split its cores
+        sharers = [g for g in range(local_world) if list(pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(g), (ncpu + 63) // 64)) == list(words)]
+        k, n = sharers.index(gpu_index) if gpu_index in sharers else 0, max(1, len(sharers))
+        per = max(1, len(near) // n)
+        mine = near[k * per:(k + 1) * per] or near
+        os.sched_setaffinity(0, mine)
+        info = {"cpus": "%d-%d" % (mine[0], mine[-1]), "numa_cpus": len(near), "ranks_on_node": n}
+    except Exception as e:  # affinity is an optimisation only
+        info = {"error": str(e)[:120]}
+    return info
 
 
 def main():
@@ -618,6 +665,7 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: >= 3 warm-up steps
+    guard_stdout()
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)

@@ -126,3 +126,33 @@ def test_window_config4_shape_and_edges(kfs, oracle):
     for bad in (0, -1, 65):
         with pytest.raises(kfs.KfsError):
             fe.setWindow(bad)
+
+
+def test_window_config5_full_size(kfs, oracle):
+    """BASELINE.json config 5 at full size on one GPU: a 3840x2160 frame, nfeatures = 10000, k = 2 + ratio 0.75 against a
+    32-keyframe window = 32 pairs of up to 10000 x 10000 (OpenCV forbids one 320000-row train matrix).  The current frame is
+    extracted on the device and matched where it lies; every pair is checked against the oracle, bit for bit."""
+    synth = __import__("importlib").import_module("keyframe-based-slam_b200.synth")
+    frame = synth.make_stream(1, 2160, 3840, seed=2, pad=32)[0]
+    fe = kfs.TrackerFrontEnd(nfeatures=10000)
+    fe.setWindow(32)
+    kp, desc = fe.extractFeatures(frame)
+    assert len(kp) >= 9900
+    rng = np.random.default_rng(11)
+    depth = make_depth(32, 32, 2)
+    kfd = []
+    for i in range(34):                                    # 34 pushed, the last 32 stay
+        n = len(desc) if i % 5 else int(rng.integers(1, len(desc)))
+        d = desc[rng.permutation(len(desc))[:n]].copy()
+        flip = rng.random(d.shape) < 0.05
+        d[flip] ^= rng.integers(1, 256, int(flip.sum()), dtype=np.uint8)
+        kfd.append(d)
+        fe.setKeyframe(d, np.zeros(n, kfs.KP_DTYPE), depth)
+    assert fe.windowCount == 32
+    good, knn = fe.matchWindow(None, 0.75, want_knn=True)  # device-resident current frame
+    assert fe.last_launches == 2
+    rknn, rgood = oracle.match_window(kfd, desc, 32, 0.75)
+    assert len(good) == 32 and sum(len(x) for x in rgood) > 100000
+    for i in range(32):
+        assert np.array_equal(knn[i], rknn[i]), "kNN rows of window keyframe %d differ" % i
+        assert np.array_equal(good[i], rgood[i]), "ratio survivors of window keyframe %d differ" % i
