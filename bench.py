@@ -482,6 +482,48 @@ def run_ours(args):
     except Exception as ex:  # latency is informative only
         lat = {"error": str(ex)[:200]}
 
+    # ---- the tracker's own call pattern through the C ABI with HOST buffers (VisualOdometry::Track, :129-172): per frame
+    #      kfs_frontend_extract_features (pinned gray frame in, keypoints + descriptors out) + kfs_frontend_match_features
+    #      against the device-resident keyframe (ratio test + back-projection, 3-D / 2-D lists out); blocking calls, one frame
+    try:
+        fe = C.c_void_p()
+        fpar = N.OrbParams()
+        L.kfs_orb_default_params(C.byref(fpar))
+        fpar.nfeatures = NF
+        N.check(L.kfs_frontend_create(C.byref(fpar), local_rank, C.byref(fe)))
+        fcap = L.kfs_frontend_capacity(fe)
+        f_kp = torch.empty((fcap, 28), dtype=torch.uint8).pin_memory().numpy()
+        f_desc = torch.empty((fcap, 32), dtype=torch.uint8).pin_memory().numpy()
+        f_m = torch.empty((fcap, 16), dtype=torch.uint8).pin_memory().numpy()
+        f_p3 = torch.empty((fcap, 3), dtype=torch.float64).pin_memory().numpy()
+        f_p2 = torch.empty((fcap, 2), dtype=torch.float64).pin_memory().numpy()
+        depth_h = torch.full((H, W), 1500, dtype=torch.int16).pin_memory().numpy().view(np.uint16)
+        intr = (C.c_double * 4)(910.1, 909.6, 640.4, 360.7)
+        fn, fg = C.c_int(), C.c_int()
+        src = pinned[0].numpy()
+
+        def track(i):
+            N.check(L.kfs_frontend_extract_features(fe, src[i % B].ctypes.data, W, W, H, 1, None, 0, f_kp.ctypes.data, f_desc.ctypes.data, fcap, C.byref(fn)))
+            if i % KF_EVERY == 0:
+                N.check(L.kfs_frontend_promote_keyframe(fe, depth_h.ctypes.data, 2 * W))
+            N.check(L.kfs_frontend_match_features(fe, None, None, 0, intr, 0.6, f_m.ctypes.data, f_p3.ctypes.data, f_p2.ctypes.data, fcap, C.byref(fg)))
+        for i in range(5):
+            track(i)
+        nh = 40
+        t0 = time.perf_counter()
+        for i in range(nh):
+            track(i)
+        host_us = (time.perf_counter() - t0) / nh * 1e6
+        if lat is not None and "error" not in lat:
+            lat["host_api_frame_us"] = round(host_us, 1)
+            lat["host_api_frames_per_s"] = round(1e6 / host_us, 1)
+            lat["host_api"] = ("kfs_frontend_extract_features + kfs_frontend_match_features per frame, pinned host frame in (%d B), keypoints + "
+                               "descriptors + matches + 3-D/2-D points out, keyframe promoted every %d frames, blocking" % (W * H, KF_EVERY))
+        L.kfs_frontend_destroy(fe)
+    except Exception as ex:
+        if isinstance(lat, dict):
+            lat["host_api_error"] = str(ex)[:200]
+
     # ---- window matching (configs[3]: current frame vs the 10 keyframes of a local-BA window = 10 pairs of 2000 x 2000 per
     #      frame; kfs_frontend_match_window issues exactly this launch): (a) one frame per call, (b) every frame of the batch
     win = None

@@ -266,7 +266,8 @@ KFS_API kfs_status kfs_frontend_set_keyframe(kfs_frontend *fe, const uint8_t *de
  * K(0,2), K(1,2)).  Survivors of d0 < ratio*d1 come out in query order: matches_out[i] (the best cv::DMatch),
  * points3d_out[3*i..] = (x, y, z) and points2d_out[2*i..] = current keypoint pt, all as the reference's doubles
  * (computed through the same float intermediates).  *n_out = survivors (may exceed capacity: then only `capacity` rows
- * were written and the status is KFS_ERR_CAPACITY). */
+ * were written and the status is KFS_ERR_CAPACITY).  Rows past *n_out (up to min(capacity, keyframe rows)) are scratch:
+ * count and lists come back in one device-to-host round trip. */
 KFS_API kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc, const kfs_keypoint *cur_kp, int n_cur,
                                                const double *intrinsics, float ratio,
                                                kfs_dmatch *matches_out, double *points3d_out, double *points2d_out,

@@ -11,6 +11,7 @@
 #include "kfs_math.cuh"
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 #include <vector>
 #include <new>
 
@@ -970,6 +971,19 @@ k_describe(const __grid_constant__ OrbDev g)
 // ======================================================================================================
 // host side
 // ======================================================================================================
+// One captured kernel chain: everything kfs_orb_run_eager's launches depend on, and the instantiated graph.
+struct OrbGraph {
+    OrbDev g;
+    int nb;
+    const uint8_t *mask;
+    size_t mask_step, mask_fs;
+    bool first;
+    cudaStream_t stream;
+    int seen;                 // calls with this key so far (the graph is captured on the second one)
+    int nlaunch;              // kernel launches inside
+    cudaGraphExec_t exec;
+};
+
 struct kfs_orb {
     kfs_orb_params p;
     int device = 0;
@@ -1000,6 +1014,9 @@ struct kfs_orb {
     int last_batch = 0;
     int launches = 0;
     bool profiling = false;
+    // CUDA graphs of the kernel chain, one per distinct launch configuration (see kfs_orb_run)
+    std::vector<OrbGraph> graphs;
+    bool use_graphs = true;
     cudaEvent_t ev[KFS_STAGE_COUNT + 1];
     bool ev_made = false;
     float stage_ms[KFS_STAGE_COUNT];
@@ -1035,8 +1052,15 @@ static void kfs_axis_table(int src, int dst, int padded, std::vector<uint32_t> &
     }
 }
 
+static void kfs_orb_drop_graphs(kfs_orb *o)
+{
+    for (OrbGraph &G : o->graphs) if (G.exec) cudaGraphExecDestroy(G.exec);
+    o->graphs.clear();
+}
+
 static void kfs_orb_free_arena(kfs_orb *o)
 {
+    kfs_orb_drop_graphs(o);
     if (o->arena) { cudaFree(o->arena); o->arena = nullptr; }
     o->W = o->H = o->B = 0;
 }
@@ -1210,7 +1234,7 @@ static kfs_status kfs_stage_mark(kfs_orb *o, int idx)
 
 // Runs the kernel chain on frames [f0, f0 + nb) whose level 0 is already described by g.lv[0].img / .mask.
 // d_mask_in points at frame f0 of the raw mask (or nullptr).  `first` = first chunk of a call: clears the counters.
-static kfs_status kfs_orb_run(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_in, size_t mask_step, size_t mask_fs, bool first)
+static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_in, size_t mask_step, size_t mask_fs, bool first)
 {
     OrbDev &g = o->g;
     const int L = g.nlevels;
@@ -1313,6 +1337,67 @@ static kfs_status kfs_orb_run(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_
     return KFS_OK;
 }
 
+// The chain is 14+ launches, two streams and a memset: for small batches (the tracker's one frame per call) the launch
+// overhead is a large part of the latency.  A launch configuration seen for the second time is captured into a CUDA graph
+// (the side-stream blur becomes a parallel branch) and replayed from then on.  The key is every input of the launches: the
+// whole OrbDev block (all pointers and sizes, frame0, per-level masks), the frame count, the mask source and the stream.
+// Profiling (per-stage events) and a stream that is itself being captured by the caller take the eager path.
+static kfs_status kfs_orb_run(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_in, size_t mask_step, size_t mask_fs, bool first)
+{
+    cudaStream_t st = o->stream;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (!o->use_graphs || o->profiling || cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) {
+        cudaGetLastError();
+        return kfs_orb_run_eager(o, f0, nb, d_mask_in, mask_step, mask_fs, first);
+    }
+    // the fields kfs_orb_run_eager sets before launching, so that the key below is complete
+    o->g.frame0 = f0;
+    if (first) for (int l = 0; l < o->g.nlevels; l++) o->g.lv[l].mask = d_mask_in ? o->mpyr[l] : nullptr;
+    OrbGraph *G = nullptr;
+    for (OrbGraph &c : o->graphs)
+        if (c.nb == nb && c.mask == d_mask_in && c.mask_step == mask_step && c.mask_fs == mask_fs && c.first == first && c.stream == st &&
+            memcmp(&c.g, &o->g, sizeof(OrbDev)) == 0) { G = &c; break; }
+    if (!G) {
+        if (o->graphs.size() >= 32) kfs_orb_drop_graphs(o);
+        OrbGraph n;
+        n.g = o->g; n.nb = nb; n.mask = d_mask_in; n.mask_step = mask_step; n.mask_fs = mask_fs; n.first = first; n.stream = st;
+        n.seen = 0; n.nlaunch = 0; n.exec = nullptr;
+        o->graphs.push_back(n);
+        G = &o->graphs.back();
+    }
+    G->seen++;
+    if (G->exec) {
+        KFS_CUDA_TRY(cudaGraphLaunch(G->exec, st));
+        o->launches += G->nlaunch;
+        o->last_batch = f0 + nb;
+        return KFS_OK;
+    }
+    if (G->seen < 2) return kfs_orb_run_eager(o, f0, nb, d_mask_in, mask_step, mask_fs, first); // also creates the side stream, sets attributes
+    if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        cudaGetLastError();
+        o->use_graphs = false;
+        return kfs_orb_run_eager(o, f0, nb, d_mask_in, mask_step, mask_fs, first);
+    }
+    const int before = o->launches;
+    const kfs_status rs = kfs_orb_run_eager(o, f0, nb, d_mask_in, mask_step, mask_fs, first);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+    cudaGraphExec_t exec = nullptr;
+    if (rs == KFS_OK && ce == cudaSuccess && graph && cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess) {
+        cudaGraphDestroy(graph);
+        G->exec = exec;
+        G->nlaunch = o->launches - before;
+        KFS_CUDA_TRY(cudaGraphLaunch(exec, st));
+        return KFS_OK;
+    }
+    // capture failed: nothing was executed; forget graphs on this handle and run the chain directly
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    o->use_graphs = false;
+    o->launches = before;
+    return kfs_orb_run_eager(o, f0, nb, d_mask_in, mask_step, mask_fs, first);
+}
+
 static kfs_status kfs_orb_check_frame_args(const kfs_orb *o, const void *gray, size_t step, int w, int h, int batch)
 {
     if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
@@ -1353,6 +1438,7 @@ kfs_status kfs_orb_create(const kfs_orb_params *params, int device, kfs_orb **ou
     o->device = device;
     o->cap_out = (int)kfs_align_up((size_t)(P.nfeatures + P.nfeatures / 4 + 64), 8);
     memset(&o->g, 0, sizeof(o->g));
+    if (const char *eg = getenv("KFS_ORB_GRAPHS")) o->use_graphs = atoi(eg) != 0; // experiments: 0 = always launch the chain directly
     memset(o->stage_ms, 0, sizeof(o->stage_ms));
     KfsDeviceGuard guard(device);
     cudaError_t e = cudaStreamCreateWithFlags(&o->own_stream, cudaStreamNonBlocking);

@@ -432,17 +432,17 @@ kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_ratio_backproject launch: %s", cudaGetErrorString(e));
     fe->launches++;
+    // one round trip: the survivor count and the lists' upper bound (at most one survivor per keyframe row) travel together
     KFS_CUDA_TRY(cudaMemcpyAsync(fe->h_nout, fe->d_nout, sizeof(int), cudaMemcpyDeviceToHost, st));
-    KFS_CUDA_TRY(cudaStreamSynchronize(st));
-    const int n = *fe->h_nout;
-    *n_out = n;
-    const int m = n < A.capacity ? n : A.capacity;
+    const int m = kf->n < A.capacity ? kf->n : A.capacity;
     if (m > 0) {
         KFS_CUDA_TRY(cudaMemcpyAsync(matches_out, fe->d_good, (size_t)m * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, st));
         KFS_CUDA_TRY(cudaMemcpyAsync(points3d_out, fe->d_p3d, (size_t)m * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
         KFS_CUDA_TRY(cudaMemcpyAsync(points2d_out, fe->d_p2d, (size_t)m * 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-        KFS_CUDA_TRY(cudaStreamSynchronize(st));
     }
+    KFS_CUDA_TRY(cudaStreamSynchronize(st));
+    const int n = *fe->h_nout;
+    *n_out = n;
     if (n > capacity) KFS_FAIL(KFS_ERR_CAPACITY, "match_features: %d survivors, output capacity %d", n, capacity);
     return KFS_OK;
 }
