@@ -258,3 +258,38 @@ def test_4k_frame_vs_oracle(kfs, oracle):
     assert r["recall"] >= RECALL_MIN and r["max_angle_err_rad"] <= ANGLE_TOL_RAD and r["desc_equal"] == r["n_common"], r
     assert np.array_equal(kp, rk) and np.array_equal(desc, rd)
     assert len(kp) >= 9900
+
+
+def test_orb_graph_replay_same_handle_many_calls(kfs, oracle):
+    """The kernel chain is replayed as a CUDA graph from the third call of a launch configuration on (kfs_orb_run): the
+    results must keep following the DATA (new frames, new masks), survive a mask appearing / disappearing, a batch and a size
+    change in between (arena re-allocation drops the graphs), and stay bit-exact against the oracle throughout."""
+    orb = kfs.ORB_create(400)
+    P = oracle.orb_params(nfeatures=400)
+    frames = synth.make_stream(9, 240, 320, seed=77)
+    mask = np.zeros((240, 320), np.uint8)
+    mask[30:200, 40:280] = 255
+    assert orb.last_launches == 0
+
+    def check(img, m=None):
+        kp, desc = orb.detectAndCompute(img, m)
+        rk, rd = oracle.detect_and_compute(img, m, P)
+        assert len(rk) > 50 and np.array_equal(kp, rk) and np.array_equal(desc, rd)
+    for f in range(5):                       # eager, capture, replay, replay, replay
+        check(frames[f])
+    n_plain = orb.last_launches
+    assert n_plain >= 13                     # a replayed graph still reports the kernels it launched
+    for f in range(4):                       # the masked chain is another graph
+        check(frames[f], mask)
+    assert orb.last_launches > n_plain
+    check(frames[5])                         # back to the unmasked graph
+    assert orb.last_launches == n_plain
+    kps, descs = orb.detectAndComputeBatch(frames[:3])          # batch change: chunked pipeline, different frame counts
+    for f in range(3):
+        rk, rd = oracle.detect_and_compute(frames[f], None, P)
+        assert np.array_equal(kps[f], rk) and np.array_equal(descs[f], rd)
+    big = synth.make_stream(4, 300, 400, seed=78)               # size change: arena re-allocated, graphs dropped
+    for f in range(4):
+        check(big[f])
+    for f in range(6, 9):                    # and the first shape again
+        check(frames[f])
