@@ -1597,7 +1597,10 @@ static kfs_status kfs_orb_pipeline_init(kfs_orb *o, int nchunks)
 static kfs_status kfs_h2d_frames(uint8_t *d, size_t dpitch, size_t dfs, const uint8_t *h, size_t step, size_t frame_stride,
                                  int w, int h_rows, int f0, int nb, cudaStream_t st)
 {
-    if (frame_stride == step * (size_t)h_rows && dfs == dpitch * (size_t)h_rows) {
+    if (frame_stride == step * (size_t)h_rows && dfs == dpitch * (size_t)h_rows && step == (size_t)w && dpitch == (size_t)w) {
+        // both sides fully contiguous: one linear copy
+        KFS_CUDA_TRY(cudaMemcpyAsync(d + (size_t)f0 * dfs, h + (size_t)f0 * frame_stride, (size_t)w * h_rows * nb, cudaMemcpyHostToDevice, st));
+    } else if (frame_stride == step * (size_t)h_rows && dfs == dpitch * (size_t)h_rows) {
         KFS_CUDA_TRY(cudaMemcpy2DAsync(d + (size_t)f0 * dfs, dpitch, h + (size_t)f0 * frame_stride, step, (size_t)w, (size_t)h_rows * nb,
                                        cudaMemcpyHostToDevice, st));
     } else {
@@ -1671,7 +1674,12 @@ kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const uint8_t *gray, size_t st
         if (s) return s;
         KFS_CUDA_TRY(cudaEventRecord(o->ev_cmp[c], o->stream));
         KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_out, o->ev_cmp[c], 0));
-        if (cp > 0) {
+        if (cp > 0 && capacity == o->cap_out) { // same row pitch on both sides: linear copies
+            KFS_CUDA_TRY(cudaMemcpyAsync(kp_out + (size_t)f0 * capacity, o->g.kp + (size_t)f0 * o->cap_out,
+                                         (size_t)nb * capacity * sizeof(kfs_keypoint), cudaMemcpyDeviceToHost, o->s_out));
+            KFS_CUDA_TRY(cudaMemcpyAsync(desc_out + (size_t)f0 * capacity * 32, o->g.desc + (size_t)f0 * o->cap_out * 32,
+                                         (size_t)nb * capacity * 32, cudaMemcpyDeviceToHost, o->s_out));
+        } else if (cp > 0) {
             KFS_CUDA_TRY(cudaMemcpy2DAsync(kp_out + (size_t)f0 * capacity, (size_t)capacity * sizeof(kfs_keypoint),
                                            o->g.kp + (size_t)f0 * o->cap_out, (size_t)o->cap_out * sizeof(kfs_keypoint),
                                            (size_t)cp * sizeof(kfs_keypoint), (size_t)nb, cudaMemcpyDeviceToHost, o->s_out));

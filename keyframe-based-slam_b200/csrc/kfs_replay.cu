@@ -232,10 +232,14 @@ kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_r
     KFS_CUDA_TRY(cudaStreamWaitEvent(s_out, S.ev_knn, 0));
     if (want_knn) {
         const int cp = io->capacity < cap ? io->capacity : cap;
-        if (io->knn && cp > 0)
+        if (io->knn && cp > 0 && io->capacity == cap)
+            KFS_CUDA_TRY(cudaMemcpyAsync(io->knn, S.d_knn, (size_t)batch * cap * 2 * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, s_out));
+        else if (io->knn && cp > 0)
             KFS_CUDA_TRY(cudaMemcpy2DAsync(io->knn, (size_t)io->capacity * 2 * sizeof(kfs_dmatch), S.d_knn, (size_t)cap * 2 * sizeof(kfs_dmatch),
                                            (size_t)cp * 2 * sizeof(kfs_dmatch), (size_t)batch, cudaMemcpyDeviceToHost, s_out));
-        if (io->good && cp > 0 && r->p.ratio > 0.f)
+        if (io->good && cp > 0 && r->p.ratio > 0.f && io->capacity == cap)
+            KFS_CUDA_TRY(cudaMemcpyAsync(io->good, S.d_good, (size_t)batch * cap * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, s_out));
+        else if (io->good && cp > 0 && r->p.ratio > 0.f)
             KFS_CUDA_TRY(cudaMemcpy2DAsync(io->good, (size_t)io->capacity * sizeof(kfs_dmatch), S.d_good, (size_t)cap * sizeof(kfs_dmatch),
                                            (size_t)cp * sizeof(kfs_dmatch), (size_t)batch, cudaMemcpyDeviceToHost, s_out));
         KFS_CUDA_TRY(cudaMemcpyAsync(S.h_small, S.d_small, 2 * sizeof(int) * (size_t)r->p.max_batch, cudaMemcpyDeviceToHost, s_out));
