@@ -27,7 +27,8 @@ constexpr int BF_QTILE = BF_QWARPS * 32 * BF_QPT; // 128 queries per CTA
 constexpr int BF_CHUNK = 512;                   // train rows per smem stage (16 KB)
 constexpr int BF_SLICE = BF_CHUNK / BF_TSPLIT;  // rows one warp group scans per stage
 constexpr uint32_t BF_INF = 0xffffffffu;
-constexpr int BF_MAX_SPLIT = 8;                // train-row splits of one (pair, query tile) across CTAs
+constexpr int BF_MAX_SPLIT = 16;               // train-row splits of one (pair, query tile) across CTAs
+constexpr int BF_GRAN = 128;                   // a split is a whole number of 128-row granules (16 rows per warp group)
 static_assert(BF_QTILE <= BF_THREADS, "one thread per query in the merge epilogue");
 
 
@@ -103,7 +104,7 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
 
     // this CTA's train rows [t0, t1)
     const int S = gridDim.z, split = blockIdx.z;
-    const int seg = S > 1 ? ((nt + BF_CHUNK - 1) / BF_CHUNK + S - 1) / S * BF_CHUNK : nt; // whole stages per split
+    const int seg = S > 1 ? ((nt + BF_GRAN - 1) / BF_GRAN + S - 1) / S * BF_GRAN : nt; // whole granules per split
     const int t0 = min(split * seg, nt), t1 = min(t0 + seg, nt);
     const int nchunks = (t1 - t0 + BF_CHUNK - 1) / BF_CHUNK;
     auto issue = [&](int chunk, int stage) {
@@ -119,9 +120,12 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
         if (c + 1 < nchunks) { issue(c + 1, stage ^ 1); bf_cp_wait<1>(); }
         else bf_cp_wait<0>();
         __syncthreads();
-        const int base = t0 + c * BF_CHUNK + tsplit * BF_SLICE;
-        const int rows = min(BF_SLICE, t1 - base); // may be <= 0 for the last chunk
-        const uint4 *tp = &s_train[stage][tsplit * BF_SLICE * 2];
+        // the rows of this stage are dealt evenly to the 8 warp groups (a short last stage keeps every group busy)
+        const int crows = min(BF_CHUNK, t1 - (t0 + c * BF_CHUNK));
+        const int slice = (crows + BF_TSPLIT - 1) / BF_TSPLIT;
+        const int base = t0 + c * BF_CHUNK + tsplit * slice;
+        const int rows = min(slice, t1 - base); // may be <= 0 for the last groups
+        const uint4 *tp = &s_train[stage][tsplit * slice * 2];
 #pragma unroll 2
         for (int j = 0; j < rows; j++) {
             const uint4 ta = tp[2 * j], tb = tp[2 * j + 1];
@@ -273,10 +277,10 @@ struct kfs_bf {
 
 // Number of train splits.  A batch with >= 4 query tiles per SM is throughput-bound as it is (S = 1).  Smaller launches
 // (one 2000 x 2000 pair is 16 tiles on 148 SMs) split the train rows over up to BF_MAX_SPLIT CTAs per tile, in whole
-// BF_CHUNK stages so that the 8 warp groups of every CTA stay evenly loaded.
+// 128-row granules (the kernel deals the rows of a stage evenly to its 8 warp groups).
 static int bf_choose_split(const kfs_bf *b, int tiles, int max_nt)
 {
-    const int nchunks = kfs_div_up(max_nt > 0 ? max_nt : 1, BF_CHUNK);
+    const int nchunks = kfs_div_up(max_nt > 0 ? max_nt : 1, BF_GRAN); // granules
     int s;
     if (b->force_split > 0) s = b->force_split;
     else {
