@@ -143,6 +143,14 @@ KFS_API kfs_status kfs_orb_set_pipeline_chunk(kfs_orb *orb, int frames);
 KFS_API kfs_status kfs_orb_level_info(kfs_orb *orb, int level, int *w, int *h, int *quota, float *scale);
 KFS_API kfs_status kfs_orb_download_level(kfs_orb *orb, int frame, int level, uint8_t *out, size_t out_step);
 /* FAST corners after NMS + border + mask filter of (frame, level): packed score<<24 | y<<12 | x, unordered. */
+/* a1.9: ORB blurs every level with OpenCV's float sepFilter2D path, whose last bit follows the CPU
+ * dispatch: fused multiply-adds with the default AVX2/AVX-512 build (fma = 1, the default here), separate multiply and add with
+ * cv::setUseOptimized(false) or on a host without FMA (fma = 0; 6 of 921600 pixels of a 720p frame differ by 1).  Pick the one
+ * the CPU path you compare against uses. */
+KFS_API kfs_status kfs_orb_set_blur_fma(kfs_orb *orb, int fma);
+/* Parity / debugging: the blurred copy of a level (rows and columns closer than 12 px to the border are never sampled by a
+ * descriptor and are not REFLECT_101-exact). */
+KFS_API kfs_status kfs_orb_download_blurred_level(kfs_orb *orb, int frame, int level, uint8_t *out, size_t out_step);
 KFS_API kfs_status kfs_orb_download_fast_corners(kfs_orb *orb, int frame, int level, uint32_t *out, int capacity, int *n_out);
 /* Per-stage device time of the last extraction when profiling is on (cudaEvent pairs on the handle's
  * stream). Stage ids: KFS_STAGE_*.  ms[KFS_STAGE_COUNT]. */

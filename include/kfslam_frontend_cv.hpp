@@ -72,6 +72,12 @@ public:
     ORB(const ORB &) = delete;
     ORB &operator=(const ORB &) = delete;
 
+    // follow the other OpenCV dispatch of the per-level blur (cv::setUseOptimized(false) / a host without FMA)
+    void setBlurFMA(bool fma)
+    {
+        const kfs_status st = kfs_orb_set_blur_fma(h_, fma ? 1 : 0);
+        if (st != KFS_OK) detail::raise(st, "kfs::ORB::setBlurFMA");
+    }
     // cv::Feature2D::detectAndCompute(image, mask, keypoints, descriptors, useProvidedKeypoints=false)
     void detectAndCompute(cv::InputArray image, cv::InputArray mask, std::vector<cv::KeyPoint> &keypoints,
                           cv::OutputArray descriptors, bool useProvidedKeypoints = false)

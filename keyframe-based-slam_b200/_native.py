@@ -75,6 +75,8 @@ SIGNATURES = {
     "kfs_orb_set_pipeline_chunk": (_i, [_vp, _i]),
     "kfs_orb_level_info": (_i, [_vp, _i, _ip, _ip, _ip, C.POINTER(_f)]),
     "kfs_orb_download_level": (_i, [_vp, _i, _i, _vp, _sz]),
+    "kfs_orb_set_blur_fma": (_i, [_vp, _i]),
+    "kfs_orb_download_blurred_level": (_i, [_vp, _i, _i, _vp, _sz]),
     "kfs_orb_download_fast_corners": (_i, [_vp, _i, _i, _vp, _i, _ip]),
     "kfs_orb_set_profiling": (_i, [_vp, _i]),
     "kfs_orb_stage_times": (_i, [_vp, C.POINTER(_f)]),

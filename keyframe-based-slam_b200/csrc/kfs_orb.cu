@@ -635,30 +635,42 @@ __device__ __forceinline__ void kfs_unpk2(kfs_f2 v, float &lo, float &hi) { asm(
 __device__ __forceinline__ kfs_f2 kfs_mul2(kfs_f2 a, kfs_f2 b) { kfs_f2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ kfs_f2 kfs_add2(kfs_f2 a, kfs_f2 b) { kfs_f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ kfs_f2 kfs_fma2(kfs_f2 a, kfs_f2 b, kfs_f2 c) { kfs_f2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+// g*p + r as OpenCV's FMA dispatch evaluates it (one rounding), or as its plain-C++ build does (cv::setUseOptimized(false) or
+// a host without FMA: product rounded, then the sum) - SURVEY a1.9 "dispatch-dependent"
+template <bool FMA> __device__ __forceinline__ kfs_f2 kfs_mad2(kfs_f2 g, kfs_f2 p, kfs_f2 r)
+{
+    if (FMA) return kfs_fma2(g, p, r);
+    // scalar on purpose: ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into one FFMA2 (even with --fmad=false), which would turn
+    // this variant back into the fused one; scalar __fmul_rn / __fadd_rn are never contracted
+    float gl, gh, pl, ph, rl, rh;
+    kfs_unpk2(g, gl, gh); kfs_unpk2(p, pl, ph); kfs_unpk2(r, rl, rh);
+    return kfs_pk2(__fadd_rn(__fmul_rn(gl, pl), rl), __fadd_rn(__fmul_rn(gh, ph), rh));
+}
 // kfs_blur_row on both lanes
-__device__ __forceinline__ kfs_f2 kfs_blur_row2(kfs_f2 g0, kfs_f2 g1, kfs_f2 g2, kfs_f2 g3, kfs_f2 p0, kfs_f2 p1, kfs_f2 p2, kfs_f2 p3,
+template <bool FMA> __device__ __forceinline__ kfs_f2 kfs_blur_row2(kfs_f2 g0, kfs_f2 g1, kfs_f2 g2, kfs_f2 g3, kfs_f2 p0, kfs_f2 p1, kfs_f2 p2, kfs_f2 p3,
                                                 kfs_f2 p4, kfs_f2 p5, kfs_f2 p6)
 {
     kfs_f2 r = kfs_mul2(g0, p0);
-    r = kfs_fma2(g1, p1, r);
-    r = kfs_fma2(g2, p2, r);
-    r = kfs_fma2(g3, p3, r);
-    r = kfs_fma2(g2, p4, r);
-    r = kfs_fma2(g1, p5, r);
-    r = kfs_fma2(g0, p6, r);
+    r = kfs_mad2<FMA>(g1, p1, r);
+    r = kfs_mad2<FMA>(g2, p2, r);
+    r = kfs_mad2<FMA>(g3, p3, r);
+    r = kfs_mad2<FMA>(g2, p4, r);
+    r = kfs_mad2<FMA>(g1, p5, r);
+    r = kfs_mad2<FMA>(g0, p6, r);
     return r;
 }
 // kfs_blur_col_bits on both lanes: the bits of (s + 1.5*2^23), byte 0 of each half is the rounded pixel
-__device__ __forceinline__ kfs_f2 kfs_blur_col2(kfs_f2 g0, kfs_f2 g1, kfs_f2 g2, kfs_f2 g3, kfs_f2 magic, kfs_f2 rm3, kfs_f2 rm2, kfs_f2 rm1,
+template <bool FMA> __device__ __forceinline__ kfs_f2 kfs_blur_col2(kfs_f2 g0, kfs_f2 g1, kfs_f2 g2, kfs_f2 g3, kfs_f2 magic, kfs_f2 rm3, kfs_f2 rm2, kfs_f2 rm1,
                                                 kfs_f2 r0, kfs_f2 rp1, kfs_f2 rp2, kfs_f2 rp3)
 {
     kfs_f2 s = kfs_mul2(g3, r0);
-    s = kfs_fma2(g2, kfs_add2(rp1, rm1), s);
-    s = kfs_fma2(g1, kfs_add2(rp2, rm2), s);
-    s = kfs_fma2(g0, kfs_add2(rp3, rm3), s);
+    s = kfs_mad2<FMA>(g2, kfs_add2(rp1, rm1), s);
+    s = kfs_mad2<FMA>(g1, kfs_add2(rp2, rm2), s);
+    s = kfs_mad2<FMA>(g0, kfs_add2(rp3, rm3), s);
     return kfs_add2(s, magic);
 }
 
+template <bool FMA>
 __global__ void __launch_bounds__(BT_THREADS)
 k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
 {
@@ -701,10 +713,10 @@ k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             float4 va, vb;
-            kfs_unpk2(kfs_blur_row2(G0, G1, G2, G3, p[4 * k + 0], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6]), va.x, vb.x);
-            kfs_unpk2(kfs_blur_row2(G0, G1, G2, G3, p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7]), va.y, vb.y);
-            kfs_unpk2(kfs_blur_row2(G0, G1, G2, G3, p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8]), va.z, vb.z);
-            kfs_unpk2(kfs_blur_row2(G0, G1, G2, G3, p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8], p[4 * k + 9]), va.w, vb.w);
+            kfs_unpk2(kfs_blur_row2<FMA>(G0, G1, G2, G3, p[4 * k + 0], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6]), va.x, vb.x);
+            kfs_unpk2(kfs_blur_row2<FMA>(G0, G1, G2, G3, p[4 * k + 1], p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7]), va.y, vb.y);
+            kfs_unpk2(kfs_blur_row2<FMA>(G0, G1, G2, G3, p[4 * k + 2], p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8]), va.z, vb.z);
+            kfs_unpk2(kfs_blur_row2<FMA>(G0, G1, G2, G3, p[4 * k + 3], p[4 * k + 4], p[4 * k + 5], p[4 * k + 6], p[4 * k + 7], p[4 * k + 8], p[4 * k + 9]), va.w, vb.w);
             const int slot = (4 * sg + k) ^ (sg >> 1);
             oa[slot] = va;
             ob[slot] = vb;
@@ -726,8 +738,8 @@ k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
         for (int k = 0; k < 8; k++) {
             if (k >= nrows) break;
             const ulonglong2 q6 = col[(k + 6) * (BT_W / 4)];
-            const kfs_f2 ab = kfs_blur_col2(G0, G1, G2, G3, magic, q0.x, q1.x, q2.x, q3.x, q4.x, q5.x, q6.x);
-            const kfs_f2 cd = kfs_blur_col2(G0, G1, G2, G3, magic, q0.y, q1.y, q2.y, q3.y, q4.y, q5.y, q6.y);
+            const kfs_f2 ab = kfs_blur_col2<FMA>(G0, G1, G2, G3, magic, q0.x, q1.x, q2.x, q3.x, q4.x, q5.x, q6.x);
+            const kfs_f2 cd = kfs_blur_col2<FMA>(G0, G1, G2, G3, magic, q0.y, q1.y, q2.y, q3.y, q4.y, q5.y, q6.y);
             // byte 0 of each magic-rounded float is the pixel
             const uint32_t a = (uint32_t)ab, b = (uint32_t)(ab >> 32), c = (uint32_t)cd, d = (uint32_t)(cd >> 32);
             *reinterpret_cast<uint32_t *>(dst) = __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
@@ -1017,6 +1029,7 @@ struct kfs_orb {
     // CUDA graphs of the kernel chain, one per distinct launch configuration (see kfs_orb_run)
     std::vector<OrbGraph> graphs;
     bool use_graphs = true;
+    bool blur_fma = true;           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
     cudaEvent_t ev[KFS_STAGE_COUNT + 1];
     bool ev_made = false;
     float stage_ms[KFS_STAGE_COUNT];
@@ -1292,7 +1305,8 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
         }
         KFS_CUDA_TRY(cudaEventRecord(o->ev_pyr, st));
         KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_blur, o->ev_pyr, 0));
-        k_blur7<<<dim3(o->blur_tiles, nb), BT_THREADS, 0, o->s_blur>>>(g, o->blur_tab);
+        if (o->blur_fma) k_blur7<true><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, o->s_blur>>>(g, o->blur_tab);
+        else k_blur7<false><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, o->s_blur>>>(g, o->blur_tab);
         KFS_LAUNCH_CHECK(o);
         KFS_CUDA_TRY(cudaEventRecord(o->ev_blur, o->s_blur));
     }
@@ -1326,7 +1340,8 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
     if (fork_blur) {
         KFS_CUDA_TRY(cudaStreamWaitEvent(st, o->ev_blur, 0));
     } else if (o->blur_tiles > 0) {
-        k_blur7<<<dim3(o->blur_tiles, nb), BT_THREADS, 0, st>>>(g, o->blur_tab);
+        if (o->blur_fma) k_blur7<true><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, st>>>(g, o->blur_tab);
+        else k_blur7<false><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, st>>>(g, o->blur_tab);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
@@ -1774,6 +1789,30 @@ kfs_status kfs_orb_download_level(kfs_orb *o, int frame, int level, uint8_t *out
     KfsDeviceGuard guard(o->device);
     const LevelDev &L = o->g.lv[level];
     KFS_CUDA_TRY(cudaMemcpy2DAsync(out, out_step, L.img + (size_t)frame * L.img_fs, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost, o->stream));
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_set_blur_fma(kfs_orb *o, int fma)
+{
+    if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
+    if (o->blur_fma != (fma != 0)) {
+        KfsDeviceGuard guard(o->device);
+        KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+        kfs_orb_drop_graphs(o); // the captured chains hold the other kernel
+        o->blur_fma = fma != 0;
+    }
+    return KFS_OK;
+}
+
+kfs_status kfs_orb_download_blurred_level(kfs_orb *o, int frame, int level, uint8_t *out, size_t out_step)
+{
+    if (!o || !o->arena || !out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_download_blurred_level: bad arguments");
+    if (level < 0 || level >= o->nlevels_active || frame < 0 || frame >= o->last_batch) KFS_FAIL(KFS_ERR_INVALID_ARG, "frame/level out of range");
+    KfsDeviceGuard guard(o->device);
+    const LevelDev &L = o->g.lv[level];
+    if (!L.blur) KFS_FAIL(KFS_ERR_INVALID_ARG, "level %d has no blurred copy (too small to hold a keypoint)", level);
+    KFS_CUDA_TRY(cudaMemcpy2DAsync(out, out_step, L.blur + (size_t)frame * L.img_fs_blur, (size_t)L.pitch_blur, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost, o->stream));
     KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
     return KFS_OK;
 }

@@ -124,6 +124,16 @@ class ORB:
         N.check(N.lib().kfs_orb_download_level(self._h, frame, level, _ptr(out), w))
         return out
 
+    def set_blur_fma(self, fma=True):
+        """a1.9: True = OpenCV's default FMA dispatch of the 7x7 blur, False = its plain mul + add build (cv2.setUseOptimized(False))."""
+        N.check(N.lib().kfs_orb_set_blur_fma(self._h, int(bool(fma))))
+
+    def download_blurred_level(self, frame, level):
+        w, h, _, _ = self.level_info(level)
+        out = np.zeros((h, w), np.uint8)
+        N.check(N.lib().kfs_orb_download_blurred_level(self._h, frame, level, out.ctypes.data, out.strides[0]))
+        return out
+
     def download_fast_corners(self, frame, level):
         """-> int32 [n,3] rows (x, y, score), sorted by (y, x)."""
         w, h, _, _ = self.level_info(level)
