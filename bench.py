@@ -166,13 +166,67 @@ class CpuArm:
         self.pool.join()
 
 
+def cpu_latency_lines(cores, nframes=6):
+    """SURVEY 8(d) 'CPU baseline timing' items (i), (ii), (iv): per-frame latency of the path (ORB + 2000x2000 kNN vs the keyframe)
+    with cv2 on one thread, cv2 with setNumThreads(all cores), and the scalar C oracle port; the CPU model."""
+    out = {}
+    try:
+        import importlib
+        synth = importlib.import_module("keyframe-based-slam_b200.synth")
+        frames = synth.make_stream(nframes + 1, H, W, seed=7)
+        try:
+            for line in open("/proc/cpuinfo"):
+                if line.startswith("model name"):
+                    out["cpu_model"] = line.split(":", 1)[1].strip()
+                    break
+        except OSError:
+            pass
+
+        def timed(fn):
+            kf = fn(frames[0], None)
+            t0 = time.perf_counter()
+            for f in frames[1:]:
+                fn(f, kf)
+            return (time.perf_counter() - t0) / nframes * 1e3
+        try:
+            import cv2
+            orb = cv2.ORB_create(NF, 1.2, 8, 31, 0, 2, cv2.ORB_HARRIS_SCORE, 31, 20)
+            bf = cv2.BFMatcher.create(cv2.NORM_HAMMING)
+
+            def cv_frame(f, kf):
+                _, d = orb.detectAndCompute(f, None)
+                if kf is not None:
+                    bf.knnMatch(kf, d, 2)
+                return d
+            cv2.setNumThreads(1)
+            out["cv2_1_thread_ms_per_frame"] = round(timed(cv_frame), 2)
+            cv2.setNumThreads(cores)
+            out["cv2_%d_threads_ms_per_frame" % cores] = round(timed(cv_frame), 2)
+            cv2.setNumThreads(1)
+        except ImportError:
+            pass
+        from oracle import oracle as O
+        P = O.orb_params(nfeatures=NF)
+
+        def port_frame(f, kf):
+            _, d = O.detect_and_compute(f, None, P)
+            if kf is not None:
+                O.knn_match(kf, d, 2)
+            return d
+        out["c_port_1_thread_ms_per_frame"] = round(timed(port_frame), 2)
+    except Exception as e:  # informative only
+        out["latency_error"] = str(e)[:160]
+    return out
+
+
 def cpu_baseline_block(arm, seconds_target=12.0):
     arm.run(1)  # warm-up (also builds the keyframe)
     fps, dt, n, _, _ = arm.run(2)
     per = max(2, int(seconds_target / max(dt / 2, 1e-3)))
     per = min(per, 200)
     fps, dt, n, nk, ng = arm.run(per)
-    return {"value": round(fps, 2), "unit": "frames/s", "cores": arm.cores, "kind": arm.kind,
+    extra = cpu_latency_lines(arm.cores)
+    return {**extra, "value": round(fps, 2), "unit": "frames/s", "cores": arm.cores, "kind": arm.kind,
             "sample": "%d frames of 1280x720 (nf=2000 ORB + 2000x2000 kNN k=2 vs keyframe) over %d worker processes x 1 thread, %.1f s wall, "
                       "%s" % (n, arm.cores, dt, "cv2 %s (OpenCV, the code behind VisualOdometry.cpp:30,39)" % __import__("cv2").__version__
                               if arm.kind == "reference" else "oracle/ C port, scalar"),
