@@ -450,7 +450,7 @@ def run_ours(args):
             N.check(L.kfs_replay_wait(rp, t))
 
     Kr = max(2, Ke)
-    r_run(3)
+    r_run(2 * n_arena + 1)   # warm-up: every arena has run its chain eagerly and captured its CUDA graph
     barrier()
     t0 = time.perf_counter()
     r_run(Kr)

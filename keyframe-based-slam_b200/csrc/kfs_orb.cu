@@ -9,6 +9,7 @@
 //   k_describe (orientation + blur + rBRIEF)
 #include "kfs_common.cuh"
 #include "kfs_math.cuh"
+#include <cuda.h> // CUtensorMap + the cuTensorMapEncodeTiled prototype only: the entry point is looked up at run time, libcuda is not linked
 #include <math.h>
 #include <string.h>
 #include <stdlib.h>
@@ -194,6 +195,42 @@ constexpr int FAST_MAXOUT = (FT_W / 2) * (FT_H / 2); // strict 3x3 maxima: at mo
 static_assert(SC_H * 4 == FAST_THREADS, "one mask word per thread");
 static_assert(FAST_MAXOUT * 4 <= FS_P * FS_H, "survivor list aliases the source tile");
 
+// ---- TMA (cp.async.bulk.tensor) staging of the source tile ------------------------------------------------------
+// One 3-D tensor map per level over [frame][row][byte] (u8, row pitch and frame stride in bytes, both multiples of 16);
+// a tile is one box of FS_P x FS_H x 1 bytes landing densely in shared memory (rows FS_P = 144 B apart); bytes outside the
+// level arrive as zeros (they only feed scores the border filter drops).  One thread arms an mbarrier with the box size
+// and issues the copy; every thread waits on the barrier's phase 0.
+struct FastMaps {
+    CUtensorMap m[KFS_MAX_LEVELS];
+    int enabled; // 0: the driver entry point is unavailable -> the tile is loaded with LDG.128 / STS.128
+};
+__device__ __forceinline__ void kfs_mbar_init(uint64_t *bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void kfs_mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void kfs_tma_load_3d(void *smem, const CUtensorMap *map, int x, int y, int z, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(map), "r"(x), "r"(y), "r"(z), "r"((uint32_t)__cvta_generic_to_shared(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void kfs_mbar_wait(uint64_t *bar, uint32_t phase)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "KFS_MBAR_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra KFS_MBAR_DONE;\n"
+                 "bra KFS_MBAR_WAIT;\n"
+                 "KFS_MBAR_DONE:\n"
+                 "}" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(phase) : "memory");
+}
+
 __device__ __forceinline__ int kfs_atoms_add(int *p, int v)
 {
     int r;
@@ -202,9 +239,10 @@ __device__ __forceinline__ int kfs_atoms_add(int *p, int v)
 }
 
 __global__ void __launch_bounds__(FAST_THREADS)
-k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
+k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, const __grid_constant__ FastMaps maps)
 {
-    __shared__ __align__(16) uint8_t s_src[FS_P * FS_H + 16];
+    __shared__ __align__(128) uint8_t s_src[FS_P * FS_H + 16];
+    __shared__ __align__(8) uint64_t s_bar;
     __shared__ __align__(16) uint8_t s_sc[SC_W * SC_H];
     __shared__ uint16_t s_q[SC_W * SC_H];
     __shared__ __align__(16) uint32_t s_mask[SC_H * 4];
@@ -222,17 +260,28 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     const uint8_t *img = L.img + (long long)f * L.img_fs;
     const int thr = g.fast_thr;
 
-    // ---- load the source tile (uint4 per thread), clear the score tile and the mask rows
-    for (int i = tid; i < FS_H * (FS_ROWB / 16); i += FAST_THREADS) {
-        const int r = i >> 3, c = i & 7;
-        const int gy = min(max(sy0 + r, 0), H - 1), gx = ox + 16 * c;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
-        *reinterpret_cast<uint4 *>(s_src + r * FS_P + 16 * c) = v;
+    // ---- load the source tile (one TMA box, or uint4 per thread), clear the score tile and the mask rows meanwhile
+    const bool tma = maps.enabled != 0;
+    if (tma) {
+        if (tid == 0) kfs_mbar_init(&s_bar, 1);
+        __syncthreads();
+        if (tid == 0) {
+            kfs_mbar_expect_tx(&s_bar, FS_P * FS_H);
+            kfs_tma_load_3d(s_src, &maps.m[l], ox, sy0, f, &s_bar);
+        }
+    } else {
+        for (int i = tid; i < FS_H * (FS_ROWB / 16); i += FAST_THREADS) {
+            const int r = i >> 3, c = i & 7;
+            const int gy = min(max(sy0 + r, 0), H - 1), gx = ox + 16 * c;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
+            *reinterpret_cast<uint4 *>(s_src + r * FS_P + 16 * c) = v;
+        }
     }
     for (int i = tid; i < SC_W * SC_H / 16; i += FAST_THREADS) reinterpret_cast<uint4 *>(s_sc)[i] = make_uint4(0, 0, 0, 0);
     s_mask[tid] = 0;
     if (tid == 0) { s_nout = 0; s_ncorner = 0; }
+    if (tma) kfs_mbar_wait(&s_bar, 0);
     __syncthreads();
 
     // ---- phase 1: quick reject, one score row per warp-iteration, 4 pixels per lane
@@ -1029,7 +1078,13 @@ struct kfs_orb {
     // CUDA graphs of the kernel chain, one per distinct launch configuration (see kfs_orb_run)
     std::vector<OrbGraph> graphs;
     bool use_graphs = true;
-    bool blur_fma = true;           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
+    bool blur_fma = true;
+    // TMA descriptors of the levels for k_fast (re-encoded only when a level's address / pitch / size changes)
+    FastMaps fmaps;
+    const uint8_t *fmap_img[KFS_MAX_LEVELS] = {};
+    long long fmap_fs[KFS_MAX_LEVELS] = {};
+    int fmap_pitch[KFS_MAX_LEVELS] = {}, fmap_h[KFS_MAX_LEVELS] = {};
+    int tma_state = 0;              // 0 = not probed yet, 1 = cuTensorMapEncodeTiled available, -1 = not (LDG path)           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
     cudaEvent_t ev[KFS_STAGE_COUNT + 1];
     bool ev_made = false;
     float stage_ms[KFS_STAGE_COUNT];
@@ -1245,6 +1300,53 @@ static kfs_status kfs_stage_mark(kfs_orb *o, int idx)
     return KFS_OK;
 }
 
+// cuTensorMapEncodeTiled is a driver-API function: looked up through the runtime so that libcuda is not a link dependency
+// (this library also has to build, and load for the ABI tests, on machines without a driver).
+typedef CUresult (*kfs_encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                        const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                        CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static kfs_encode_tiled_fn kfs_encode_tiled()
+{
+    static kfs_encode_tiled_fn fn = nullptr;
+    static bool probed = false;
+    if (!probed) {
+        probed = true;
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (kfs_encode_tiled_fn)p;
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+
+// (Re)builds the per-level tensor maps k_fast's TMA loads use.  KFS_ORB_TMA=0 forces the LDG path (experiments).
+static void kfs_orb_update_fast_maps(kfs_orb *o)
+{
+    if (o->tma_state == 0) {
+        const char *e = getenv("KFS_ORB_TMA");
+        o->tma_state = (e && atoi(e) == 0) || !kfs_encode_tiled() ? -1 : 1;
+        memset(&o->fmaps, 0, sizeof(o->fmaps));
+    }
+    o->fmaps.enabled = o->tma_state > 0;
+    if (o->tma_state < 0) return;
+    const OrbDev &g = o->g;
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelDev &L = g.lv[l];
+        if (L.tiles_x <= 0 || L.tiles_y <= 0) continue;
+        if (o->fmap_img[l] == L.img && o->fmap_fs[l] == L.img_fs && o->fmap_pitch[l] == L.pitch && o->fmap_h[l] == L.h) continue;
+        const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.h, 65535};
+        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.img_fs};
+        const cuuint32_t box[3] = {(cuuint32_t)FS_P, (cuuint32_t)FS_H, 1}, estr[3] = {1, 1, 1};
+        const bool ok = ((uintptr_t)L.img % 16 == 0) && (L.pitch % 16 == 0) && (L.img_fs % 16 == 0) &&
+                        kfs_encode_tiled()(&o->fmaps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)L.img, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+        if (!ok) { o->tma_state = -1; o->fmaps.enabled = 0; return; } // e.g. an unaligned caller buffer: stay on the LDG path for good
+        o->fmap_img[l] = L.img; o->fmap_fs[l] = L.img_fs; o->fmap_pitch[l] = L.pitch; o->fmap_h[l] = L.h;
+    }
+}
+
 // Runs the kernel chain on frames [f0, f0 + nb) whose level 0 is already described by g.lv[0].img / .mask.
 // d_mask_in points at frame f0 of the raw mask (or nullptr).  `first` = first chunk of a call: clears the counters.
 static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d_mask_in, size_t mask_step, size_t mask_fs, bool first)
@@ -1312,7 +1414,8 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
     }
     if (kfs_stage_mark(o, KFS_STAGE_FAST)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
-        k_fast<<<dim3(g.total_tiles, nb), FAST_THREADS, 0, st>>>(g, o->tile_tab);
+        kfs_orb_update_fast_maps(o);
+        k_fast<<<dim3(g.total_tiles, nb), FAST_THREADS, 0, st>>>(g, o->tile_tab, o->fmaps);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_SELECT_HARRIS)) return KFS_ERR_CUDA;
