@@ -721,9 +721,10 @@ template <bool FMA> __device__ __forceinline__ kfs_f2 kfs_blur_col2(kfs_f2 g0, k
 
 template <bool FMA>
 __global__ void __launch_bounds__(BT_THREADS)
-k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
+k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, const __grid_constant__ FastMaps maps)
 {
-    __shared__ __align__(16) uint8_t s_src[BS_P * BS_H];
+    __shared__ __align__(128) uint8_t s_src[BS_P * BS_H];
+    __shared__ __align__(8) uint64_t s_bar;
     __shared__ __align__(16) float s_row[BS_H * BT_W];
     const int tid = threadIdx.x;
     const int f = blockIdx.y + g.frame0;
@@ -733,15 +734,25 @@ k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab)
     const int H = L.h, pitch = L.pitch;
     const int x0 = BT_W * tix, y0 = BT_Y0 + BT_H * tiy;
     const uint8_t *img = L.img + (long long)f * L.img_fs;
-    for (int i = tid; i < BS_H * (BS_P / 16); i += BT_THREADS) {
-        const int r = i / (BS_P / 16), c = i - r * (BS_P / 16);
-        const int gy = min(max(y0 - 3 + r, 0), H - 1), gx = x0 - 16 + 16 * c;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (gx >= 0 && gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
-        *reinterpret_cast<uint4 *>(s_src + r * BS_P + 16 * c) = v;
-    }
     const kfs_f2 G0 = kfs_pk2(KFS_G0, KFS_G0), G1 = kfs_pk2(KFS_G1, KFS_G1), G2 = kfs_pk2(KFS_G2, KFS_G2), G3 = kfs_pk2(KFS_G3, KFS_G3);
-    __syncthreads();
+    if (maps.enabled) { // one TMA box (bytes outside the level arrive as zeros: they only feed outputs that are never sampled)
+        if (tid == 0) kfs_mbar_init(&s_bar, 1);
+        __syncthreads();
+        if (tid == 0) {
+            kfs_mbar_expect_tx(&s_bar, BS_P * BS_H);
+            kfs_tma_load_3d(s_src, &maps.m[l], x0 - 16, y0 - 3, f, &s_bar);
+        }
+        kfs_mbar_wait(&s_bar, 0);
+    } else {
+        for (int i = tid; i < BS_H * (BS_P / 16); i += BT_THREADS) {
+            const int r = i / (BS_P / 16), c = i - r * (BS_P / 16);
+            const int gy = min(max(y0 - 3 + r, 0), H - 1), gx = x0 - 16 + 16 * c;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (gx >= 0 && gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
+            *reinterpret_cast<uint4 *>(s_src + r * BS_P + 16 * c) = v;
+        }
+        __syncthreads();
+    }
     // ---- row pass: rows 2m (low lanes) and 2m+1 (high lanes), pixels [16 sg, 16 sg + 16)
     {
         const int m = tid >> 3, sg = tid & 7;
@@ -1045,6 +1056,14 @@ struct OrbGraph {
     cudaGraphExec_t exec;
 };
 
+// Tensor maps of one kernel's tile shape + what they were encoded from
+struct MapCache {
+    FastMaps maps;
+    const uint8_t *img[KFS_MAX_LEVELS] = {};
+    long long fs[KFS_MAX_LEVELS] = {};
+    int pitch[KFS_MAX_LEVELS] = {}, h[KFS_MAX_LEVELS] = {};
+};
+
 struct kfs_orb {
     kfs_orb_params p;
     int device = 0;
@@ -1080,10 +1099,7 @@ struct kfs_orb {
     bool use_graphs = true;
     bool blur_fma = true;
     // TMA descriptors of the levels for k_fast (re-encoded only when a level's address / pitch / size changes)
-    FastMaps fmaps;
-    const uint8_t *fmap_img[KFS_MAX_LEVELS] = {};
-    long long fmap_fs[KFS_MAX_LEVELS] = {};
-    int fmap_pitch[KFS_MAX_LEVELS] = {}, fmap_h[KFS_MAX_LEVELS] = {};
+    MapCache fmaps, bmaps;          // k_fast's 144 x 70 boxes, k_blur7's 160 x 64 boxes
     int tma_state = 0;              // 0 = not probed yet, 1 = cuTensorMapEncodeTiled available, -1 = not (LDG path)           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
     cudaEvent_t ev[KFS_STAGE_COUNT + 1];
     bool ev_made = false;
@@ -1321,29 +1337,28 @@ static kfs_encode_tiled_fn kfs_encode_tiled()
     return fn;
 }
 
-// (Re)builds the per-level tensor maps k_fast's TMA loads use.  KFS_ORB_TMA=0 forces the LDG path (experiments).
-static void kfs_orb_update_fast_maps(kfs_orb *o)
+// (Re)builds the per-level tensor maps of one kernel's tile shape (box_w x box_h bytes).  KFS_ORB_TMA=0 forces the LDG path.
+static void kfs_orb_update_maps(kfs_orb *o, MapCache &C, int box_w, int box_h)
 {
     if (o->tma_state == 0) {
         const char *e = getenv("KFS_ORB_TMA");
         o->tma_state = (e && atoi(e) == 0) || !kfs_encode_tiled() ? -1 : 1;
-        memset(&o->fmaps, 0, sizeof(o->fmaps));
     }
-    o->fmaps.enabled = o->tma_state > 0;
+    C.maps.enabled = o->tma_state > 0;
     if (o->tma_state < 0) return;
     const OrbDev &g = o->g;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelDev &L = g.lv[l];
-        if (L.tiles_x <= 0 || L.tiles_y <= 0) continue;
-        if (o->fmap_img[l] == L.img && o->fmap_fs[l] == L.img_fs && o->fmap_pitch[l] == L.pitch && o->fmap_h[l] == L.h) continue;
+        if (L.list_cap <= 0) continue; // no keypoint can come from this level: neither kernel has a tile on it
+        if (C.img[l] == L.img && C.fs[l] == L.img_fs && C.pitch[l] == L.pitch && C.h[l] == L.h) continue;
         const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.h, 65535};
         const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.img_fs};
-        const cuuint32_t box[3] = {(cuuint32_t)FS_P, (cuuint32_t)FS_H, 1}, estr[3] = {1, 1, 1};
+        const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1}, estr[3] = {1, 1, 1};
         const bool ok = ((uintptr_t)L.img % 16 == 0) && (L.pitch % 16 == 0) && (L.img_fs % 16 == 0) &&
-                        kfs_encode_tiled()(&o->fmaps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)L.img, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        kfs_encode_tiled()(&C.maps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)L.img, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-        if (!ok) { o->tma_state = -1; o->fmaps.enabled = 0; return; } // e.g. an unaligned caller buffer: stay on the LDG path for good
-        o->fmap_img[l] = L.img; o->fmap_fs[l] = L.img_fs; o->fmap_pitch[l] = L.pitch; o->fmap_h[l] = L.h;
+        if (!ok) { o->tma_state = -1; C.maps.enabled = 0; return; } // e.g. an unaligned caller buffer: stay on the LDG path for good
+        C.img[l] = L.img; C.fs[l] = L.img_fs; C.pitch[l] = L.pitch; C.h[l] = L.h;
     }
 }
 
@@ -1407,15 +1422,16 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
         }
         KFS_CUDA_TRY(cudaEventRecord(o->ev_pyr, st));
         KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_blur, o->ev_pyr, 0));
-        if (o->blur_fma) k_blur7<true><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, o->s_blur>>>(g, o->blur_tab);
-        else k_blur7<false><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, o->s_blur>>>(g, o->blur_tab);
+        kfs_orb_update_maps(o, o->bmaps, BS_P, BS_H);
+        if (o->blur_fma) k_blur7<true><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, o->s_blur>>>(g, o->blur_tab, o->bmaps.maps);
+        else k_blur7<false><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, o->s_blur>>>(g, o->blur_tab, o->bmaps.maps);
         KFS_LAUNCH_CHECK(o);
         KFS_CUDA_TRY(cudaEventRecord(o->ev_blur, o->s_blur));
     }
     if (kfs_stage_mark(o, KFS_STAGE_FAST)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
-        kfs_orb_update_fast_maps(o);
-        k_fast<<<dim3(g.total_tiles, nb), FAST_THREADS, 0, st>>>(g, o->tile_tab, o->fmaps);
+        kfs_orb_update_maps(o, o->fmaps, FS_P, FS_H);
+        k_fast<<<dim3(g.total_tiles, nb), FAST_THREADS, 0, st>>>(g, o->tile_tab, o->fmaps.maps);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_SELECT_HARRIS)) return KFS_ERR_CUDA;
@@ -1443,8 +1459,9 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
     if (fork_blur) {
         KFS_CUDA_TRY(cudaStreamWaitEvent(st, o->ev_blur, 0));
     } else if (o->blur_tiles > 0) {
-        if (o->blur_fma) k_blur7<true><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, st>>>(g, o->blur_tab);
-        else k_blur7<false><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, st>>>(g, o->blur_tab);
+        kfs_orb_update_maps(o, o->bmaps, BS_P, BS_H);
+        if (o->blur_fma) k_blur7<true><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, st>>>(g, o->blur_tab, o->bmaps.maps);
+        else k_blur7<false><<<dim3(o->blur_tiles, nb), BT_THREADS, 0, st>>>(g, o->blur_tab, o->bmaps.maps);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
