@@ -570,7 +570,23 @@ def run_ours(args):
         for i in range(nh):
             track(i)
         host_us = (time.perf_counter() - t0) / nh * 1e6
+        # the same in ONE call / one synchronisation per frame (kfs_frontend_track)
+        fm = C.c_int()
+
+        def track1(i):
+            N.check(L.kfs_frontend_track(fe, src[i % B].ctypes.data, W, W, H, 1, None, 0, intr, 0.6, f_kp.ctypes.data, f_desc.ctypes.data, fcap, C.byref(fn),
+                                         f_m.ctypes.data, f_p3.ctypes.data, f_p2.ctypes.data, fcap, C.byref(fm)))
+            if i % KF_EVERY == 0:
+                N.check(L.kfs_frontend_promote_keyframe(fe, depth_h.ctypes.data, 2 * W))
+        for i in range(5):
+            track1(i)
+        t0 = time.perf_counter()
+        for i in range(nh):
+            track1(i)
+        track_us = (time.perf_counter() - t0) / nh * 1e6
         if lat is not None and "error" not in lat:
+            lat["host_api_track_call_us"] = round(track_us, 1)
+            lat["host_api_track_frames_per_s"] = round(1e6 / track_us, 1)
             lat["host_api_frame_us"] = round(host_us, 1)
             lat["host_api_frames_per_s"] = round(1e6 / host_us, 1)
             lat["host_api"] = ("kfs_frontend_extract_features + kfs_frontend_match_features per frame, pinned host frame in (%d B), keypoints + "

@@ -280,6 +280,18 @@ KFS_API kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *
                                                const double *intrinsics, float ratio,
                                                kfs_dmatch *matches_out, double *points3d_out, double *points2d_out,
                                                int capacity, int *n_out);
+/* The front half of VisualOdometry::Track (/root/reference/src/lib/VisualOdometry.cpp:129-172) for one frame in ONE call with
+ * ONE host synchronisation: ExtractFeatures (:138) and MatchFeatures against the cached keyframe (:144) are enqueued back to
+ * back (upload, colour conversion, ORB chain, kNN, ratio test + back-projection, every result copy).  Arguments as in
+ * kfs_frontend_extract_features and kfs_frontend_match_features (the current frame is the one just extracted).
+ * *n_matches_out = -1 when no keyframe is cached yet (only the extraction ran: the tracker then promotes this frame,
+ * VisualOdometry.cpp:105-123).  Rows past the returned counts are scratch. */
+KFS_API kfs_status kfs_frontend_track(kfs_frontend *fe, const uint8_t *image, size_t step, int w, int h, int channels,
+                                      const uint8_t *mask, size_t mask_step, const double *intrinsics, float ratio,
+                                      kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out,
+                                      kfs_dmatch *matches_out, double *points3d_out, double *points2d_out, int match_capacity,
+                                      int *n_matches_out);
+
 /* ---- keyframe window --------------------------------------------------------
  *   Map::GetNKeyFrames(win)   /root/reference/src/lib/Map.cpp:72-78    the last `win` keyframes, oldest first, or all of
  *                             them while fewer exist

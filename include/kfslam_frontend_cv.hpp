@@ -271,6 +271,33 @@ public:
         return {points3D, points2D};
     }
 
+    // ExtractFeatures + MatchFeatures of one frame with one host synchronisation (VisualOdometry.cpp:138,144).  Returns false
+    // while no keyframe is cached (only keypoints / descriptors are filled: promote this frame).
+    bool Track(const cv::Mat &rgb, const cv::Mat &mask, std::vector<cv::KeyPoint> &keypoints, cv::Mat &descriptors,
+               std::vector<cv::Point3d> &points3D, std::vector<cv::Point2d> &points2D, std::vector<cv::DMatch> &matches)
+    {
+        const int cap = kfs_frontend_capacity(h_);
+        keypoints.resize((size_t)cap);
+        std::vector<uint8_t> d((size_t)cap * 32);
+        std::vector<cv::DMatch> m((size_t)cap);
+        std::vector<double> p3((size_t)cap * 3), p2((size_t)cap * 2);
+        int n = 0, nm = -1;
+        const kfs_status st = kfs_frontend_track(h_, rgb.data, (size_t)rgb.step, rgb.cols, rgb.rows, rgb.channels(), mask.empty() ? nullptr : mask.data,
+                                                 mask.empty() ? 0 : (size_t)mask.step, k_, ratio_, reinterpret_cast<kfs_keypoint *>(keypoints.data()), d.data(), cap,
+                                                 &n, reinterpret_cast<kfs_dmatch *>(m.data()), p3.data(), p2.data(), cap, &nm);
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::Track");
+        keypoints.resize((size_t)n);
+        detail::make_desc(descriptors, n);
+        for (int i = 0; i < n; i++) std::memcpy(descriptors.ptr(i), d.data() + (size_t)i * 32, 32);
+        points3D.clear(); points2D.clear(); matches.clear();
+        for (int i = 0; i < nm; i++) {
+            matches.push_back(m[(size_t)i]);
+            points3D.push_back(cv::Point3d(p3[3 * (size_t)i], p3[3 * (size_t)i + 1], p3[3 * (size_t)i + 2]));
+            points2D.push_back(cv::Point2d(p2[2 * (size_t)i], p2[2 * (size_t)i + 1]));
+        }
+        return nm >= 0;
+    }
+
     // ---- keyframe window: Map::GetNKeyFrames (src/lib/Map.cpp:72-78; window 5 at include/lib/Optimizers.hpp:70) ----
     void SetWindow(int window)
     {

@@ -106,6 +106,7 @@ SIGNATURES = {
     "kfs_frontend_promote_keyframe": (_i, [_vp, _vp, _sz]),
     "kfs_frontend_set_keyframe": (_i, [_vp, _vp, _vp, _i, _vp, _sz, _i, _i]),
     "kfs_frontend_match_features": (_i, [_vp, _vp, _vp, _i, C.POINTER(C.c_double), _f, _vp, _vp, _vp, _i, _ip]),
+    "kfs_frontend_track": (_i, [_vp, _vp, _sz, _i, _i, _i, _vp, _sz, C.POINTER(C.c_double), _f, _vp, _vp, _i, _ip, _vp, _vp, _vp, _i, _ip]),
     "kfs_frontend_set_window": (_i, [_vp, _i]),
     "kfs_frontend_window": (_i, [_vp]),
     "kfs_frontend_window_count": (_i, [_vp]),

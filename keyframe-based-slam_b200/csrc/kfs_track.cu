@@ -266,7 +266,7 @@ kfs_status kfs_frontend_create(const kfs_orb_params *params, int device, kfs_fro
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_p3d, n * 3 * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_p2d, n * 2 * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&fe->d_nout, sizeof(int));
-    if (e == cudaSuccess) e = cudaMallocHost(&fe->h_nout, sizeof(int));
+    if (e == cudaSuccess) e = cudaMallocHost(&fe->h_nout, 2 * sizeof(int));
     if (e == cudaSuccess) e = cudaMallocHost(&fe->h_wn, KFS_MAX_WINDOW * sizeof(int));
     if (e != cudaSuccess) {
         kfs_frontend_destroy(fe);
@@ -281,19 +281,15 @@ kfs_status kfs_frontend_create(const kfs_orb_params *params, int device, kfs_fro
 int kfs_frontend_capacity(const kfs_frontend *fe) { return fe ? fe->cap : 0; }
 int kfs_frontend_last_launches(const kfs_frontend *fe) { return fe ? fe->launches : 0; }
 
-kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t *image, size_t step, int w, int h, int channels,
-                                         const uint8_t *mask, size_t mask_step,
-                                         kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out)
+// Validates the frame, uploads it (+ mask), converts colour and runs the ORB chain; nothing synchronises.  On return the
+// device views of the current frame are set; cur_n is still unknown (-2 = "on the device, count pending").
+static kfs_status fe_enqueue_extract(kfs_frontend *fe, const uint8_t *image, size_t step, int w, int h, int channels,
+                                     const uint8_t *mask, size_t mask_step, const char *who)
 {
-    if (!fe || !n_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle or n_out is NULL");
-    *n_out = 0;
-    if (channels != 1 && channels != 3) KFS_FAIL(KFS_ERR_UNSUPPORTED, "ExtractFeatures: %d channels (the reference handles 1 or 3, VisualOdometry.cpp:27)", channels);
-    if (w < 0 || h < 0 || capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "negative size");
-    if (w == 0 || h == 0) { fe->cur_n = 0; return KFS_OK; }
+    if (channels != 1 && channels != 3) KFS_FAIL(KFS_ERR_UNSUPPORTED, "%s: %d channels (the reference handles 1 or 3, VisualOdometry.cpp:27)", who, channels);
+    if (w <= 0 || h <= 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "%s: empty image", who);
     if (!image || step < (size_t)w * channels) KFS_FAIL(KFS_ERR_INVALID_ARG, "image is NULL or step < w*channels");
     if (mask && mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < w");
-    if (capacity > 0 && (!kp_out || !desc_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
-    KfsDeviceGuard guard(fe->device);
     cudaStream_t st = fe->stream;
     const size_t gpitch = kfs_align_up((size_t)w, 128);
     kfs_status s = fe_reserve(&fe->d_gray, &fe->gray_bytes, gpitch * h);
@@ -324,9 +320,25 @@ kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t *image,
     int dcap = 0, nb = 0;
     s = kfs_orb_device_results(fe->orb, &fe->d_cur_kp, &fe->d_cur_desc, &fe->d_cur_count, &dcap, &nb);
     if (s) return s;
-    s = kfs_orb_fetch_results(fe->orb, kp_out, desc_out, capacity, n_out);
-    fe->cur_n = *n_out < dcap ? *n_out : dcap;
     fe->cur_w = w; fe->cur_h = h;
+    return KFS_OK;
+}
+
+kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t *image, size_t step, int w, int h, int channels,
+                                         const uint8_t *mask, size_t mask_step,
+                                         kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out)
+{
+    if (!fe || !n_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle or n_out is NULL");
+    *n_out = 0;
+    if (channels != 1 && channels != 3) KFS_FAIL(KFS_ERR_UNSUPPORTED, "ExtractFeatures: %d channels (the reference handles 1 or 3, VisualOdometry.cpp:27)", channels);
+    if (w < 0 || h < 0 || capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "negative size");
+    if (w == 0 || h == 0) { fe->cur_n = 0; return KFS_OK; }
+    if (capacity > 0 && (!kp_out || !desc_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
+    KfsDeviceGuard guard(fe->device);
+    kfs_status s = fe_enqueue_extract(fe, image, step, w, h, channels, mask, mask_step, "ExtractFeatures");
+    if (s) return s;
+    s = kfs_orb_fetch_results(fe->orb, kp_out, desc_out, capacity, n_out);
+    fe->cur_n = *n_out < fe->cap ? *n_out : fe->cap;
     return s;
 }
 
@@ -381,6 +393,45 @@ kfs_status kfs_frontend_set_keyframe(kfs_frontend *fe, const uint8_t *desc, cons
     return KFS_OK;
 }
 
+// kNN against keyframe `kf` + ratio test / back-projection + the device-to-host copies of the count and the lists; nothing
+// synchronises.  count_on_device: `nt` is only a capacity, the live row count is *d_cnt (a frame whose extraction is still in
+// flight).
+static kfs_status fe_enqueue_match(kfs_frontend *fe, KfSlot *kf, const kfs_keypoint *d_kp, const uint8_t *d_desc, const int *d_cnt, int nt,
+                                   bool count_on_device, const double *intrinsics, float ratio, int capacity,
+                                   kfs_dmatch *matches_out, double *points3d_out, double *points2d_out)
+{
+    // the reference indexes knnMatches[i][1] unguarded (:46): with fewer than 2 current keypoints it is undefined there;
+    // here such rows simply never pass
+    kfs_bf_pair pair;
+    pair.query = kf->desc; pair.nq = kf->n; pair.d_nq = nullptr;
+    pair.train = d_desc; pair.nt = nt; pair.d_nt = count_on_device ? d_cnt : nullptr;
+    pair.out = fe->d_knn; pair.counts = nullptr;
+    cudaStream_t st = fe->stream;
+    kfs_status s = kfs_bf_knn_match_pairs_device(fe->bf, &pair, 1, 2);
+    if (s) return s;
+    fe->launches += kfs_bf_last_launches(fe->bf) > 0 ? 1 : 0;
+    TrackArgs A;
+    A.knn = fe->d_knn; A.kf_kp = kf->kp; A.cur_kp = d_kp; A.d_ncur = d_cnt;
+    A.depth = kf->depth; A.depth_pitch = kf->w; A.depth_w = kf->w; A.depth_h = kf->h;
+    A.fx = intrinsics[0]; A.fy = intrinsics[1]; A.cx = intrinsics[2]; A.cy = intrinsics[3];
+    A.ratio = ratio; A.nq = kf->n; A.n_cur = nt;
+    A.capacity = capacity < fe->cap ? capacity : fe->cap;
+    A.matches = fe->d_good; A.p3d = fe->d_p3d; A.p2d = fe->d_p2d; A.n_out = fe->d_nout;
+    k_ratio_backproject<<<1, 1024, 0, st>>>(A);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_ratio_backproject launch: %s", cudaGetErrorString(e));
+    fe->launches++;
+    // one round trip: the survivor count and the lists' upper bound (at most one survivor per keyframe row) travel together
+    KFS_CUDA_TRY(cudaMemcpyAsync(fe->h_nout, fe->d_nout, sizeof(int), cudaMemcpyDeviceToHost, st));
+    const int m = kf->n < A.capacity ? kf->n : A.capacity;
+    if (m > 0) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(matches_out, fe->d_good, (size_t)m * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, st));
+        KFS_CUDA_TRY(cudaMemcpyAsync(points3d_out, fe->d_p3d, (size_t)m * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        KFS_CUDA_TRY(cudaMemcpyAsync(points2d_out, fe->d_p2d, (size_t)m * 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    }
+    return KFS_OK;
+}
+
 kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc, const kfs_keypoint *cur_kp, int n_cur,
                                        const double *intrinsics, float ratio,
                                        kfs_dmatch *matches_out, double *points3d_out, double *points2d_out,
@@ -412,38 +463,53 @@ kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc
     }
     fe->launches = 0;
     if (kf->n == 0) return KFS_OK; // knnMatch of an empty query: no rows
-    // the reference indexes knnMatches[i][1] unguarded (:46): with fewer than 2 current keypoints it is undefined there;
-    // here such rows simply never pass
-    kfs_bf_pair pair;
-    pair.query = kf->desc; pair.nq = kf->n; pair.d_nq = nullptr;
-    pair.train = d_desc; pair.nt = nt; pair.d_nt = nullptr;
-    pair.out = fe->d_knn; pair.counts = nullptr;
-    kfs_status s = kfs_bf_knn_match_pairs_device(fe->bf, &pair, 1, 2);
+    kfs_status s = fe_enqueue_match(fe, kf, d_kp, d_desc, d_cnt, nt, false, intrinsics, ratio, capacity, matches_out, points3d_out, points2d_out);
     if (s) return s;
-    fe->launches += kfs_bf_last_launches(fe->bf) > 0 ? 1 : 0;
-    TrackArgs A;
-    A.knn = fe->d_knn; A.kf_kp = kf->kp; A.cur_kp = d_kp; A.d_ncur = d_cnt;
-    A.depth = kf->depth; A.depth_pitch = kf->w; A.depth_w = kf->w; A.depth_h = kf->h;
-    A.fx = intrinsics[0]; A.fy = intrinsics[1]; A.cx = intrinsics[2]; A.cy = intrinsics[3];
-    A.ratio = ratio; A.nq = kf->n; A.n_cur = nt;
-    A.capacity = capacity < fe->cap ? capacity : fe->cap;
-    A.matches = fe->d_good; A.p3d = fe->d_p3d; A.p2d = fe->d_p2d; A.n_out = fe->d_nout;
-    k_ratio_backproject<<<1, 1024, 0, st>>>(A);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_ratio_backproject launch: %s", cudaGetErrorString(e));
-    fe->launches++;
-    // one round trip: the survivor count and the lists' upper bound (at most one survivor per keyframe row) travel together
-    KFS_CUDA_TRY(cudaMemcpyAsync(fe->h_nout, fe->d_nout, sizeof(int), cudaMemcpyDeviceToHost, st));
-    const int m = kf->n < A.capacity ? kf->n : A.capacity;
-    if (m > 0) {
-        KFS_CUDA_TRY(cudaMemcpyAsync(matches_out, fe->d_good, (size_t)m * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, st));
-        KFS_CUDA_TRY(cudaMemcpyAsync(points3d_out, fe->d_p3d, (size_t)m * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
-        KFS_CUDA_TRY(cudaMemcpyAsync(points2d_out, fe->d_p2d, (size_t)m * 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-    }
     KFS_CUDA_TRY(cudaStreamSynchronize(st));
     const int n = *fe->h_nout;
     *n_out = n;
     if (n > capacity) KFS_FAIL(KFS_ERR_CAPACITY, "match_features: %d survivors, output capacity %d", n, capacity);
+    return KFS_OK;
+}
+
+// VisualOdometry::Track's front half (:138 ExtractFeatures, :144 MatchFeatures) in ONE call with ONE host synchronisation:
+// upload, colour conversion, the ORB chain, kNN against the cached keyframe, ratio test + back-projection and every
+// device-to-host copy are enqueued back to back.  Without a cached keyframe only the extraction runs (*n_matches_out = -1).
+kfs_status kfs_frontend_track(kfs_frontend *fe, const uint8_t *image, size_t step, int w, int h, int channels,
+                              const uint8_t *mask, size_t mask_step, const double *intrinsics, float ratio,
+                              kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out,
+                              kfs_dmatch *matches_out, double *points3d_out, double *points2d_out, int match_capacity, int *n_matches_out)
+{
+    if (!fe || !n_out || !n_matches_out || !intrinsics) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle, intrinsics, n_out or n_matches_out is NULL");
+    *n_out = 0; *n_matches_out = -1;
+    if (capacity < 0 || match_capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "negative capacity");
+    if (capacity > 0 && (!kp_out || !desc_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
+    if (match_capacity > 0 && (!matches_out || !points3d_out || !points2d_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "match output buffers are NULL");
+    if (intrinsics[0] == 0.0 || intrinsics[1] == 0.0) KFS_FAIL(KFS_ERR_INVALID_ARG, "fx or fy is zero");
+    KfsDeviceGuard guard(fe->device);
+    cudaStream_t st = fe->stream;
+    kfs_status s = fe_enqueue_extract(fe, image, step, w, h, channels, mask, mask_step, "Track");
+    if (s) return s;
+    const int cp = capacity < fe->cap ? capacity : fe->cap;
+    KFS_CUDA_TRY(cudaMemcpyAsync(fe->h_nout + 1, fe->d_cur_count, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (cp > 0) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(kp_out, fe->d_cur_kp, (size_t)cp * sizeof(kfs_keypoint), cudaMemcpyDeviceToHost, st));
+        KFS_CUDA_TRY(cudaMemcpyAsync(desc_out, fe->d_cur_desc, (size_t)cp * 32, cudaMemcpyDeviceToHost, st));
+    }
+    KfSlot *kf = fe_newest(fe);
+    const bool matched = kf && kf->n > 0;
+    if (matched) {
+        s = fe_enqueue_match(fe, kf, fe->d_cur_kp, fe->d_cur_desc, fe->d_cur_count, fe->cap, true, intrinsics, ratio, match_capacity,
+                             matches_out, points3d_out, points2d_out);
+        if (s) return s;
+    }
+    KFS_CUDA_TRY(cudaStreamSynchronize(st));
+    const int n = fe->h_nout[1];
+    *n_out = n;
+    fe->cur_n = n < fe->cap ? n : fe->cap;
+    if (kf) *n_matches_out = matched ? fe->h_nout[0] : 0;
+    if (n > cp) KFS_FAIL(KFS_ERR_CAPACITY, "Track: %d keypoints, output capacity %d (handle capacity %d)", n, capacity, fe->cap);
+    if (matched && fe->h_nout[0] > match_capacity) KFS_FAIL(KFS_ERR_CAPACITY, "Track: %d survivors, output capacity %d", fe->h_nout[0], match_capacity);
     return KFS_OK;
 }
 

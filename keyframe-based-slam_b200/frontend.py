@@ -388,6 +388,33 @@ class TrackerFrontEnd:
                                                     intr, ratio, m.ctypes.data, p3.ctypes.data, p2.ctypes.data, cap, C.byref(n)))
         return p3[:n.value].copy(), p2[:n.value].copy(), m[:n.value].copy()
 
+    def track(self, rgb, K, mask=None, ratio=0.6):
+        """ExtractFeatures + MatchFeatures of one frame in one call / one synchronisation (VisualOdometry::Track's front half).
+        -> (keypoints, descriptors, points3D, points2D, matches); the last three are None while no keyframe is cached."""
+        rgb = np.asarray(rgb)
+        assert rgb.dtype == np.uint8 and rgb.ndim in (2, 3)
+        rgb = np.ascontiguousarray(rgb)
+        ch = 1 if rgb.ndim == 2 else rgb.shape[2]
+        h, w = rgb.shape[:2]
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, dtype=np.uint8)
+        K = np.asarray(K, dtype=np.float64)
+        intr = (C.c_double * 4)(K[0, 0], K[1, 1], K[0, 2], K[1, 2])
+        cap = self.capacity
+        kp = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        m = np.zeros(cap, DM_DTYPE)
+        p3 = np.zeros((cap, 3), np.float64)
+        p2 = np.zeros((cap, 2), np.float64)
+        n, nm = C.c_int(), C.c_int()
+        N.check(N.lib().kfs_frontend_track(self._h, rgb.ctypes.data, rgb.strides[0], w, h, ch, _ptr(mask), mask.strides[0] if mask is not None else 0,
+                                           intr, ratio, kp.ctypes.data, desc.ctypes.data, cap, C.byref(n),
+                                           m.ctypes.data, p3.ctypes.data, p2.ctypes.data, cap, C.byref(nm)))
+        k = min(n.value, cap)
+        if nm.value < 0:
+            return kp[:k].copy(), desc[:k].copy(), None, None, None
+        return kp[:k].copy(), desc[:k].copy(), p3[:nm.value].copy(), p2[:nm.value].copy(), m[:nm.value].copy()
+
     # ---- keyframe window (Map::GetNKeyFrames, /root/reference/src/lib/Map.cpp:72-78) ----
     def setWindow(self, window):
         """Keep the last `window` keyframes on the device (drops the cached ones)."""

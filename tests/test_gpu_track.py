@@ -99,3 +99,36 @@ def test_track_720p_nf3000_reference_configuration(kfs, oracle):
     got = fe.matchFeatures(K7)
     ref = oracle.match_features(knn, rka, rkb, depth, K7, 0.6)
     assert len(ref[2]) > 300 and all(np.array_equal(x, y) for x, y in zip(got, ref))
+
+
+def test_track_one_call_per_frame(kfs, oracle):
+    """kfs_frontend_track = ExtractFeatures + MatchFeatures of a frame in one call / one synchronisation: a 6-frame sequence
+    with a keyframe promotion in the middle, against the two-call path's oracle (detect_and_compute, knn_match, match_features)."""
+    fe = kfs.TrackerFrontEnd(nfeatures=800)
+    P = oracle.orb_params(nfeatures=800)
+    depth = [make_depth(480, 640, 70 + i) for i in range(2)]
+    frames = [make_rgb(480, 640, 61, shift=s) for s in (0, 2, 4, 7, 9, 12)]
+    ref = [oracle.detect_and_compute(oracle.rgb2gray(f), None, P) for f in frames]
+    kf = None
+    for i, f in enumerate(frames):
+        kp, desc, p3, p2, m = fe.track(f, K)
+        assert np.array_equal(kp, ref[i][0]) and np.array_equal(desc, ref[i][1])
+        if kf is None:
+            assert m is None                       # no keyframe yet: extraction only
+        else:
+            knn, _ = oracle.knn_match(ref[kf][1], ref[i][1], 2)
+            r3, r2, rm = oracle.match_features(knn, ref[kf][0], ref[i][0], depth[0 if kf == 0 else 1], K, 0.6)
+            assert len(rm) > 30 and np.array_equal(m, rm) and np.array_equal(p3, r3) and np.array_equal(p2, r2)
+        if i in (0, 3):                            # this frame becomes the keyframe (VisualOdometry.cpp:105-123)
+            fe.promoteKeyframe(depth[0 if i == 0 else 1])
+            kf = i
+    # masked + gray input, and the two-call path agrees with the fused call on the same frame
+    gray = oracle.rgb2gray(frames[5])
+    mask = np.zeros((480, 640), np.uint8)
+    mask[50:400, 60:600] = 255
+    kp, desc, p3, p2, m = fe.track(gray, K, mask=mask, ratio=0.75)
+    k2, d2 = fe.extractFeatures(gray, mask)
+    q3, q2, qm = fe.matchFeatures(K, ratio=0.75)
+    assert np.array_equal(kp, k2) and np.array_equal(desc, d2) and np.array_equal(m, qm) and np.array_equal(p3, q3) and np.array_equal(p2, q2)
+    rk, rd = oracle.detect_and_compute(gray, mask, P)
+    assert np.array_equal(kp, rk) and np.array_equal(desc, rd)
