@@ -14,6 +14,7 @@
 #include <string.h>
 #include <stdlib.h>
 #include <vector>
+#include <algorithm>
 #include <new>
 
 #ifndef KFS_DK
@@ -236,6 +237,85 @@ __device__ __forceinline__ int kfs_atoms_add(int *p, int v)
     int r;
     asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
     return r;
+}
+
+// ======================================================================================================
+// a1.1 / a1.2  the whole pyramid in ONE launch (used when every level's region fits shared memory)
+// ======================================================================================================
+// A CTA owns one 32 x 16 tile of the COARSEST level and, on every finer level, the proportional tile.  It loads the level-0
+// region all of that depends on with one TMA box, then walks down the levels in shared memory: level l is computed from the
+// CTA's own copy of level l-1 (same 8.8 fixed-point arithmetic and tables as k_resize_generic), the part it owns is written to
+// global memory, the rest (a 1-2 px halo the next level needs) stays private.  The chained resize reads each level from
+// shared memory instead of HBM/L2 (2.85 instead of 4.71 MB per 720p frame) and a frame costs one launch instead of seven.
+// Regions (host-computed from the same tables, kfs_orb_plan_pyramid): per (tile, level) C = computed box, O = owned box.
+struct PyrDev {
+    int nlevels, box_bytes;
+    int soff[KFS_MAX_LEVELS], spitch[KFS_MAX_LEVELS];      // shared-memory offset / row pitch of level l's region
+    int sw[KFS_MAX_LEVELS], sh[KFS_MAX_LEVELS];            // level sizes
+    uint8_t *dst[KFS_MAX_LEVELS];                          // level buffers (l >= 1)
+    long long dfs[KFS_MAX_LEVELS];
+    int dpitch[KFS_MAX_LEVELS];
+    const uint32_t *xtab[KFS_MAX_LEVELS], *ytab[KFS_MAX_LEVELS];
+    const short *rects;                                    // [tiles][nlevels][8]: C.x0, C.y0, C.w, C.h, O.x0, O.y0, O.w, O.h
+};
+
+struct PyrMap { CUtensorMap m; };
+// One launch instead of six dependent ones is what a single frame wants (20 instead of 36 us for the 720p pyramid); a full batch
+// keeps the per-level kernels, whose PRMT tap gather is 2.2x cheaper per pixel than this kernel's byte loads from shared memory.
+constexpr int PYR_FUSED_MAX_FRAMES = 4;
+
+__global__ void __launch_bounds__(256)
+k_pyramid(const __grid_constant__ PyrDev P, const __grid_constant__ PyrMap map0, int frame0, int mask_mode)
+{
+    extern __shared__ __align__(128) uint8_t s_pyr[];
+    __shared__ __align__(8) uint64_t s_bar;
+    const int tid = threadIdx.x, f = blockIdx.y + frame0;
+    const short *R = P.rects + (size_t)blockIdx.x * P.nlevels * 8;
+    if (tid == 0) kfs_mbar_init(&s_bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+        kfs_mbar_expect_tx(&s_bar, (uint32_t)P.box_bytes);
+        kfs_tma_load_3d(s_pyr + P.soff[0], &map0.m, R[0], R[1], f, &s_bar); // R[0] is a multiple of 16 (plan)
+    }
+    kfs_mbar_wait(&s_bar, 0);
+    for (int l = 1; l < P.nlevels; l++) {
+        const short *Rc = R + 8 * l, *Rp = Rc - 8;
+        const int cx0 = Rc[0], cy0 = Rc[1], cw4 = Rc[2] >> 2, ch = Rc[3];
+        const int ox0 = Rc[4], oy0 = Rc[5], ox1 = ox0 + Rc[6], oy1 = oy0 + Rc[7];
+        const int px0 = Rp[0], py0 = Rp[1];
+        const uint8_t *src = s_pyr + P.soff[l - 1];
+        uint8_t *dsm = s_pyr + P.soff[l];
+        const int sp = P.spitch[l - 1], dp = P.spitch[l];
+        const int swm = P.sw[l - 1] - 1, shm = P.sh[l - 1] - 1;
+        const uint32_t *xt = P.xtab[l], *yt = P.ytab[l];
+        uint8_t *dg = P.dst[l] + (long long)f * P.dfs[l];
+        const int dgp = P.dpitch[l];
+        for (int i = tid; i < cw4 * ch; i += 256) {
+            const int gy = i / cw4, gx = (i - gy * cw4) * 4;
+            const int y = cy0 + gy, x = cx0 + gx;
+            const uint32_t ye = __ldg(yt + y);
+            const int y0 = ye & 0xffffu, y1 = min(y0 + 1, shm);
+            const uint32_t n1 = ye >> 16, n0 = 256u - n1;
+            const uint8_t *r0 = src + (y0 - py0) * sp - px0, *r1 = src + (y1 - py0) * sp - px0;
+            const uint4 xe4 = __ldg(reinterpret_cast<const uint4 *>(xt + x));
+            const uint32_t xe[4] = {xe4.x, xe4.y, xe4.z, xe4.w};
+            uint32_t outw = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int a0 = xe[j] & 0xffffu, a1 = min(a0 + 1, swm);
+                const uint32_t m1 = xe[j] >> 16, m0 = 256u - m1;
+                const uint32_t h0 = m0 * r0[a0] + m1 * r0[a1], h1 = m0 * r1[a0] + m1 * r1[a1];
+                outw |= ((n0 * h0 + n1 * h1 + 32768u) >> 16) << (8 * j);
+            }
+            if (mask_mode) { // keep only bytes == 255
+                const uint32_t t = ((outw & 0x7f7f7f7fu) + 0x01010101u) & outw & 0x80808080u;
+                outw = (t >> 7) * 255u;
+            }
+            *reinterpret_cast<uint32_t *>(dsm + gy * dp + gx) = outw;
+            if (y >= oy0 && y < oy1 && x >= ox0 && x < ox1) *reinterpret_cast<uint32_t *>(dg + (long long)y * dgp + x) = outw;
+        }
+        __syncthreads();
+    }
 }
 
 __global__ void __launch_bounds__(FAST_THREADS)
@@ -1056,6 +1136,7 @@ struct OrbGraph {
     cudaGraphExec_t exec;
 };
 
+struct PyrMapKeyStore { const uint8_t *base; long long fs; int pitch, h, bw, bh; };
 // Tensor maps of one kernel's tile shape + what they were encoded from
 struct MapCache {
     FastMaps maps;
@@ -1100,6 +1181,16 @@ struct kfs_orb {
     bool blur_fma = true;
     // TMA descriptors of the levels for k_fast (re-encoded only when a level's address / pitch / size changes)
     MapCache fmaps, bmaps;          // k_fast's 144 x 70 boxes, k_blur7's 160 x 64 boxes
+    // fused pyramid (k_pyramid): host copies of the resize tables, the region plan, level-0 tensor maps of image / mask
+    std::vector<uint32_t> h_xtab[KFS_MAX_LEVELS], h_ytab[KFS_MAX_LEVELS];
+    bool pyr_fused = false;
+    int pyr_mode = 1;               // KFS_ORB_FUSED_PYRAMID: 0 = never, 1 = calls of at most PYR_FUSED_MAX_FRAMES frames, 2 = always
+    PyrDev pyr_dev;
+    short *d_rects = nullptr;
+    int pyr_tiles = 0, pyr_box_w = 0, pyr_box_h = 0;
+    size_t pyr_smem = 0;
+    PyrMap pyr_map_img, pyr_map_mask;
+    PyrMapKeyStore pyr_key_img = {}, pyr_key_mask = {};
     int tma_state = 0;              // 0 = not probed yet, 1 = cuTensorMapEncodeTiled available, -1 = not (LDG path)           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
     cudaEvent_t ev[KFS_STAGE_COUNT + 1];
     bool ev_made = false;
@@ -1145,9 +1236,13 @@ static void kfs_orb_drop_graphs(kfs_orb *o)
 static void kfs_orb_free_arena(kfs_orb *o)
 {
     kfs_orb_drop_graphs(o);
+    if (o->d_rects) { cudaFree(o->d_rects); o->d_rects = nullptr; }
+    o->pyr_fused = false;
     if (o->arena) { cudaFree(o->arena); o->arena = nullptr; }
     o->W = o->H = o->B = 0;
 }
+
+static kfs_status kfs_orb_plan_pyramid(kfs_orb *o);
 
 static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_mask)
 {
@@ -1252,6 +1347,7 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
             for (int tx = 0; tx < D.tiles_x; tx++) ttab.push_back(((uint32_t)l << 24) | ((uint32_t)ty << 12) | (uint32_t)tx);
         if (l > 0) {
             kfs_axis_table(o->lw[l - 1], o->lw[l], (int)kfs_align_up((size_t)o->lw[l], 4), tab);
+            o->h_xtab[l] = tab;
             KFS_CUDA_TRY(cudaMemcpyAsync(o->xtab[l], tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, o->stream));
             KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
             {   // group tables of the fast path: {a0, sel, 0, 0} {M0..M3}; usable when every group's taps fit 8 bytes
@@ -1278,6 +1374,7 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
                 KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
             }
             kfs_axis_table(o->lh[l - 1], o->lh[l], o->lh[l], tab);
+            o->h_ytab[l] = tab;
             KFS_CUDA_TRY(cudaMemcpyAsync(o->ytab[l], tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, o->stream));
             KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
         }
@@ -1295,7 +1392,7 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     if (o->h_counts) { cudaFreeHost(o->h_counts); o->h_counts = nullptr; }
     KFS_CUDA_TRY(cudaMallocHost(&o->h_counts, sizeof(int) * (size_t)batch));
     o->W = w; o->H = h; o->B = batch; o->has_mask_alloc = need_mask;
-    return KFS_OK;
+    return kfs_orb_plan_pyramid(o);
 }
 
 #define KFS_LAUNCH_CHECK(o)                                                                     \
@@ -1335,6 +1432,102 @@ static kfs_encode_tiled_fn kfs_encode_tiled()
             cudaGetLastError();
     }
     return fn;
+}
+
+// Regions of the fused pyramid kernel (k_pyramid): tile (i, j) of the coarsest level owns, on every level l, the box between
+// the proportional boundaries bx(l, i) .. bx(l, i+1) (multiples of 4 in x) and by(l, j) .. by(l, j+1); what it has to COMPUTE on
+// level l is the bounding box of that and of the pre-image of what it computes on level l+1 (read off the resize tables).
+// Leaves o->pyr_fused false when a level-0 region does not fit one TMA box / the shared-memory budget (large scale factors).
+static kfs_status kfs_orb_plan_pyramid(kfs_orb *o)
+{
+    o->pyr_fused = false;
+    const int L = o->nlevels_active;
+    const char *env = getenv("KFS_ORB_FUSED_PYRAMID");
+    o->pyr_mode = env ? atoi(env) : 1;
+    if (L < 2 || o->pyr_mode <= 0) return KFS_OK;
+    const int TW = 32, TH = 16;
+    const int Wc = o->lw[L - 1], Hc = o->lh[L - 1];
+    if (Wc < 1 || Hc < 1) return KFS_OK;
+    const int nx = kfs_div_up(Wc, TW), ny = kfs_div_up(Hc, TH);
+    auto bx = [&](int l, int i) { return i >= nx ? (int)kfs_align_up((size_t)o->lw[l], 4) : (int)(((long long)i * TW * o->lw[l] / Wc) & ~3LL); };
+    auto by = [&](int l, int j) { return j >= ny ? o->lh[l] : (int)((long long)j * TH * o->lh[l] / Hc); };
+    struct Box { int x0, y0, x1, y1; };
+    std::vector<short> rects((size_t)nx * ny * L * 8, 0);
+    int maxw[KFS_MAX_LEVELS] = {}, maxh[KFS_MAX_LEVELS] = {};
+    for (int j = 0; j < ny; j++)
+        for (int i = 0; i < nx; i++) {
+            Box C[KFS_MAX_LEVELS], O[KFS_MAX_LEVELS];
+            C[L - 1] = O[L - 1] = Box{bx(L - 1, i), by(L - 1, j), bx(L - 1, i + 1), by(L - 1, j + 1)};
+            for (int l = L - 1; l >= 1; l--) {
+                const std::vector<uint32_t> &xt = o->h_xtab[l], &yt = o->h_ytab[l];
+                Box Pm;
+                Pm.x0 = (int)(xt[(size_t)C[l].x0] & 0xffffu);
+                Pm.x1 = std::min((int)(xt[(size_t)C[l].x1 - 1] & 0xffffu) + 1, o->lw[l - 1] - 1) + 1;
+                Pm.y0 = (int)(yt[(size_t)C[l].y0] & 0xffffu);
+                Pm.y1 = std::min((int)(yt[(size_t)C[l].y1 - 1] & 0xffffu) + 1, o->lh[l - 1] - 1) + 1;
+                if (l - 1 >= 1) {
+                    O[l - 1] = Box{bx(l - 1, i), by(l - 1, j), bx(l - 1, i + 1), by(l - 1, j + 1)};
+                    Box U = O[l - 1];
+                    if (U.x1 <= U.x0 || U.y1 <= U.y0) U = Pm;
+                    U.x0 = std::min(U.x0, Pm.x0) & ~3; U.y0 = std::min(U.y0, Pm.y0);
+                    U.x1 = std::min((std::max(U.x1, Pm.x1) + 3) & ~3, (int)kfs_align_up((size_t)o->lw[l - 1], 4));
+                    U.y1 = std::max(U.y1, Pm.y1);
+                    C[l - 1] = U;
+                } else {
+                    Pm.x0 &= ~15; // the TMA box has to start on a 16-byte boundary in global memory
+                    C[0] = Pm; O[0] = Box{0, 0, 0, 0};
+                }
+            }
+            for (int l = 0; l < L; l++) {
+                short *r = &rects[(((size_t)j * nx + i) * L + l) * 8];
+                r[0] = (short)C[l].x0; r[1] = (short)C[l].y0; r[2] = (short)(C[l].x1 - C[l].x0); r[3] = (short)(C[l].y1 - C[l].y0);
+                r[4] = (short)O[l].x0; r[5] = (short)O[l].y0; r[6] = (short)std::max(O[l].x1 - O[l].x0, 0); r[7] = (short)std::max(O[l].y1 - O[l].y0, 0);
+                if (r[2] <= 0 || r[3] <= 0) return KFS_OK; // degenerate geometry: keep the per-level kernels
+                maxw[l] = std::max(maxw[l], (int)r[2]); maxh[l] = std::max(maxh[l], (int)r[3]);
+            }
+        }
+    PyrDev &P = o->pyr_dev;
+    memset(&P, 0, sizeof(P));
+    P.nlevels = L;
+    size_t off = 0;
+    for (int l = 0; l < L; l++) {
+        P.spitch[l] = (int)kfs_align_up((size_t)maxw[l], 16);
+        P.soff[l] = (int)off;
+        off = kfs_align_up(off + (size_t)P.spitch[l] * maxh[l], 128);
+        P.sw[l] = o->lw[l]; P.sh[l] = o->lh[l];
+        P.xtab[l] = o->xtab[l]; P.ytab[l] = o->ytab[l];
+    }
+    if (P.spitch[0] > 256 || maxh[0] > 256 || off > 160 * 1024) return KFS_OK; // one TMA box is at most 256 x 256; leave room for 1 CTA / SM at least
+    o->pyr_box_w = P.spitch[0]; o->pyr_box_h = maxh[0];
+    P.box_bytes = P.spitch[0] * maxh[0];
+    o->pyr_smem = off;
+    o->pyr_tiles = nx * ny;
+    if (o->d_rects) { cudaFree(o->d_rects); o->d_rects = nullptr; }
+    KFS_CUDA_TRY(cudaMalloc((void **)&o->d_rects, rects.size() * sizeof(short)));
+    KFS_CUDA_TRY(cudaMemcpyAsync(o->d_rects, rects.data(), rects.size() * sizeof(short), cudaMemcpyHostToDevice, o->stream));
+    KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
+    P.rects = o->d_rects;
+    if (off > 48 * 1024) KFS_CUDA_TRY(cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)off));
+    memset(&o->pyr_key_img, 0, sizeof(o->pyr_key_img));
+    memset(&o->pyr_key_mask, 0, sizeof(o->pyr_key_mask));
+    o->pyr_fused = true;
+    return KFS_OK;
+}
+
+// Level-0 tensor map of the fused pyramid kernel (image or mask source), re-encoded only when the source changes.
+static bool kfs_orb_pyramid_map(kfs_orb *o, PyrMap *pmap, PyrMapKeyStore *key, const uint8_t *base, int pitch, long long fs, int h)
+{
+    if (!kfs_encode_tiled()) return false;
+    if (key->base == base && key->fs == fs && key->pitch == pitch && key->h == h && key->bw == o->pyr_box_w && key->bh == o->pyr_box_h) return true;
+    if (((uintptr_t)base % 16) || (pitch % 16) || (fs % 16)) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)pitch, (cuuint64_t)h, 65535};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)fs};
+    const cuuint32_t box[3] = {(cuuint32_t)o->pyr_box_w, (cuuint32_t)o->pyr_box_h, 1}, estr[3] = {1, 1, 1};
+    if (kfs_encode_tiled()(&pmap->m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    key->base = base; key->fs = fs; key->pitch = pitch; key->h = h; key->bw = o->pyr_box_w; key->bh = o->pyr_box_h;
+    return true;
 }
 
 // (Re)builds the per-level tensor maps of one kernel's tile shape (box_w x box_h bytes).  KFS_ORB_TMA=0 forces the LDG path.
@@ -1381,7 +1574,23 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
             d_mask_in, (long long)mask_fs, (long long)mask_step, o->mpyr[0] + (size_t)f0 * o->lfs[0], o->lfs[0], o->lpitch[0], o->lw[0], o->lh[0]);
         KFS_LAUNCH_CHECK(o);
     }
-    for (int l = 1; l < L; l++) {
+    // the whole pyramid in one launch when the plan allows it (kfs_orb_plan_pyramid) and the level-0 source can be described
+    // by a tensor map; otherwise level by level
+    bool fused = o->pyr_fused && L >= 2 && (o->pyr_mode >= 2 || nb <= PYR_FUSED_MAX_FRAMES);
+    if (fused) fused = kfs_orb_pyramid_map(o, &o->pyr_map_img, &o->pyr_key_img, g.lv[0].img, g.lv[0].pitch, g.lv[0].img_fs, o->lh[0]);
+    if (fused && has_mask) fused = kfs_orb_pyramid_map(o, &o->pyr_map_mask, &o->pyr_key_mask, o->mpyr[0], o->lpitch[0], o->lfs[0], o->lh[0]);
+    if (fused) {
+        PyrDev P = o->pyr_dev;
+        for (int l = 1; l < L; l++) { P.dst[l] = o->pyr[l]; P.dfs[l] = o->lfs[l]; P.dpitch[l] = o->lpitch[l]; }
+        k_pyramid<<<dim3(o->pyr_tiles, nb), 256, o->pyr_smem, st>>>(P, o->pyr_map_img, f0, 0);
+        KFS_LAUNCH_CHECK(o);
+        if (has_mask) {
+            for (int l = 1; l < L; l++) P.dst[l] = o->mpyr[l];
+            k_pyramid<<<dim3(o->pyr_tiles, nb), 256, o->pyr_smem, st>>>(P, o->pyr_map_mask, f0, 1);
+            KFS_LAUNCH_CHECK(o);
+        }
+    }
+    for (int l = 1; l < L && !fused; l++) {
         const long long sfs = g.lv[l - 1].img_fs;
         const uint8_t *simg = g.lv[l - 1].img + (long long)f0 * sfs;
         const int spitch = g.lv[l - 1].pitch;

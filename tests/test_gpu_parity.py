@@ -278,7 +278,7 @@ def test_orb_graph_replay_same_handle_many_calls(kfs, oracle):
     for f in range(5):                       # eager, capture, replay, replay, replay
         check(frames[f])
     n_plain = orb.last_launches
-    assert n_plain >= 13                     # a replayed graph still reports the kernels it launched
+    assert n_plain >= 7                      # a replayed graph still reports the kernels it launched (7 with the one-launch pyramid)
     for f in range(4):                       # the masked chain is another graph
         check(frames[f], mask)
     assert orb.last_launches > n_plain
