@@ -519,10 +519,11 @@ __global__ void __launch_bounds__(SEL_THREADS)
 k_select_fast(const __grid_constant__ OrbDev g)
 {
     __shared__ int s_hist[256];
-    __shared__ int s_thr;
+    __shared__ int s_thr, s_ccount;
     const int l = blockIdx.x, f = blockIdx.y + g.frame0, tid = threadIdx.x, lane = tid & 31;
     const LevelDev &L = g.lv[l];
     if (L.list_cap == 0) return;
+    if (tid == 0) s_ccount = 0;
     const int n = min(g.raw_count[f * KFS_MAX_LEVELS + l], L.list_cap);
     const int target = 2 * L.quota;
     const uint32_t *raw = g.raw + (long long)f * g.list_fs + L.list_off;
@@ -559,7 +560,9 @@ k_select_fast(const __grid_constant__ OrbDev g)
     }
     if (target <= 0) thr = 256; // nothing is kept for a zero quota
     uint32_t *cand = g.cand_xy + (long long)f * g.list_fs + L.list_off;
-    int *ccount = g.cand_count + f * KFS_MAX_LEVELS + l;
+    // this CTA is the only writer of the level's candidate list: slots come from a shared-memory counter (a warp waits ~30
+    // cycles for its base instead of a global-atomic round trip per 32 corners); the count goes out once at the end
+    __syncthreads();
     for (int i0 = 0; i0 < n; i0 += SEL_THREADS) {
         const int i = i0 + tid;
         uint32_t v = 0;
@@ -568,11 +571,13 @@ k_select_fast(const __grid_constant__ OrbDev g)
         const uint32_t b = __ballot_sync(0xffffffffu, keep);
         if (b) {
             int base = 0;
-            if (lane == 0) base = atomicAdd(ccount, __popc(b));
+            if (lane == 0) base = atomicAdd(&s_ccount, __popc(b));
             base = __shfl_sync(0xffffffffu, base, 0);
             if (keep) cand[base + __popc(b & ((1u << lane) - 1u))] = v;
         }
     }
+    __syncthreads();
+    if (tid == 0) g.cand_count[f * KFS_MAX_LEVELS + l] = s_ccount;
 }
 
 // ======================================================================================================
@@ -593,15 +598,29 @@ k_harris(const __grid_constant__ OrbDev g)
         const uint32_t v = cand[i];
         const int x = v & 0xfff, y = (v >> 12) & 0xfff;
         const uint8_t *p = img + (long long)(y - 4) * pitch + (x - 4);
-        int r0[9], r1[9], r2[9];
+        // the 9 x 9 bytes arrive as 9 x 3 aligned words, all in flight at once (a keypoint is >= 31 px from every border, so the
+        // up to 3 bytes before / after the 9 of a row are inside the image); a row is then shifted into place
+        uint32_t w[9][3];
+        int sh[9];
 #pragma unroll
-        for (int j = 0; j < 9; j++) { r0[j] = __ldg(p + j); r1[j] = __ldg(p + pitch + j); }
+        for (int r = 0; r < 9; r++) {
+            const uintptr_t a = (uintptr_t)(p + (long long)r * pitch);
+            const uint32_t *q = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+            sh[r] = (int)(a & 3) * 8;
+            w[r][0] = __ldg(q); w[r][1] = __ldg(q + 1); w[r][2] = __ldg(q + 2);
+        }
+        int r0[9], r1[9], r2[9];
+        auto unpack = [&](int r, int *o) {
+            const uint32_t lo = __funnelshift_r(w[r][0], w[r][1], sh[r]), hi = __funnelshift_r(w[r][1], w[r][2], sh[r]);
+#pragma unroll
+            for (int j = 0; j < 4; j++) { o[j] = (lo >> (8 * j)) & 0xff; o[4 + j] = (hi >> (8 * j)) & 0xff; }
+            o[8] = (w[r][2] >> sh[r]) & 0xff;
+        };
+        unpack(0, r0); unpack(1, r1);
         int a = 0, b = 0, c = 0;
 #pragma unroll
         for (int i7 = 0; i7 < 7; i7++) {
-            const uint8_t *q = p + (long long)(i7 + 2) * pitch;
-#pragma unroll
-            for (int j = 0; j < 9; j++) r2[j] = __ldg(q + j);
+            unpack(i7 + 2, r2);
 #pragma unroll
             for (int j = 0; j < 7; j++) {
                 const int Ix = (r1[j + 2] - r1[j]) * 2 + (r0[j + 2] - r0[j]) + (r2[j + 2] - r2[j]);
@@ -651,9 +670,15 @@ k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
             if (tid < 256) s_hist[tid] = 0;
             __syncthreads();
             const uint32_t prefix = s_prefix;
-            for (int i = tid; i < n; i += SORT_THREADS) {
-                const uint32_t k = in_smem ? s_key[i] : kfs_float_key(resp[i]);
-                if ((k & hi_mask) == prefix) atomicAdd(&s_hist[(k >> shift) & 255u], 1);
+            // the responses of one level share their top byte(s): lanes with the same bin add once (MATCH.ANY) instead of
+            // queueing on one shared-memory word
+            for (int i0 = 0; i0 < n; i0 += SORT_THREADS) {
+                const int i = i0 + tid;
+                uint32_t k = 0;
+                if (i < n) k = in_smem ? s_key[i] : kfs_float_key(resp[i]);
+                const int bin = (i < n && (k & hi_mask) == prefix) ? (int)((k >> shift) & 255u) : -1;
+                const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+                if (bin >= 0 && lane == __ffs(peers) - 1) atomicAdd(&s_hist[bin], __popc(peers));
             }
             __syncthreads();
             if (tid < 32) {
@@ -907,7 +932,8 @@ k_blur7(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab,
 //      8 descriptor words; sample coordinates are rounded half-even by a magic add whose constant already carries the
 //      window origin and the shared-memory address, so a sample costs 4 FMUL + 2 FADD + 2 FADD + IMAD + IADD + LDS.U8
 constexpr int DK = KFS_DK;    // warps (keypoints in flight) per CTA
-constexpr int KPW = KFS_KPW;  // keypoints per warp, one after the other (the lane's sample pairs stay in registers)
+constexpr int KPW = KFS_KPW;  // keypoints per warp, one after the other (the lane's sample pairs stay in registers); a call of fewer
+                              // than KPW frames walks fewer (kernel argument kpw): one frame alone has 2000 warps instead of 250
 constexpr int BW_P = 64;      // pitch of the blurred window
 __device__ __align__(16) const float d_patf[1024] = {
 #include "orb_pattern.inc"
@@ -955,7 +981,7 @@ __device__ __forceinline__ void kfs_cp_async16_zfill(void *smem, const void *gme
 constexpr int IC_BYTES = 31 * 48, WB_BYTES = 37 * BW_P;
 
 __global__ void __launch_bounds__(32 * DK)
-k_describe(const __grid_constant__ OrbDev g)
+k_describe(const __grid_constant__ OrbDev g, int kpw)
 {
     // per warp, double-buffered: the 31 x 48 B un-blurred rows of the IC disc and the 37 x 64 B blurred window
     __shared__ __align__(16) uint8_t s_win[DK][2][IC_BYTES + WB_BYTES];
@@ -974,7 +1000,7 @@ k_describe(const __grid_constant__ OrbDev g)
     const int total = __shfl_sync(0xffffffffu, incl, KFS_MAX_LEVELS - 1);
     if (blockIdx.x == 0 && threadIdx.x == 0) g.n_out[f] = total;
     const int nvalid = min(total, g.cap_out);
-    if (blockIdx.x * (DK * KPW) >= nvalid) return; // whole CTA beyond the last keypoint
+    if (blockIdx.x * (DK * kpw) >= nvalid) return; // whole CTA beyond the last keypoint
     // this lane's 8 sample pairs (pair 32h + lane), kept in registers for all KPW keypoints of the warp
     float4 pat[8];
 #pragma unroll
@@ -984,8 +1010,8 @@ k_describe(const __grid_constant__ OrbDev g)
     // keypoint of round `it` of this warp: slot -> (level, rank) -> (x, y, response); xy = ~0 when there is none
     auto load_meta = [&](int it, uint32_t &xy, float &resp, int &level) {
         xy = 0xffffffffu; resp = 0.f; level = 0;
-        const int slot = (blockIdx.x * KPW + it) * DK + warp;
-        if (it < KPW && slot < nvalid) { // warp-uniform
+        const int slot = (blockIdx.x * kpw + it) * DK + warp;
+        if (it < kpw && slot < nvalid) { // warp-uniform
             level = __popc(__ballot_sync(0xffffffffu, incl <= slot) & ((1u << KFS_MAX_LEVELS) - 1u));
             const int excl = __shfl_sync(0xffffffffu, incl - cnt, level);
             const long long li = (long long)f * g.list_fs + g.lv[level].list_off + (slot - excl);
@@ -1026,8 +1052,8 @@ k_describe(const __grid_constant__ OrbDev g)
     load_meta(1, xy_n, resp_n, level_n);
 
 #pragma unroll 1
-    for (int it = 0; it < KPW; it++) {
-        const int slot0 = (blockIdx.x * KPW + it) * DK; // first slot of this round (block-uniform)
+    for (int it = 0; it < kpw; it++) {
+        const int slot0 = (blockIdx.x * kpw + it) * DK; // first slot of this round (block-uniform)
         if (slot0 >= nvalid) break;
         const int buf = it & 1;
         issue(xy_n, level_n, buf ^ 1);           // next keypoint's windows fly while this one is computed
@@ -1445,7 +1471,7 @@ static kfs_status kfs_orb_plan_pyramid(kfs_orb *o)
     const char *env = getenv("KFS_ORB_FUSED_PYRAMID");
     o->pyr_mode = env ? atoi(env) : 1;
     if (L < 2 || o->pyr_mode <= 0) return KFS_OK;
-    const int TW = 32, TH = 16;
+    const int TW = getenv("KFS_PYR_TW") ? atoi(getenv("KFS_PYR_TW")) : 32, TH = getenv("KFS_PYR_TH") ? atoi(getenv("KFS_PYR_TH")) : 16;
     const int Wc = o->lw[L - 1], Hc = o->lh[L - 1];
     if (Wc < 1 || Hc < 1) return KFS_OK;
     const int nx = kfs_div_up(Wc, TW), ny = kfs_div_up(Hc, TH);
@@ -1674,7 +1700,8 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
-    k_describe<<<dim3(kfs_div_up(g.cap_out, DK * KPW), nb), 32 * DK, 0, st>>>(g);
+    const int kpw = std::max(1, std::min(KPW, nb));
+    k_describe<<<dim3(kfs_div_up(g.cap_out, DK * kpw), nb), 32 * DK, 0, st>>>(g, kpw);
     KFS_LAUNCH_CHECK(o);
     if (kfs_stage_mark(o, KFS_STAGE_COUNT)) return KFS_ERR_CUDA;
     o->last_batch = f0 + nb;
