@@ -208,3 +208,9 @@ KFS_HD uint32_t kfs_float_key(float f)
 #endif
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
+#if defined(__CUDACC__)
+__device__ __forceinline__ float kfs_key_float(uint32_t k) // inverse of kfs_float_key (bit-exact, -0.f and NaN payloads included)
+{
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+#endif

@@ -643,13 +643,16 @@ k_harris(const __grid_constant__ OrbDev g)
 constexpr int SORT_THREADS = 512;
 // dynamic shared memory: key[N] | pos[N] | cpos[N] | cidx[N]  (u32 each), N = smem_n (host: 2*max quota + slack)
 __global__ void __launch_bounds__(SORT_THREADS)
-k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
+k_select_sort(const __grid_constant__ OrbDev g, int smem_n, int rows_cap)
 {
     extern __shared__ __align__(16) uint32_t s_dyn[];
     uint32_t *s_key = s_dyn, *s_pos = s_dyn + smem_n, *s_cpos = s_dyn + 2 * smem_n, *s_cidx = s_dyn + 3 * smem_n;
+    int *s_rowa = reinterpret_cast<int *>(s_dyn + 4 * smem_n), *s_rowb = s_rowa + rows_cap; // per image row: start / fill cursor
+    __shared__ int s_wsum[SORT_THREADS / 32];
     __shared__ int s_hist[256];
     __shared__ uint32_t s_prefix;
-    __shared__ int s_need, s_nkept;
+    __shared__ int s_need, s_nkept, s_small, s_ngather;
+    __shared__ uint32_t s_gather[32];
     const int l = blockIdx.x, f = blockIdx.y + g.frame0, tid = threadIdx.x, lane = tid & 31;
     const LevelDev &L = g.lv[l];
     if (L.list_cap == 0) return;
@@ -659,7 +662,7 @@ k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
     const bool in_smem = n <= smem_n;
     if (in_smem)
         for (int i = tid; i < n; i += SORT_THREADS) { s_key[i] = kfs_float_key(resp[i]); s_pos[i] = cand[i] & 0xffffffu; }
-    if (tid == 0) { s_prefix = 0; s_need = L.quota; s_nkept = 0; }
+    if (tid == 0) { s_prefix = 0; s_need = L.quota; s_nkept = 0; s_small = 0; s_ngather = 0; }
     __syncthreads();
     uint32_t thr_key = 0;
     if (L.quota <= 0) thr_key = 0xffffffffu;
@@ -701,9 +704,36 @@ k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
                 }
                 const uint32_t b = __ballot_sync(0xffffffffu, found >= 0);
                 const int src = __ffs(b) - 1;
-                if (b && lane == src) { s_prefix = prefix | ((uint32_t)found << shift); s_need = need - before; }
+                if (b && lane == src) {
+                    s_prefix = prefix | ((uint32_t)found << shift);
+                    s_need = need - before;
+                    s_small = (pass < 3 && s_hist[found] <= 32) ? s_hist[found] : 0;
+                }
             }
             __syncthreads();
+            const int small = s_small;
+            if (small > 0) {
+                // the bin that holds the quota-th response has at most 32 keys: one warp finishes the select on the full keys
+                // instead of one more histogram pass per remaining byte
+                const uint32_t pfx = s_prefix, msk = 0xffffffffu << shift;
+                for (int i = tid; i < n; i += SORT_THREADS) {
+                    const uint32_t k = in_smem ? s_key[i] : kfs_float_key(resp[i]);
+                    if ((k & msk) == pfx) s_gather[atomicAdd(&s_ngather, 1)] = k;
+                }
+                __syncthreads();
+                if (tid < 32) {
+                    const uint32_t mine = lane < small ? s_gather[lane] : 0u;
+                    const int need = s_need;
+                    int greater = 0, ge = 0;
+                    for (int j = 0; j < small; j++) {
+                        const uint32_t kj = __shfl_sync(0xffffffffu, mine, j);
+                        greater += kj > mine; ge += kj >= mine;
+                    }
+                    if (lane < small && greater < need && need <= ge) s_prefix = mine; // equal keys write the same value
+                }
+                __syncthreads();
+                break;
+            }
         }
         thr_key = s_prefix;
     }
@@ -727,19 +757,61 @@ k_select_sort(const __grid_constant__ OrbDev g, int smem_n)
             }
         }
         __syncthreads();
-        const int nk = s_nkept, nk4 = (nk + 3) & ~3;
-        for (int i = nk + tid; i < nk4; i += SORT_THREADS) s_cpos[i] = 0xffffffffu; // pad: never smaller than a real key
-        __syncthreads();
-        for (int e = tid; e < nk; e += SORT_THREADS) {
-            const uint32_t pi = s_cpos[e];
-            int rank = 0;
-#pragma unroll 2
-            for (int j = 0; j < nk4; j += 4) {
-                const uint4 p = *reinterpret_cast<const uint4 *>(s_cpos + j);
-                rank += (p.x < pi) + (p.y < pi) + (p.z < pi) + (p.w < pi);
+        const int nk = s_nkept;
+        // (y, x) order without the nk^2 compares: count the kept entries per image row, prefix-sum the rows, drop every entry
+        // into its row's segment (any order), then rank it inside the segment (a handful of entries) by x
+        const int nrows = L.h + 1; // entry L.h of the scan = nk: closes the last row's segment
+        if (nrows <= rows_cap) {
+            for (int i = tid; i < nrows; i += SORT_THREADS) s_rowa[i] = 0;
+            __syncthreads();
+            for (int e = tid; e < nk; e += SORT_THREADS) atomicAdd(&s_rowa[s_cpos[e] >> 12], 1);
+            __syncthreads();
+            {   // exclusive scan of s_rowa[0 .. nrows): thread = contiguous chunk, warp scan of the chunk sums, scan of the warp sums
+                const int chunk = (nrows + SORT_THREADS - 1) / SORT_THREADS, i0 = tid * chunk, i1 = min(i0 + chunk, nrows);
+                int sum = 0;
+                for (int i = i0; i < i1; i++) sum += s_rowa[i];
+                int incl = sum;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                if (lane == 31) s_wsum[tid >> 5] = incl;
+                __syncthreads();
+                if (tid < 32) {
+                    const int w = tid < SORT_THREADS / 32 ? s_wsum[tid] : 0;
+                    int wi = w;
+#pragma unroll
+                    for (int d = 1; d < SORT_THREADS / 32; d <<= 1) {
+                        const int v = __shfl_up_sync(0xffffffffu, wi, d);
+                        if (lane >= d) wi += v;
+                    }
+                    if (tid < SORT_THREADS / 32) s_wsum[tid] = wi - w;
+                }
+                __syncthreads();
+                int run = s_wsum[tid >> 5] + incl - sum;
+                for (int i = i0; i < i1; i++) { const int c = s_rowa[i]; s_rowa[i] = run; s_rowb[i] = run; run += c; }
             }
-            kxy[rank] = pi;
-            kresp[rank] = resp[s_cidx[e]];
+            __syncthreads();
+            for (int e = tid; e < nk; e += SORT_THREADS) s_pos[atomicAdd(&s_rowb[s_cpos[e] >> 12], 1)] = (uint32_t)e; // s_pos is free by now
+            __syncthreads();
+            for (int t = tid; t < nk; t += SORT_THREADS) {
+                const int e = (int)s_pos[t];
+                const uint32_t pi = s_cpos[e];
+                const int y = (int)(pi >> 12), seg0 = s_rowa[y], seg1 = s_rowa[y + 1];
+                int rank = seg0;
+                for (int u = seg0; u < seg1; u++) rank += s_cpos[s_pos[u]] < pi;
+                kxy[rank] = pi;
+                kresp[rank] = kfs_key_float(s_key[s_cidx[e]]);
+            }
+        } else { // more rows than the row arrays hold (cannot happen for heights the position encoding allows): nk^2 compares
+            for (int e = tid; e < nk; e += SORT_THREADS) {
+                const uint32_t pi = s_cpos[e];
+                int rank = 0;
+                for (int j = 0; j < nk; j++) rank += s_cpos[j] < pi;
+                kxy[rank] = pi;
+                kresp[rank] = kfs_key_float(s_key[s_cidx[e]]);
+            }
         }
         if (tid == 0) g.kept_count[f * KFS_MAX_LEVELS + l] = nk;
         return;
@@ -1681,13 +1753,14 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
     if (kfs_stage_mark(o, KFS_STAGE_SELECT_SORT)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
         int smem_n = (2 * maxq + maxq / 2 + 64 + 63) / 64 * 64;
-        if (smem_n > 13312) smem_n = 13312; // 16 B per entry -> 208 KB, under the 227 KB opt-in limit
-        const size_t dyn = (size_t)smem_n * 16;
+        if (smem_n > 11264) smem_n = 11264; // 16 B per entry -> 176 KB (+ <= 32 KB of row arrays), under the 227 KB opt-in limit
+        const int rows_cap = o->lh[0] + 2; // two row arrays (segment start / fill cursor) for the (y, x) ordering
+        const size_t dyn = (size_t)smem_n * 16 + (size_t)rows_cap * 8;
         if (dyn > 48 * 1024 && dyn != o->sort_smem_set) {
             KFS_CUDA_TRY(cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
             o->sort_smem_set = dyn;
         }
-        k_select_sort<<<dim3(L, nb), SORT_THREADS, dyn, st>>>(g, smem_n);
+        k_select_sort<<<dim3(L, nb), SORT_THREADS, dyn, st>>>(g, smem_n, rows_cap);
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_BLUR)) return KFS_ERR_CUDA;
