@@ -255,7 +255,10 @@ struct PyrDev {
     uint8_t *dst[KFS_MAX_LEVELS];                          // level buffers (l >= 1)
     long long dfs[KFS_MAX_LEVELS];
     int dpitch[KFS_MAX_LEVELS];
-    const uint32_t *xtab[KFS_MAX_LEVELS], *ytab[KFS_MAX_LEVELS];
+    const uint32_t *ytab[KFS_MAX_LEVELS];
+    const uint4 *xtab4[KFS_MAX_LEVELS];                    // k_resize's 4-pixel group tables
+    int tab_off, xt_off;                                   // shared-memory offset of the table slices; of the x tables inside them
+    int ytoff[KFS_MAX_LEVELS], xtoff[KFS_MAX_LEVELS];      // level l's slice: first y entry / first 4-pixel group
     const short *rects;                                    // [tiles][nlevels][8]: C.x0, C.y0, C.w, C.h, O.x0, O.y0, O.w, O.h
 };
 
@@ -264,55 +267,90 @@ struct PyrMap { CUtensorMap m; };
 // keeps the per-level kernels, whose PRMT tap gather is 2.2x cheaper per pixel than this kernel's byte loads from shared memory.
 constexpr int PYR_FUSED_MAX_FRAMES = 4;
 
-__global__ void __launch_bounds__(256)
+constexpr int PYR_THREADS = 512;
+__global__ void __launch_bounds__(PYR_THREADS)
 k_pyramid(const __grid_constant__ PyrDev P, const __grid_constant__ PyrMap map0, int frame0, int mask_mode)
 {
     extern __shared__ __align__(128) uint8_t s_pyr[];
     __shared__ __align__(8) uint64_t s_bar;
-    const int tid = threadIdx.x, f = blockIdx.y + frame0;
-    const short *R = P.rects + (size_t)blockIdx.x * P.nlevels * 8;
+    __shared__ short s_R[KFS_MAX_LEVELS * 8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, f = blockIdx.y + frame0;
+    const int L = P.nlevels;
     if (tid == 0) kfs_mbar_init(&s_bar, 1);
+    if (tid < L * 8) s_R[tid] = __ldg(P.rects + (size_t)blockIdx.x * L * 8 + tid);
     __syncthreads();
     if (tid == 0) {
         kfs_mbar_expect_tx(&s_bar, (uint32_t)P.box_bytes);
-        kfs_tma_load_3d(s_pyr + P.soff[0], &map0.m, R[0], R[1], f, &s_bar); // R[0] is a multiple of 16 (plan)
+        kfs_tma_load_3d(s_pyr + P.soff[0], &map0.m, s_R[0], s_R[1], f, &s_bar); // s_R[0] is a multiple of 16 (plan)
+    }
+    // While the level-0 box is in flight: this tile's slices of every level's resize tables go to shared memory, one warp per
+    // (level, table), so that the level loop below waits on no global load (it used to pay three dependent ones per level)
+    uint32_t *s_yt = reinterpret_cast<uint32_t *>(s_pyr + P.tab_off);
+    uint4 *s_xt = reinterpret_cast<uint4 *>(s_pyr + P.tab_off + P.xt_off);
+    for (int job = warp; job < 2 * (L - 1); job += PYR_THREADS / 32) {
+        const int l = 1 + (job >> 1);
+        const short *Rc = s_R + 8 * l;
+        if (job & 1) {
+            const uint4 *src = P.xtab4[l] + 2 * (Rc[0] >> 2);
+            uint4 *dst = s_xt + 2 * P.xtoff[l];
+            for (int j = lane; j < 2 * (Rc[2] >> 2); j += 32) dst[j] = __ldg(src + j);
+        } else {
+            const uint32_t *src = P.ytab[l] + Rc[1];
+            uint32_t *dst = s_yt + P.ytoff[l];
+            for (int j = lane; j < Rc[3]; j += 32) dst[j] = __ldg(src + j);
+        }
     }
     kfs_mbar_wait(&s_bar, 0);
-    for (int l = 1; l < P.nlevels; l++) {
-        const short *Rc = R + 8 * l, *Rp = Rc - 8;
+    __syncthreads();
+    for (int l = 1; l < L; l++) {
+        const short *Rc = s_R + 8 * l, *Rp = Rc - 8;
         const int cx0 = Rc[0], cy0 = Rc[1], cw4 = Rc[2] >> 2, ch = Rc[3];
         const int ox0 = Rc[4], oy0 = Rc[5], ox1 = ox0 + Rc[6], oy1 = oy0 + Rc[7];
         const int px0 = Rp[0], py0 = Rp[1];
         const uint8_t *src = s_pyr + P.soff[l - 1];
         uint8_t *dsm = s_pyr + P.soff[l];
         const int sp = P.spitch[l - 1], dp = P.spitch[l];
-        const int swm = P.sw[l - 1] - 1, shm = P.sh[l - 1] - 1;
-        const uint32_t *xt = P.xtab[l], *yt = P.ytab[l];
+        const int shm = P.sh[l - 1] - 1;
+        const uint32_t *yt = s_yt + P.ytoff[l];
+        const uint4 *xt4 = s_xt + 2 * P.xtoff[l];
         uint8_t *dg = P.dst[l] + (long long)f * P.dfs[l];
         const int dgp = P.dpitch[l];
-        for (int i = tid; i < cw4 * ch; i += 256) {
-            const int gy = i / cw4, gx = (i - gy * cw4) * 4;
-            const int y = cy0 + gy, x = cx0 + gx;
-            const uint32_t ye = __ldg(yt + y);
-            const int y0 = ye & 0xffffu, y1 = min(y0 + 1, shm);
-            const uint32_t n1 = ye >> 16, n0 = 256u - n1;
-            const uint8_t *r0 = src + (y0 - py0) * sp - px0, *r1 = src + (y1 - py0) * sp - px0;
-            const uint4 xe4 = __ldg(reinterpret_cast<const uint4 *>(xt + x));
-            const uint32_t xe[4] = {xe4.x, xe4.y, xe4.z, xe4.w};
-            uint32_t outw = 0;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const int a0 = xe[j] & 0xffffu, a1 = min(a0 + 1, swm);
-                const uint32_t m1 = xe[j] >> 16, m0 = 256u - m1;
-                const uint32_t h0 = m0 * r0[a0] + m1 * r0[a1], h1 = m0 * r1[a0] + m1 * r1[a1];
-                outw |= ((n0 * h0 + n1 * h1 + 32768u) >> 16) << (8 * j);
+        // lane = 4-pixel group (its table entry, selectors and word offset stay in registers), warp = every 16th output row:
+        // the arithmetic of k_resize (three words per source row, funnel shift, PRMT tap select, IDP.2A, two IMADs), the
+        // words coming from this CTA's copy of level l-1
+        for (int g4 = lane; g4 < cw4; g4 += 32) {
+            const int x = cx0 + 4 * g4;
+            const uint4 ta = xt4[2 * g4], tm = xt4[2 * g4 + 1];
+            const uint32_t off = ta.x - (uint32_t)px0, w0 = off >> 2;
+            const int shb = (int)(off & 3u) * 8;
+            const uint32_t s0 = ta.y, s1 = ta.y >> 8, s2 = ta.y >> 16, s3 = ta.y >> 24;
+            const bool xown = x >= ox0 && x < ox1;
+            const uint32_t *sw = reinterpret_cast<const uint32_t *>(src) + w0;
+            uint32_t *dw = reinterpret_cast<uint32_t *>(dsm) + g4;
+            uint32_t *gw = reinterpret_cast<uint32_t *>(dg + x);
+            const int spw = sp >> 2, dpw = dp >> 2, gpw = dgp >> 2;
+            for (int gy = warp; gy < ch; gy += PYR_THREADS / 32) {
+                const int y = cy0 + gy;
+                const uint32_t ye = yt[gy];
+                const int y0 = ye & 0xffffu, y1 = min(y0 + 1, shm);
+                const uint32_t n1 = ye >> 16, n0 = 256u - n1;
+                const uint32_t *r0 = sw + (y0 - py0) * spw, *r1 = sw + (y1 - py0) * spw;
+                const uint32_t a0 = r0[0], a1 = r0[1], a2 = r0[2]; // words past the region's last tap are never selected
+                const uint32_t b0 = r1[0], b1 = r1[1], b2 = r1[2];
+                const uint32_t lo0 = __funnelshift_r(a0, a1, shb), hi0 = __funnelshift_r(a1, a2, shb);
+                const uint32_t lo1 = __funnelshift_r(b0, b1, shb), hi1 = __funnelshift_r(b1, b2, shb);
+                const uint32_t S0 = n0 * __dp2a_lo(tm.x, kfs_prmt(lo0, hi0, s0), 0u) + (n1 * __dp2a_lo(tm.x, kfs_prmt(lo1, hi1, s0), 0u) + 32768u);
+                const uint32_t S1 = n0 * __dp2a_lo(tm.y, kfs_prmt(lo0, hi0, s1), 0u) + (n1 * __dp2a_lo(tm.y, kfs_prmt(lo1, hi1, s1), 0u) + 32768u);
+                const uint32_t S2 = n0 * __dp2a_lo(tm.z, kfs_prmt(lo0, hi0, s2), 0u) + (n1 * __dp2a_lo(tm.z, kfs_prmt(lo1, hi1, s2), 0u) + 32768u);
+                const uint32_t S3 = n0 * __dp2a_lo(tm.w, kfs_prmt(lo0, hi0, s3), 0u) + (n1 * __dp2a_lo(tm.w, kfs_prmt(lo1, hi1, s3), 0u) + 32768u);
+                uint32_t outw = kfs_prmt(kfs_prmt(S0, S1, 0x0062u), kfs_prmt(S2, S3, 0x0062u), 0x5410u);
+                if (mask_mode) { // keep only bytes == 255
+                    const uint32_t t = ((outw & 0x7f7f7f7fu) + 0x01010101u) & outw & 0x80808080u;
+                    outw = (t >> 7) * 255u;
+                }
+                dw[gy * dpw] = outw;
+                if (xown && y >= oy0 && y < oy1) gw[(long long)y * gpw] = outw;
             }
-            if (mask_mode) { // keep only bytes == 255
-                const uint32_t t = ((outw & 0x7f7f7f7fu) + 0x01010101u) & outw & 0x80808080u;
-                outw = (t >> 7) * 255u;
-            }
-            *reinterpret_cast<uint32_t *>(dsm + gy * dp + gx) = outw;
-            if (y >= oy0 && y < oy1 && x >= ox0 && x < ox1) *reinterpret_cast<uint32_t *>(dg + (long long)y * dgp + x) = outw;
         }
         __syncthreads();
     }
@@ -1543,7 +1581,7 @@ static kfs_status kfs_orb_plan_pyramid(kfs_orb *o)
     const char *env = getenv("KFS_ORB_FUSED_PYRAMID");
     o->pyr_mode = env ? atoi(env) : 1;
     if (L < 2 || o->pyr_mode <= 0) return KFS_OK;
-    const int TW = getenv("KFS_PYR_TW") ? atoi(getenv("KFS_PYR_TW")) : 32, TH = getenv("KFS_PYR_TH") ? atoi(getenv("KFS_PYR_TH")) : 16;
+    const int TW = 48, TH = 16; // 720p: 8 x 13 tiles of the coarsest level; 40 x 20, 32 x 16 and 48 x 24 are within 10 % of it
     const int Wc = o->lw[L - 1], Hc = o->lh[L - 1];
     if (Wc < 1 || Hc < 1) return KFS_OK;
     const int nx = kfs_div_up(Wc, TW), ny = kfs_div_up(Hc, TH);
@@ -1593,11 +1631,20 @@ static kfs_status kfs_orb_plan_pyramid(kfs_orb *o)
         P.soff[l] = (int)off;
         off = kfs_align_up(off + (size_t)P.spitch[l] * maxh[l], 128);
         P.sw[l] = o->lw[l]; P.sh[l] = o->lh[l];
-        P.xtab[l] = o->xtab[l]; P.ytab[l] = o->ytab[l];
+        P.xtab4[l] = o->xtab4[l]; P.ytab[l] = o->ytab[l];
+        if (l >= 1 && !o->resize_fast[l]) return KFS_OK; // scale factor > 2: the per-level generic kernel
     }
-    if (P.spitch[0] > 256 || maxh[0] > 256 || off > 160 * 1024) return KFS_OK; // one TMA box is at most 256 x 256; leave room for 1 CTA / SM at least
+    if (P.spitch[0] > 256 || maxh[0] > 256 || off > 140 * 1024) return KFS_OK; // one TMA box is at most 256 x 256; leave room for 1 CTA / SM at least
     o->pyr_box_w = P.spitch[0]; o->pyr_box_h = maxh[0];
     P.box_bytes = P.spitch[0] * maxh[0];
+    off += 16; // a row's third word may lie past the last region
+    {   // table slices: y entries of every level, then (16-byte aligned) the 2 x uint4 per 4-pixel group
+        P.tab_off = (int)off;
+        int n_y = 0, n_g = 0;
+        for (int l = 1; l < L; l++) { P.ytoff[l] = n_y; n_y += maxh[l]; P.xtoff[l] = n_g; n_g += maxw[l] / 4; }
+        P.xt_off = (int)kfs_align_up((size_t)n_y * 4, 16);
+        off += (size_t)P.xt_off + (size_t)n_g * 32;
+    }
     o->pyr_smem = off;
     o->pyr_tiles = nx * ny;
     if (o->d_rects) { cudaFree(o->d_rects); o->d_rects = nullptr; }
@@ -1605,7 +1652,7 @@ static kfs_status kfs_orb_plan_pyramid(kfs_orb *o)
     KFS_CUDA_TRY(cudaMemcpyAsync(o->d_rects, rects.data(), rects.size() * sizeof(short), cudaMemcpyHostToDevice, o->stream));
     KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
     P.rects = o->d_rects;
-    if (off > 48 * 1024) KFS_CUDA_TRY(cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)off));
+    if (o->pyr_smem > 48 * 1024) KFS_CUDA_TRY(cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)o->pyr_smem));
     memset(&o->pyr_key_img, 0, sizeof(o->pyr_key_img));
     memset(&o->pyr_key_mask, 0, sizeof(o->pyr_key_mask));
     o->pyr_fused = true;
@@ -1680,11 +1727,11 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
     if (fused) {
         PyrDev P = o->pyr_dev;
         for (int l = 1; l < L; l++) { P.dst[l] = o->pyr[l]; P.dfs[l] = o->lfs[l]; P.dpitch[l] = o->lpitch[l]; }
-        k_pyramid<<<dim3(o->pyr_tiles, nb), 256, o->pyr_smem, st>>>(P, o->pyr_map_img, f0, 0);
+        k_pyramid<<<dim3(o->pyr_tiles, nb), PYR_THREADS, o->pyr_smem, st>>>(P, o->pyr_map_img, f0, 0);
         KFS_LAUNCH_CHECK(o);
         if (has_mask) {
             for (int l = 1; l < L; l++) P.dst[l] = o->mpyr[l];
-            k_pyramid<<<dim3(o->pyr_tiles, nb), 256, o->pyr_smem, st>>>(P, o->pyr_map_mask, f0, 1);
+            k_pyramid<<<dim3(o->pyr_tiles, nb), PYR_THREADS, o->pyr_smem, st>>>(P, o->pyr_map_mask, f0, 1);
             KFS_LAUNCH_CHECK(o);
         }
     }
