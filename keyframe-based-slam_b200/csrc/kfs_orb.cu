@@ -193,6 +193,8 @@ constexpr int SC_W = 128, SC_H = FT_H + 2;
 constexpr int FAST_X0 = 20; // interior x origin of tile column 0; source origin 16 (+112k) keeps rows 16B-aligned
 constexpr int FAST_THREADS = 256;
 constexpr int FAST_MAXOUT = (FT_W / 2) * (FT_H / 2); // strict 3x3 maxima: at most one per 2x2 block
+constexpr int FT_HH = 31;      // tile height of the low-latency variant (k_fast<FT_HH>)
+constexpr int FAST_HALF_MAX_FRAMES = 2;
 static_assert(SC_H * 4 == FAST_THREADS, "one mask word per thread");
 static_assert(FAST_MAXOUT * 4 <= FS_P * FS_H, "survivor list aliases the source tile");
 
@@ -364,14 +366,19 @@ k_pyramid(const __grid_constant__ PyrDev P, const __grid_constant__ PyrMap map0,
     }
 }
 
+// TH = tile height: 62 for batches; 31 for calls of one or two frames, whose 388 tiles per 720p frame leave the SMs with 2-3 CTAs
+// of long dependent phases each (twice the CTAs of half the work finish sooner: one wave either way).
+template <int TH>
 __global__ void __launch_bounds__(FAST_THREADS)
 k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, const __grid_constant__ FastMaps maps)
 {
+    constexpr int FT_H = TH, FS_H = TH + 8, SC_H = TH + 2; // shadow the batch geometry above
+    static_assert(SC_H * 4 <= FAST_THREADS, "one mask word per thread");
     __shared__ __align__(128) uint8_t s_src[FS_P * FS_H + 16];
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ __align__(16) uint8_t s_sc[SC_W * SC_H];
     __shared__ uint16_t s_q[SC_W * SC_H];
-    __shared__ __align__(16) uint32_t s_mask[SC_H * 4];
+    __shared__ __align__(16) uint32_t s_mask[FAST_THREADS]; // rows past SC_H stay zero
     __shared__ int s_wsum[FAST_THREADS / 32];
     __shared__ int s_nout, s_gbase, s_ncorner;
 
@@ -1319,6 +1326,9 @@ struct kfs_orb {
     size_t arena_bytes = 0;
     int *counters = nullptr;        // raw_count | cand_count | kept_count | n_out
     uint32_t *tile_tab = nullptr;   // FAST tile -> level<<24 | tiy<<12 | tix
+    uint32_t *tile_tab_h = nullptr; // the same for tiles of height FT_HH (calls of one or two frames)
+    int total_tiles_h = 0;
+    bool fast_half = !(getenv("KFS_ORB_FAST_HALF") && atoi(getenv("KFS_ORB_FAST_HALF")) == 0);
     size_t counters_bytes = 0;
     OrbDev g;
     int last_batch = 0;
@@ -1329,7 +1339,7 @@ struct kfs_orb {
     bool use_graphs = true;
     bool blur_fma = true;
     // TMA descriptors of the levels for k_fast (re-encoded only when a level's address / pitch / size changes)
-    MapCache fmaps, bmaps;          // k_fast's 144 x 70 boxes, k_blur7's 160 x 64 boxes
+    MapCache fmaps, fmaps_h, bmaps; // k_fast's 144 x 70 (144 x 39 for half-height tiles) boxes, k_blur7's 160 x 64 boxes
     // fused pyramid (k_pyramid): host copies of the resize tables, the region plan, level-0 tensor maps of image / mask
     std::vector<uint32_t> h_xtab[KFS_MAX_LEVELS], h_ytab[KFS_MAX_LEVELS];
     bool pyr_fused = false;
@@ -1447,6 +1457,10 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     for (int l = 0; l < L; l++)
         if (list_cap[l] > 0) n_tiles_total += kfs_div_up(o->lw[l] - KFS_BORDER - FAST_X0, FT_W) * kfs_div_up(o->lh[l] - 2 * KFS_BORDER, FT_H);
     const size_t o_tt = take((size_t)(n_tiles_total + 1) * 4);
+    int n_tiles_half = 0;
+    for (int l = 0; l < L; l++)
+        if (list_cap[l] > 0) n_tiles_half += kfs_div_up(o->lw[l] - KFS_BORDER - FAST_X0, FT_W) * kfs_div_up(o->lh[l] - 2 * KFS_BORDER, FT_HH);
+    const size_t o_tth = take((size_t)(n_tiles_half + 1) * 4);
     int n_blur_tiles = 0;
     for (int l = 0; l < L; l++)
         if (list_cap[l] > 0) n_blur_tiles += kfs_div_up(o->lw[l], BT_W) * kfs_div_up(o->lh[l] - 2 * BT_Y0, BT_H);
@@ -1467,8 +1481,9 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     g.kept_count = g.cand_count + (size_t)batch * KFS_MAX_LEVELS; g.n_out = g.kept_count + (size_t)batch * KFS_MAX_LEVELS;
     g.kp = (kfs_keypoint *)(base + o_kp); g.desc = base + o_desc; g.rot = (float2 *)(base + o_rot); g.slot_meta = (uint32_t *)(base + o_meta);
     int tile_base = 0;
-    std::vector<uint32_t> tab, ttab, btab;
+    std::vector<uint32_t> tab, ttab, ttab_h, btab;
     o->tile_tab = (uint32_t *)(base + o_tt);
+    o->tile_tab_h = (uint32_t *)(base + o_tth);
     o->blur_tab = (uint32_t *)(base + o_bt);
     for (int l = 0; l < L; l++) {
         o->pyr[l] = base + o_pyr[l];
@@ -1495,6 +1510,9 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
         tile_base += D.tiles_x * D.tiles_y;
         for (int ty = 0; ty < D.tiles_y; ty++)
             for (int tx = 0; tx < D.tiles_x; tx++) ttab.push_back(((uint32_t)l << 24) | ((uint32_t)ty << 12) | (uint32_t)tx);
+        if (list_cap[l] > 0)
+            for (int ty = 0; ty < kfs_div_up(D.h - 2 * KFS_BORDER, FT_HH); ty++)
+                for (int tx = 0; tx < D.tiles_x; tx++) ttab_h.push_back(((uint32_t)l << 24) | ((uint32_t)ty << 12) | (uint32_t)tx);
         if (l > 0) {
             kfs_axis_table(o->lw[l - 1], o->lw[l], (int)kfs_align_up((size_t)o->lw[l], 4), tab);
             o->h_xtab[l] = tab;
@@ -1530,6 +1548,8 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
         }
     }
     g.total_tiles = tile_base;
+    o->total_tiles_h = (int)ttab_h.size();
+    if (!ttab_h.empty()) KFS_CUDA_TRY(cudaMemcpyAsync(o->tile_tab_h, ttab_h.data(), ttab_h.size() * 4, cudaMemcpyHostToDevice, o->stream));
     if (!ttab.empty()) {
         KFS_CUDA_TRY(cudaMemcpyAsync(o->tile_tab, ttab.data(), ttab.size() * 4, cudaMemcpyHostToDevice, o->stream));
         KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
@@ -1813,8 +1833,13 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
     }
     if (kfs_stage_mark(o, KFS_STAGE_FAST)) return KFS_ERR_CUDA;
     if (g.total_tiles > 0) {
-        kfs_orb_update_maps(o, o->fmaps, FS_P, FS_H);
-        kfs_launch_pdl(pdl, k_fast, dim3(g.total_tiles, nb), dim3(FAST_THREADS), 0, st, g, (const uint32_t *)o->tile_tab, o->fmaps.maps);
+        if (o->fast_half && nb <= FAST_HALF_MAX_FRAMES && o->total_tiles_h > 0) {
+            kfs_orb_update_maps(o, o->fmaps_h, FS_P, FT_HH + 8);
+            kfs_launch_pdl(pdl, k_fast<FT_HH>, dim3(o->total_tiles_h, nb), dim3(FAST_THREADS), 0, st, g, (const uint32_t *)o->tile_tab_h, o->fmaps_h.maps);
+        } else {
+            kfs_orb_update_maps(o, o->fmaps, FS_P, FS_H);
+            kfs_launch_pdl(pdl, k_fast<FT_H>, dim3(g.total_tiles, nb), dim3(FAST_THREADS), 0, st, g, (const uint32_t *)o->tile_tab, o->fmaps.maps);
+        }
         KFS_LAUNCH_CHECK(o);
     }
     if (kfs_stage_mark(o, KFS_STAGE_SELECT_HARRIS)) return KFS_ERR_CUDA;
