@@ -1707,10 +1707,19 @@ static kfs_status kfs_orb_plan_pyramid(kfs_orb *o)
     return KFS_OK;
 }
 
+// KFS_ORB_TMA=0 or a driver without cuTensorMapEncodeTiled: every kernel stays on its LDG path (and the pyramid on k_resize)
+static void kfs_orb_tma_probe(kfs_orb *o)
+{
+    if (o->tma_state != 0) return;
+    const char *e = getenv("KFS_ORB_TMA");
+    o->tma_state = (e && atoi(e) == 0) || !kfs_encode_tiled() ? -1 : 1;
+}
+
 // Level-0 tensor map of the fused pyramid kernel (image or mask source), re-encoded only when the source changes.
 static bool kfs_orb_pyramid_map(kfs_orb *o, PyrMap *pmap, PyrMapKeyStore *key, const uint8_t *base, int pitch, long long fs, int h)
 {
-    if (!kfs_encode_tiled()) return false;
+    kfs_orb_tma_probe(o);
+    if (o->tma_state <= 0) return false;
     if (key->base == base && key->fs == fs && key->pitch == pitch && key->h == h && key->bw == o->pyr_box_w && key->bh == o->pyr_box_h) return true;
     if (((uintptr_t)base % 16) || (pitch % 16) || (fs % 16)) return false;
     const cuuint64_t dims[3] = {(cuuint64_t)pitch, (cuuint64_t)h, 65535};
@@ -1726,10 +1735,7 @@ static bool kfs_orb_pyramid_map(kfs_orb *o, PyrMap *pmap, PyrMapKeyStore *key, c
 // (Re)builds the per-level tensor maps of one kernel's tile shape (box_w x box_h bytes).  KFS_ORB_TMA=0 forces the LDG path.
 static void kfs_orb_update_maps(kfs_orb *o, MapCache &C, int box_w, int box_h)
 {
-    if (o->tma_state == 0) {
-        const char *e = getenv("KFS_ORB_TMA");
-        o->tma_state = (e && atoi(e) == 0) || !kfs_encode_tiled() ? -1 : 1;
-    }
+    kfs_orb_tma_probe(o);
     C.maps.enabled = o->tma_state > 0;
     if (o->tma_state < 0) return;
     const OrbDev &g = o->g;
