@@ -4,9 +4,11 @@
 // not vendor).  Every kernel carries a leading batch dimension (blockIdx.y / .z = frame) so that one
 // launch covers a whole batch of frames; nothing on this path ever goes back to the host for a count.
 //
-// Kernel chain per batch (DESIGN.md §3):
-//   k_mask_binarise*  k_resize x(L-1) [x2 with a mask]  k_fast  k_select_fast  k_harris  k_select_sort
-//   k_describe (orientation + blur + rBRIEF)
+// Kernel chain per batch (DESIGN.md §4):
+//   k_mask_binarise*  k_resize x(L-1) [x2 with a mask]  k_blur7 (side stream) || k_fast<62>  k_select_fast  k_harris
+//   k_select_sort  k_describe (orientation + rBRIEF on the blurred levels)
+// Calls of a few frames (the tracker's one frame per call): k_pyramid instead of the k_resize chain, k_fast<31>, programmatic
+// dependent launch along the chain, the whole chain replayed as a CUDA graph.
 #include "kfs_common.cuh"
 #include "kfs_math.cuh"
 #include <cuda.h> // CUtensorMap + the cuTensorMapEncodeTiled prototype only: the entry point is looked up at run time, libcuda is not linked
@@ -1337,7 +1339,7 @@ struct kfs_orb {
     // CUDA graphs of the kernel chain, one per distinct launch configuration (see kfs_orb_run)
     std::vector<OrbGraph> graphs;
     bool use_graphs = true;
-    bool blur_fma = true;
+    bool blur_fma = true;           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
     // TMA descriptors of the levels for k_fast (re-encoded only when a level's address / pitch / size changes)
     MapCache fmaps, fmaps_h, bmaps; // k_fast's 144 x 70 (144 x 39 for half-height tiles) boxes, k_blur7's 160 x 64 boxes
     // fused pyramid (k_pyramid): host copies of the resize tables, the region plan, level-0 tensor maps of image / mask
@@ -1351,7 +1353,7 @@ struct kfs_orb {
     size_t pyr_smem = 0;
     PyrMap pyr_map_img, pyr_map_mask;
     PyrMapKeyStore pyr_key_img = {}, pyr_key_mask = {};
-    int tma_state = 0;              // 0 = not probed yet, 1 = cuTensorMapEncodeTiled available, -1 = not (LDG path)           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
+    int tma_state = 0;              // 0 = not probed yet, 1 = cuTensorMapEncodeTiled available, -1 = not (LDG path)
     cudaEvent_t ev[KFS_STAGE_COUNT + 1];
     bool ev_made = false;
     float stage_ms[KFS_STAGE_COUNT];
