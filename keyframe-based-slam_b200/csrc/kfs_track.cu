@@ -162,6 +162,9 @@ struct kfs_frontend {
     double *d_p3d = nullptr, *d_p2d = nullptr;
     int *d_nout = nullptr;
     int *h_nout = nullptr; // pinned
+    // kfs_frontend_track: keypoints / descriptors go home on a side stream while the matcher already runs on `stream`
+    cudaStream_t s_copy = nullptr;
+    cudaEvent_t ev_extracted = nullptr, ev_copied = nullptr;
     int launches = 0;
 };
 
@@ -239,6 +242,9 @@ void kfs_frontend_destroy(kfs_frontend *fe)
     for (void *b : bufs) if (b) cudaFree(b);
     fe_free_ring(fe);
     if (fe->h_nout) cudaFreeHost(fe->h_nout);
+    if (fe->s_copy) { cudaStreamSynchronize(fe->s_copy); cudaStreamDestroy(fe->s_copy); }
+    if (fe->ev_extracted) cudaEventDestroy(fe->ev_extracted);
+    if (fe->ev_copied) cudaEventDestroy(fe->ev_copied);
     if (fe->h_wn) cudaFreeHost(fe->h_wn);
     delete fe;
 }
@@ -491,18 +497,28 @@ kfs_status kfs_frontend_track(kfs_frontend *fe, const uint8_t *image, size_t ste
     kfs_status s = fe_enqueue_extract(fe, image, step, w, h, channels, mask, mask_step, "Track");
     if (s) return s;
     const int cp = capacity < fe->cap ? capacity : fe->cap;
-    KFS_CUDA_TRY(cudaMemcpyAsync(fe->h_nout + 1, fe->d_cur_count, sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (cp > 0) {
-        KFS_CUDA_TRY(cudaMemcpyAsync(kp_out, fe->d_cur_kp, (size_t)cp * sizeof(kfs_keypoint), cudaMemcpyDeviceToHost, st));
-        KFS_CUDA_TRY(cudaMemcpyAsync(desc_out, fe->d_cur_desc, (size_t)cp * 32, cudaMemcpyDeviceToHost, st));
+    if (!fe->s_copy) {
+        KFS_CUDA_TRY(cudaStreamCreateWithFlags(&fe->s_copy, cudaStreamNonBlocking));
+        KFS_CUDA_TRY(cudaEventCreateWithFlags(&fe->ev_extracted, cudaEventDisableTiming));
+        KFS_CUDA_TRY(cudaEventCreateWithFlags(&fe->ev_copied, cudaEventDisableTiming));
     }
+    // the frame's own results leave on the side stream; the matcher does not queue behind their copies
+    KFS_CUDA_TRY(cudaEventRecord(fe->ev_extracted, st));
+    KFS_CUDA_TRY(cudaStreamWaitEvent(fe->s_copy, fe->ev_extracted, 0));
+    KFS_CUDA_TRY(cudaMemcpyAsync(fe->h_nout + 1, fe->d_cur_count, sizeof(int), cudaMemcpyDeviceToHost, fe->s_copy));
+    if (cp > 0) {
+        KFS_CUDA_TRY(cudaMemcpyAsync(kp_out, fe->d_cur_kp, (size_t)cp * sizeof(kfs_keypoint), cudaMemcpyDeviceToHost, fe->s_copy));
+        KFS_CUDA_TRY(cudaMemcpyAsync(desc_out, fe->d_cur_desc, (size_t)cp * 32, cudaMemcpyDeviceToHost, fe->s_copy));
+    }
+    KFS_CUDA_TRY(cudaEventRecord(fe->ev_copied, fe->s_copy));
     KfSlot *kf = fe_newest(fe);
     const bool matched = kf && kf->n > 0;
     if (matched) {
         s = fe_enqueue_match(fe, kf, fe->d_cur_kp, fe->d_cur_desc, fe->d_cur_count, fe->cap, true, intrinsics, ratio, match_capacity,
                              matches_out, points3d_out, points2d_out);
-        if (s) return s;
+        if (s) { cudaStreamSynchronize(fe->s_copy); return s; } // nothing may land in the caller's buffers after the return
     }
+    KFS_CUDA_TRY(cudaStreamWaitEvent(st, fe->ev_copied, 0)); // join: still ONE host synchronisation per frame
     KFS_CUDA_TRY(cudaStreamSynchronize(st));
     const int n = fe->h_nout[1];
     *n_out = n;
