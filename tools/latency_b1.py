@@ -39,4 +39,13 @@ with torch.cuda.stream(stream):
         torch.cuda.synchronize()
         tot += a.elapsed_time(b)
     print("chain per frame: %.1f us (graphs %s, %d launches)" % (tot / 50 * 1e3, os.environ.get("KFS_ORB_GRAPHS", "1"), orb.last_launches))
+    dev = 0
+    for i in range(50):                          # the host runs ahead behind a 100 us spin kernel: device time alone
+        torch.cuda._sleep(200000)
+        a.record(stream)
+        orb.extract_device(fd[0].data_ptr(), W, W * H, W, H, 1)
+        b.record(stream)
+        torch.cuda.synchronize()
+        dev += a.elapsed_time(b)
+    print("chain on the device alone (host enqueue hidden): %.1f us" % (dev / 50 * 1e3))
 orb.close()
