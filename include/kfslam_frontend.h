@@ -19,6 +19,10 @@
  *
  * There is no CPU fallback: every entry point that computes needs a CUDA device (sm_100a build) and
  * returns KFS_ERR_NO_DEVICE / KFS_ERR_CUDA otherwise.
+ *
+ * Environment switches (read when a handle is created or first sized; results are identical for every
+ * setting, they select mechanisms for A/B measurements — DESIGN.md section 4): KFS_ORB_GRAPHS,
+ * KFS_ORB_TMA, KFS_ORB_FUSED_PYRAMID, KFS_ORB_FAST_HALF, KFS_ORB_PDL (0 = off), KFS_BF_SPLIT (1..16).
  */
 #ifndef KFSLAM_FRONTEND_H
 #define KFSLAM_FRONTEND_H
