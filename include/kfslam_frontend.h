@@ -198,6 +198,15 @@ KFS_API kfs_status kfs_bf_knn_match_pairs_device(kfs_bf *bf, const kfs_bf_pair *
 KFS_API kfs_status kfs_bf_knn_match_ratio(kfs_bf *bf, const uint8_t *query, int nq, const uint8_t *train, int nt,
                                           float ratio, kfs_dmatch *good, int *n_good);
 
+/* Descriptor rows that kfs_orb_detect_and_compute[_batch] of `orb` just wrote to host memory are still on the device.  A matcher
+ * attached to that extractor matches such rows where they are instead of uploading them again: a query / train pointer of
+ * kfs_bf_knn_match[_pairs] is recognised when it is row 0 of a frame of that extractor's LAST host-buffer call's desc_out and
+ * its row count does not exceed that frame's keypoints (the tracker's knnMatch(keyframe, dpCurrImg): the train side,
+ * VisualOdometry.cpp:39).  The caller promises not to have modified those host rows in between; any other pointer is uploaded
+ * as before.  orb == NULL detaches; the extractor must outlive the attachment and live on the same device.
+ * kfs_bf_last_aliased: descriptor matrices of the last host-buffer call that were matched in place. */
+KFS_API kfs_status kfs_bf_attach_orb(kfs_bf *bf, kfs_orb *orb);
+KFS_API int kfs_bf_last_aliased(const kfs_bf *bf);
 KFS_API kfs_status kfs_bf_set_stream(kfs_bf *bf, void *cuda_stream);
 KFS_API void *kfs_bf_get_stream(kfs_bf *bf);
 KFS_API kfs_status kfs_bf_sync(kfs_bf *bf);
@@ -221,22 +230,33 @@ typedef struct kfs_replay_params {
     float ratio;             /* ratio-test threshold (reference: 0.6f, :46); <= 0 disables the fused `good` output */
     int32_t chunk_frames;    /* frames per H2D/kernel/D2H chunk inside one batch; 0 = the whole batch (batches already
                               * overlap each other; smaller chunks only cut the latency of a lone batch) */
+    int32_t arenas;          /* batches that can be in flight: 2..KFS_REPLAY_MAX_ARENAS, 0 = the default (3) */
 } kfs_replay_params;
+#define KFS_REPLAY_MAX_ARENAS 6
 #define KFS_REPLAY_NO_MATCH INT32_MIN
+#define KFS_REPLAY_SKIP_ROWS 1   /* kfs_replay_frame.flags: this frame's keypoints / descriptors stay on the device */
 typedef struct kfs_replay_frame {
     int32_t keyframe;   /* >= 0: index of the frame of THIS batch that is this frame's keyframe; < 0: -(1 + slot) of the
                          * keyframe cache (content stored by an EARLIER submit); KFS_REPLAY_NO_MATCH: extract only */
     int32_t store_slot; /* >= 0: after this batch's matching, keep this frame's descriptors in that cache slot; -1: no */
+    int32_t flags;      /* 0, or KFS_REPLAY_SKIP_ROWS: io.kp / io.desc rows of this frame are not written (n_kp still is) — the
+                         * tracker keeps keypoints and descriptors only of frames that become keyframes (VisualOdometry.cpp:155-165) */
 } kfs_replay_frame;
 typedef struct kfs_replay_io { /* host buffers; must stay valid until kfs_replay_wait returns */
-    const uint8_t *gray; size_t step, frame_stride; int32_t w, h;   /* batch frames, 8-bit gray */
+    const uint8_t *gray; size_t step, frame_stride; int32_t w, h;   /* batch frames: 8-bit gray, or R,G,B bytes when channels == 3 */
     kfs_keypoint *kp; uint8_t *desc; int32_t capacity; int32_t *n_kp; /* [batch][capacity] (x32 B for desc), [batch] */
     kfs_dmatch *knn;    /* [batch][capacity][2]: row q = the keyframe's descriptor q; NULL: not wanted */
     int32_t *n_query;   /* [batch]: valid rows of knn = the keyframe's keypoint count; may be NULL */
     kfs_dmatch *good;   /* [batch][capacity]: ratio-test survivors in query order; NULL: not wanted */
     int32_t *n_good;    /* [batch]; may be NULL */
+    const uint8_t *mask; size_t mask_step, mask_frame_stride; /* NULL (cv::noArray()) or one h x w mask per frame, non-zero = keep
+                         * (the reference passes one on every call: VisualOdometry.cpp:30, main.cpp:31-34) */
+    int32_t channels;   /* 0 or 1: gray; 3: R,G,B as the reference receives it (:25-28), step = bytes per row */
 } kfs_replay_io;
-KFS_API void kfs_replay_default_params(kfs_replay_params *p); /* ORB defaults, max_batch 64, 8 slots, ratio 0.6 */
+/* Only rows that can be live travel device -> host: min(capacity, nfeatures) rows per frame right behind the kernels (a frame
+ * keeps more than nfeatures keypoints only after ties on a selection threshold; those extra rows — and the kNN rows of such a
+ * keyframe — are fetched by kfs_replay_wait when a count says so).  Rows past the returned counts are scratch. */
+KFS_API void kfs_replay_default_params(kfs_replay_params *p); /* ORB defaults, max_batch 64, 8 slots, ratio 0.6, 3 arenas */
 KFS_API kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_replay **out);
 KFS_API void kfs_replay_destroy(kfs_replay *r);
 KFS_API int kfs_replay_capacity(const kfs_replay *r);           /* per-frame capacity the outputs should have */
@@ -259,6 +279,10 @@ typedef struct kfs_frontend kfs_frontend;
 KFS_API kfs_status kfs_frontend_create(const kfs_orb_params *params, int device, kfs_frontend **out);
 KFS_API void kfs_frontend_destroy(kfs_frontend *fe);
 KFS_API int kfs_frontend_capacity(const kfs_frontend *fe);   /* rows kp_out / desc_out / the match outputs should have */
+/* Changes that capacity (default nfeatures + nfeatures/4 + 64: ties on the selection thresholds may keep more than nfeatures
+ * keypoints).  Drops the cached keyframes and the current frame.  A frame that overflows makes
+ * extract_features / track return KFS_ERR_CAPACITY with *n_out = the rows it needs (cv::ORB would have returned them all). */
+KFS_API kfs_status kfs_frontend_set_capacity(kfs_frontend *fe, int capacity);
 
 /* ExtractFeatures(rgb, mask): image = h rows of w pixels x `channels` bytes (1 = already gray, 3 = R,G,B byte order as the
  * reference receives it), rows `step` bytes apart, host memory.  Gray = (R*9798 + G*19235 + B*3735 + 16384) >> 15, which
@@ -268,7 +292,8 @@ KFS_API kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t
                                                  const uint8_t *mask, size_t mask_step,
                                                  kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out);
 /* The current frame becomes the keyframe (device-to-device copy of its descriptors and keypoints) and `depth`
- * (h x w uint16 millimetres, rows depth_step BYTES apart, host) is uploaded next to them. */
+ * (h x w uint16 millimetres, rows depth_step BYTES apart, host) is uploaded next to them.  Blocks until the depth image has
+ * left the caller's buffer. */
 KFS_API kfs_status kfs_frontend_promote_keyframe(kfs_frontend *fe, const uint16_t *depth, size_t depth_step);
 /* Same, from host copies of a keyframe (n rows of descriptors and keypoints, a w x h depth image). */
 KFS_API kfs_status kfs_frontend_set_keyframe(kfs_frontend *fe, const uint8_t *desc, const kfs_keypoint *kp, int n,

@@ -46,10 +46,13 @@ namespace detail {
 inline cv::Mat as_mat(cv::InputArray a) { return a.getMat(); }
 inline void make_desc(cv::OutputArray d, int n) { if (n) d.create(n, 32, CV_8U); else d.release(); }
 inline cv::Mat out_mat(cv::OutputArray d) { return d.getMat(); }
+// keep the first n rows of a matrix created with more, WITHOUT moving them (the matcher recognises the rows by their address)
+inline void shrink_desc(cv::OutputArray d, int n) { if (n) { cv::Mat m = d.getMat(); d.getMatRef() = m.rowRange(0, n); } else d.release(); }
 #else
 inline const cv::Mat &as_mat(cv::InputArray a) { return a; }
 inline void make_desc(cv::OutputArray d, int n) { if (n) d.create(n, 32, cv::CV_8U); else d.release(); }
 inline cv::Mat &out_mat(cv::OutputArray d) { return d; }
+inline void shrink_desc(cv::OutputArray d, int n) { if (n) d.rows = n; else d.release(); }
 #endif
 } // namespace detail
 
@@ -90,12 +93,16 @@ public:
         if (!msk.empty() && (msk.rows != img.rows || msk.cols != img.cols)) throw_unsupported("mask size differs from image size");
         int cap = kfs_orb_capacity(h_);
         for (;;) {
+            // the descriptors are written straight into the output matrix (created with the handle's capacity, cut to n rows
+            // in place afterwards): no staging copy, and an attached kfs::BFMatcher finds the rows it is handed next
+            // (knnMatch(keyframe, dpCurrImg), VisualOdometry.cpp:39) still on the device by their host address
             keypoints.resize((size_t)cap);
-            scratch_.resize((size_t)cap * 32);
+            detail::make_desc(descriptors, cap);
+            auto d = detail::out_mat(descriptors);
             int n = 0;
             const kfs_status st = kfs_orb_detect_and_compute(h_, img.ptr(0), (size_t)img.step, img.cols, img.rows,
                                                              msk.empty() ? nullptr : msk.ptr(0), msk.empty() ? 0 : (size_t)msk.step,
-                                                             reinterpret_cast<kfs_keypoint *>(keypoints.data()), scratch_.data(), cap, &n);
+                                                             reinterpret_cast<kfs_keypoint *>(keypoints.data()), d.ptr(0), cap, &n);
             if (st == KFS_ERR_CAPACITY) { // ties pushed the count over the handle's slack: grow and redo
                 if (kfs_orb_set_capacity(h_, n + 64) != KFS_OK) detail::raise(KFS_ERR_CUDA, "kfs::ORB::detectAndCompute");
                 cap = kfs_orb_capacity(h_);
@@ -103,11 +110,7 @@ public:
             }
             if (st != KFS_OK) detail::raise(st, "kfs::ORB::detectAndCompute");
             keypoints.resize((size_t)n);
-            detail::make_desc(descriptors, n);
-            if (n) {
-                auto d = detail::out_mat(descriptors);
-                for (int r = 0; r < n; r++) std::memcpy(d.ptr(r), scratch_.data() + (size_t)r * 32, 32);
-            }
+            detail::shrink_desc(descriptors, n);
             return;
         }
     }
@@ -124,7 +127,6 @@ private:
 #endif
     }
     kfs_orb *h_;
-    std::vector<uint8_t> scratch_;
 };
 
 // Stand-in for cv::BFMatcher (DescriptorMatcher).
@@ -171,6 +173,13 @@ public:
         for (int i = 0; i < nq; i++) matches[(size_t)i].assign(flat_.begin() + (size_t)i * k, flat_.begin() + (size_t)i * k + counts_[(size_t)i]);
     }
     kfs_bf *handle() const { return h_; }
+    // Descriptor rows `orb` has just returned are matched where they still are on the device instead of being uploaded again
+    // (kfs_bf_attach_orb); the extractor must outlive this matcher or be detached with attach(nullptr).
+    void attach(const cv::Ptr<ORB> &orb)
+    {
+        const kfs_status st = kfs_bf_attach_orb(h_, orb ? orb->handle() : nullptr);
+        if (st != KFS_OK) detail::raise(st, "kfs::BFMatcher::attach");
+    }
 
 private:
     explicit BFMatcher(kfs_bf *h) : h_(h) {}
@@ -209,6 +218,13 @@ public:
     TrackerFrontEnd(const TrackerFrontEnd &) = delete;
     TrackerFrontEnd &operator=(const TrackerFrontEnd &) = delete;
 
+    // rows per frame (default nfeatures + nfeatures/4 + 64); drops the cached keyframes: call before tracking starts
+    void SetCapacity(int rows)
+    {
+        const kfs_status st = kfs_frontend_set_capacity(h_, rows);
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::SetCapacity");
+    }
+    int Capacity() const { return kfs_frontend_capacity(h_); }
     // K(0,0), K(1,1), K(0,2), K(1,2) of the reference's camera matrix (VisualOdometry.cpp:53-54)
     void setIntrinsics(double fx, double fy, double cx, double cy) { k_[0] = fx; k_[1] = fy; k_[2] = cx; k_[3] = cy; }
     void setRatio(float r) { ratio_ = r; } // 0.6f in the reference (:46)
@@ -224,8 +240,9 @@ public:
         const kfs_status st = kfs_frontend_extract_features(h_, rgb.data, (size_t)rgb.step, rgb.cols, rgb.rows, rgb.channels(),
                                                             mask.empty() ? nullptr : mask.data, mask.empty() ? 0 : (size_t)mask.step,
                                                             reinterpret_cast<kfs_keypoint *>(kp.data()), d.data(), cap, &n);
-        if (st != KFS_OK && st != KFS_ERR_CAPACITY) detail::raise(st, "kfs::TrackerFrontEnd::ExtractFeatures");
-        if (n > cap) n = cap;
+        // a tie-rich frame that overflows the handle is an error here exactly as in Track(): never a silently shorter keypoint set
+        // (kfs::ORB::detectAndCompute grows and retries; this handle also owns the keyframe ring, so growing is SetCapacity's job)
+        if (st != KFS_OK) detail::raise(st, "kfs::TrackerFrontEnd::ExtractFeatures");
         kp.resize((size_t)n);
         detail::make_desc(desc, n);
         if (n) {

@@ -37,20 +37,22 @@ class BfPair(C.Structure):
 
 class ReplayParams(C.Structure):
     _fields_ = [("orb", OrbParams), ("max_batch", C.c_int32), ("keyframe_slots", C.c_int32), ("ratio", C.c_float),
-                ("chunk_frames", C.c_int32)]
+                ("chunk_frames", C.c_int32), ("arenas", C.c_int32)]
 
 
 class ReplayFrame(C.Structure):
-    _fields_ = [("keyframe", C.c_int32), ("store_slot", C.c_int32)]
+    _fields_ = [("keyframe", C.c_int32), ("store_slot", C.c_int32), ("flags", C.c_int32)]
 
 
 class ReplayIO(C.Structure):
     _fields_ = [("gray", C.c_void_p), ("step", C.c_size_t), ("frame_stride", C.c_size_t), ("w", C.c_int32), ("h", C.c_int32),
                 ("kp", C.c_void_p), ("desc", C.c_void_p), ("capacity", C.c_int32), ("n_kp", C.c_void_p),
-                ("knn", C.c_void_p), ("n_query", C.c_void_p), ("good", C.c_void_p), ("n_good", C.c_void_p)]
+                ("knn", C.c_void_p), ("n_query", C.c_void_p), ("good", C.c_void_p), ("n_good", C.c_void_p),
+                ("mask", C.c_void_p), ("mask_step", C.c_size_t), ("mask_frame_stride", C.c_size_t), ("channels", C.c_int32)]
 
 
 REPLAY_NO_MATCH = -2**31
+REPLAY_SKIP_ROWS = 1
 
 # name -> (restype, argtypes); this table is also what tests/test_abi.py checks against the header.
 _vp, _i, _sz, _f = C.c_void_p, C.c_int, C.c_size_t, C.c_float
@@ -91,6 +93,8 @@ SIGNATURES = {
     "kfs_bf_get_stream": (_vp, [_vp]),
     "kfs_bf_sync": (_i, [_vp]),
     "kfs_bf_last_launches": (_i, [_vp]),
+    "kfs_bf_attach_orb": (_i, [_vp, _vp]),
+    "kfs_bf_last_aliased": (_i, [_vp]),
     "kfs_replay_default_params": (None, [C.POINTER(ReplayParams)]),
     "kfs_replay_create": (_i, [C.POINTER(ReplayParams), _i, C.POINTER(_vp)]),
     "kfs_replay_destroy": (None, [_vp]),
@@ -102,6 +106,7 @@ SIGNATURES = {
     "kfs_frontend_create": (_i, [C.POINTER(OrbParams), _i, C.POINTER(_vp)]),
     "kfs_frontend_destroy": (None, [_vp]),
     "kfs_frontend_capacity": (_i, [_vp]),
+    "kfs_frontend_set_capacity": (_i, [_vp, _i]),
     "kfs_frontend_extract_features": (_i, [_vp, _vp, _sz, _i, _i, _i, _vp, _sz, _vp, _vp, _i, _ip]),
     "kfs_frontend_promote_keyframe": (_i, [_vp, _vp, _sz]),
     "kfs_frontend_set_keyframe": (_i, [_vp, _vp, _vp, _i, _vp, _sz, _i, _i]),

@@ -273,6 +273,8 @@ struct kfs_bf {
     int *d_counters = nullptr;    // [tiles] arrival counters (zero between launches)
     size_t scratch_tiles = 0, scratch_elems = 0;
     int force_split = 0;          // KFS_BF_SPLIT (tests / experiments): 0 = automatic
+    const kfs_orb *attached = nullptr; // kfs_bf_attach_orb: host rows this extractor just delivered are matched on the device
+    int aliased = 0;              // descriptor matrices of the last host-buffer call that were found on the device
 };
 
 // Number of train splits.  A batch with >= 4 query tiles per SM is throughput-bound as it is (S = 1).  Smaller launches
@@ -426,8 +428,8 @@ kfs_status kfs_bf_create(int norm_type, int cross_check, int device, kfs_bf **ou
     if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "out of host memory");
     b->device = device;
     KfsDeviceGuard guard(device);
-    cudaError_t e = cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking);
-    if (e != cudaSuccess) { delete b; KFS_FAIL(KFS_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+    cudaError_t e = guard.ok ? cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking) : cudaErrorInvalidDevice;
+    if (e != cudaSuccess) { delete b; KFS_FAIL(KFS_ERR_CUDA, "kfs_bf_create on device %d: %s", device, cudaGetErrorString(e)); }
     cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
     if (const char *fs = getenv("KFS_BF_SPLIT")) b->force_split = atoi(fs);
     b->stream = b->own_stream;
@@ -452,7 +454,7 @@ void kfs_bf_destroy(kfs_bf *b)
 kfs_status kfs_bf_set_stream(kfs_bf *b, void *s)
 {
     if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
-    KfsDeviceGuard guard(b->device);
+    KFS_DEVICE_GUARD(b->device);
     KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
     b->stream = s ? (cudaStream_t)s : b->own_stream;
     return KFS_OK;
@@ -461,18 +463,26 @@ void *kfs_bf_get_stream(kfs_bf *b) { return b ? (void *)b->stream : nullptr; }
 kfs_status kfs_bf_sync(kfs_bf *b)
 {
     if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
-    KfsDeviceGuard guard(b->device);
+    KFS_DEVICE_GUARD(b->device);
     KFS_CUDA_TRY(cudaStreamSynchronize(b->stream));
     return KFS_OK;
 }
 int kfs_bf_last_launches(const kfs_bf *b) { return b ? b->launches : 0; }
+
+kfs_status kfs_bf_attach_orb(kfs_bf *b, kfs_orb *orb)
+{
+    if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
+    b->attached = orb;
+    return KFS_OK;
+}
+int kfs_bf_last_aliased(const kfs_bf *b) { return b ? b->aliased : 0; }
 
 kfs_status kfs_bf_knn_match_pairs_device(kfs_bf *b, const kfs_bf_pair *pairs, int npairs, int k)
 {
     if (!b) KFS_FAIL(KFS_ERR_INVALID_ARG, "bf handle is NULL");
     kfs_status s = bf_check_pairs(pairs, npairs, k, true);
     if (s) return s;
-    KfsDeviceGuard guard(b->device);
+    KFS_DEVICE_GUARD(b->device);
     b->launches = 0;
     std::vector<BfPairDev> h((size_t)npairs);
     for (int i = 0; i < npairs; i++) {
@@ -514,7 +524,7 @@ kfs_status kfs_bf_knn_match_pairs(kfs_bf *b, const kfs_bf_pair *pairs, int npair
     kfs_status s = bf_check_pairs(pairs, npairs, k, false);
     if (s) return s;
     if (npairs == 0) return KFS_OK;
-    KfsDeviceGuard guard(b->device);
+    KFS_DEVICE_GUARD(b->device);
     b->launches = 0;
     int max_rows = 0, max_nq = 0;
     for (int i = 0; i < npairs; i++) {
@@ -530,13 +540,18 @@ kfs_status kfs_bf_knn_match_pairs(kfs_bf *b, const kfs_bf_pair *pairs, int npair
     std::vector<BfCopyRun> up, down, down_cnt;
     std::vector<int> sq((size_t)npairs), st((size_t)npairs);
     int nslots = 0;
+    std::vector<const uint8_t *> alias; // per slot: where the rows already are on the device (attached extractor), or nullptr
+    b->aliased = 0;
     auto slot_for = [&](const uint8_t *h, int rows) {
         const BfBufKey key{h, rows};
         auto it = slot_of.find(key);
         if (it != slot_of.end()) return it->second;
         const int sl = nslots++;
         slot_of.emplace(key, sl);
-        if (rows > 0) bf_add_to_runs(up, h, (size_t)sl * in_slot, (size_t)rows * 32, in_slot);
+        const uint8_t *dev = b->attached ? kfs_orb_alias_desc(b->attached, h, rows, b->device) : nullptr;
+        alias.push_back(dev);
+        if (dev) b->aliased++;
+        else if (rows > 0) bf_add_to_runs(up, h, (size_t)sl * in_slot, (size_t)rows * 32, in_slot);
         return sl;
     };
     for (int i = 0; i < npairs; i++) { sq[i] = slot_for(pairs[i].query, pairs[i].nq); st[i] = slot_for(pairs[i].train, pairs[i].nt); }
@@ -549,7 +564,9 @@ kfs_status kfs_bf_knn_match_pairs(kfs_bf *b, const kfs_bf_pair *pairs, int npair
     }
     std::vector<BfPairDev> h((size_t)npairs);
     for (int i = 0; i < npairs; i++) {
-        h[i].query = b->d_buf + (size_t)sq[i] * in_slot; h[i].train = b->d_buf + (size_t)st[i] * in_slot; h[i].d_nq = nullptr; h[i].d_nt = nullptr;
+        h[i].query = alias[(size_t)sq[i]] ? alias[(size_t)sq[i]] : b->d_buf + (size_t)sq[i] * in_slot;
+        h[i].train = alias[(size_t)st[i]] ? alias[(size_t)st[i]] : b->d_buf + (size_t)st[i] * in_slot;
+        h[i].d_nq = nullptr; h[i].d_nt = nullptr;
         h[i].out = (kfs_dmatch *)(b->d_buf + o_out + (size_t)i * out_slot); h[i].counts = (int *)(b->d_buf + o_cnt + (size_t)i * cnt_slot);
         h[i].nq = pairs[i].nq; h[i].nt = pairs[i].nt;
         if (pairs[i].nq) {
@@ -587,7 +604,7 @@ kfs_status kfs_bf_knn_match_ratio(kfs_bf *b, const uint8_t *query, int nq, const
     kfs_status s = bf_check_pairs(&p, 1, 2, false);
     if (s) return s;
     if (nq == 0) return KFS_OK;
-    KfsDeviceGuard guard(b->device);
+    KFS_DEVICE_GUARD(b->device);
     b->launches = 0;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t r = off; off = kfs_align_up(off + bytes, 256); return r; };

@@ -41,6 +41,12 @@ struct KfsDeviceGuard {
     }
 };
 
+// Every entry point that returns a status selects its handle's device through this: a failed cudaSetDevice is an error, not a
+// silent run on whatever device happens to be current.
+#define KFS_DEVICE_GUARD(dev)                                                             \
+    KfsDeviceGuard guard(dev);                                                            \
+    if (!guard.ok) KFS_FAIL(KFS_ERR_CUDA, "cudaSetDevice(%d) failed", (int)(dev))
+
 // ---- library-internal interfaces between the translation units (not part of the C ABI) -----------------
 // One (query, train) matching problem as the kernels see it (device pointers).
 struct BfPairDev {
@@ -49,9 +55,19 @@ struct BfPairDev {
     kfs_dmatch *out; int *counts;
     int nq, nt;
 };
-kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const uint8_t *gray, size_t step, size_t frame_stride, int w, int h, int batch,
-                                      const uint8_t *mask, size_t mask_step, size_t mask_frame_stride,
-                                      kfs_keypoint *kp_out, uint8_t *desc_out, int capacity);
+// One batch of host frames through the ORB handle's three-stream pipeline (H2D | kernel chain | D2H).
+struct KfsHostBatch {
+    const uint8_t *image; size_t step, frame_stride; int w, h, channels, batch; // channels 1 (gray) or 3 (R,G,B bytes: converted on the device)
+    const uint8_t *mask; size_t mask_step, mask_frame_stride;                    // nullptr = cv::noArray()
+    kfs_keypoint *kp_out; uint8_t *desc_out; int capacity;                       // [batch][capacity] host rows
+    int out_rows;              // rows per frame copied right behind the kernels (<= capacity; 0 = capacity): nfeatures covers every
+                               // frame whose selection thresholds had no ties; the rest of a longer frame is fetched by finish()
+    const uint8_t *skip_rows;  // [batch] or nullptr: non-zero = this frame's keypoints / descriptors are not wanted on the host
+};
+kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const KfsHostBatch &hb);
+const uint8_t *kfs_orb_alias_desc(const kfs_orb *o, const uint8_t *host, int rows, int device);
+kfs_status kfs_launch_rgb2gray(const uint8_t *src, long long sstep, long long sfs, uint8_t *dst, int dpitch, long long dfs, int w, int h, int nframes,
+                               cudaStream_t st);
 kfs_status kfs_orb_finish_host_batch(kfs_orb *o, int batch, int *n_out);
 void kfs_orb_internal_streams(kfs_orb *o, cudaStream_t *s_in, cudaStream_t *s_out);
 void kfs_orb_internal_start_fence(kfs_orb *o, bool on);

@@ -72,7 +72,7 @@ extern "C" kfs_status kfs_pipe_peak(int device, int what, double *gops)
 {
     if (!gops || what < 0 || what > 1) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_pipe_peak: bad arguments");
     if (kfs_device_count() <= device || device < 0) KFS_FAIL(KFS_ERR_NO_DEVICE, "kfs_pipe_peak: no CUDA device %d", device);
-    KfsDeviceGuard guard(device);
+    KFS_DEVICE_GUARD(device);
     cudaDeviceProp prop;
     KFS_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     uint32_t *d = nullptr;

@@ -18,6 +18,7 @@
 #include <vector>
 #include <algorithm>
 #include <new>
+#include <mutex>
 
 #ifndef KFS_DK
 #define KFS_DK 2
@@ -1366,10 +1367,13 @@ struct kfs_orb {
     cudaEvent_t ev_start = nullptr;
     int pipeline_chunk = 0;       // frames per chunk; 0 = auto
     bool start_fence = true;      // copy streams wait for work already queued on the compute stream (off: replay executor)
-    int pending_capacity = 0;     // capacity of the host batch in flight (enqueue -> finish)
+    bool alias_valid = false;     // the last host batch is complete and nothing has run since: its descriptors are still in g.desc
+    KfsHostBatch pending = {};    // the host batch in flight (enqueue -> finish)
+    int pending_rows = 0;         // rows per frame its eager copies carried
+    uint8_t *rgb_stage = nullptr; // colour frames of a host batch ([batch][h][align16(3w)]), converted into level 0 on the device
+    size_t rgb_stage_bytes = 0;
     uint8_t *mask_stage = nullptr; // raw host mask staged on the device
     size_t mask_stage_bytes = 0;
-    size_t sort_smem_set = 0;
 };
 
 static int kfs_cvround(double v) { return (int)lrint(v); }
@@ -1401,6 +1405,7 @@ static void kfs_orb_free_arena(kfs_orb *o)
     if (o->d_rects) { cudaFree(o->d_rects); o->d_rects = nullptr; }
     o->pyr_fused = false;
     if (o->arena) { cudaFree(o->arena); o->arena = nullptr; }
+    o->alias_valid = false;
     o->W = o->H = o->B = 0;
 }
 
@@ -1606,18 +1611,33 @@ typedef CUresult (*kfs_encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuui
                                         CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static kfs_encode_tiled_fn kfs_encode_tiled()
 {
-    static kfs_encode_tiled_fn fn = nullptr;
-    static bool probed = false;
-    if (!probed) {
-        probed = true;
+    // function-local static: initialised exactly once, also when several host threads create their handles at the same time
+    static const kfs_encode_tiled_fn fn = [] {
         void *p = nullptr;
         cudaDriverEntryPointQueryResult q;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = (kfs_encode_tiled_fn)p;
-        else
-            cudaGetLastError();
-    }
+            return (kfs_encode_tiled_fn)p;
+        cudaGetLastError();
+        return (kfs_encode_tiled_fn) nullptr;
+    }();
     return fn;
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-function, per-DEVICE limit shared by every handle of the process: both
+// kernels that may ask for more than 48 KB get the device's opt-in maximum once per device and it is never lowered again
+// (a per-handle cache of "what I set last" let a second handle with a smaller request pull the limit below the first one's).
+static cudaError_t kfs_orb_raise_smem_limits(int device)
+{
+    static std::mutex mu;
+    static bool done[64] = {};
+    std::lock_guard<std::mutex> lock(mu);
+    if (device >= 0 && device < 64 && done[device]) return cudaSuccess;
+    int optin = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+    if (e == cudaSuccess && device >= 0 && device < 64) done[device] = true;
+    return e;
 }
 
 // Regions of the fused pyramid kernel (k_pyramid): tile (i, j) of the coarsest level owns, on every level l, the box between
@@ -1702,7 +1722,6 @@ static kfs_status kfs_orb_plan_pyramid(kfs_orb *o)
     KFS_CUDA_TRY(cudaMemcpyAsync(o->d_rects, rects.data(), rects.size() * sizeof(short), cudaMemcpyHostToDevice, o->stream));
     KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
     P.rects = o->d_rects;
-    if (o->pyr_smem > 48 * 1024) KFS_CUDA_TRY(cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)o->pyr_smem));
     memset(&o->pyr_key_img, 0, sizeof(o->pyr_key_img));
     memset(&o->pyr_key_mask, 0, sizeof(o->pyr_key_mask));
     o->pyr_fused = true;
@@ -1865,10 +1884,6 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
         if (smem_n > 11264) smem_n = 11264; // 16 B per entry -> 176 KB (+ <= 32 KB of row arrays), under the 227 KB opt-in limit
         const int rows_cap = o->lh[0] + 2; // two row arrays (segment start / fill cursor) for the (y, x) ordering
         const size_t dyn = (size_t)smem_n * 16 + (size_t)rows_cap * 8;
-        if (dyn > 48 * 1024 && dyn != o->sort_smem_set) {
-            KFS_CUDA_TRY(cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-            o->sort_smem_set = dyn;
-        }
         kfs_launch_pdl(pdl, k_select_sort, dim3(L, nb), dim3(SORT_THREADS), dyn, st, g, smem_n, rows_cap);
         KFS_LAUNCH_CHECK(o);
     }
@@ -1994,10 +2009,12 @@ kfs_status kfs_orb_create(const kfs_orb_params *params, int device, kfs_orb **ou
     if (const char *eg = getenv("KFS_ORB_GRAPHS")) o->use_graphs = atoi(eg) != 0; // experiments: 0 = always launch the chain directly
     memset(o->stage_ms, 0, sizeof(o->stage_ms));
     KfsDeviceGuard guard(device);
-    cudaError_t e = cudaStreamCreateWithFlags(&o->own_stream, cudaStreamNonBlocking);
+    cudaError_t e = guard.ok ? cudaStreamCreateWithFlags(&o->own_stream, cudaStreamNonBlocking) : cudaErrorInvalidDevice;
+    if (e == cudaSuccess) e = kfs_orb_raise_smem_limits(device);
     if (e != cudaSuccess) {
+        if (o->own_stream) cudaStreamDestroy(o->own_stream);
         delete o;
-        KFS_FAIL(KFS_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
+        KFS_FAIL(KFS_ERR_CUDA, "kfs_orb_create on device %d: %s", device, cudaGetErrorString(e));
     }
     o->stream = o->own_stream;
     *out = o;
@@ -2016,6 +2033,7 @@ void kfs_orb_destroy(kfs_orb *o)
     for (cudaEvent_t e : o->ev_cmp) cudaEventDestroy(e);
     if (o->ev_start) cudaEventDestroy(o->ev_start);
     if (o->mask_stage) cudaFree(o->mask_stage);
+    if (o->rgb_stage) cudaFree(o->rgb_stage);
     if (o->ev_pyr) cudaEventDestroy(o->ev_pyr);
     if (o->ev_blur) cudaEventDestroy(o->ev_blur);
     if (o->s_blur) cudaStreamDestroy(o->s_blur);
@@ -2030,7 +2048,7 @@ int kfs_orb_capacity(const kfs_orb *o) { return o ? o->cap_out : 0; }
 kfs_status kfs_orb_set_capacity(kfs_orb *o, int capacity)
 {
     if (!o || capacity < 1) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_set_capacity: bad arguments");
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     const int c = (int)kfs_align_up((size_t)capacity, 8);
     if (c != o->cap_out) {
         if (o->arena) { KFS_CUDA_TRY(cudaStreamSynchronize(o->stream)); kfs_orb_free_arena(o); }
@@ -2042,7 +2060,7 @@ kfs_status kfs_orb_set_capacity(kfs_orb *o, int capacity)
 kfs_status kfs_orb_set_stream(kfs_orb *o, void *s)
 {
     if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
     o->stream = s ? (cudaStream_t)s : o->own_stream;
     return KFS_OK;
@@ -2053,7 +2071,7 @@ void *kfs_orb_get_stream(kfs_orb *o) { return o ? (void *)o->stream : nullptr; }
 kfs_status kfs_orb_sync(kfs_orb *o)
 {
     if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
     return KFS_OK;
 }
@@ -2063,8 +2081,9 @@ kfs_status kfs_orb_extract_device(kfs_orb *o, const uint8_t *d_gray, size_t step
 {
     kfs_status s = kfs_orb_check_frame_args(o, d_gray, step, w, h, batch);
     if (s) return s;
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     o->launches = 0;
+    o->alias_valid = false;
     if (w == 0 || h == 0) { o->last_batch = 0; return KFS_OK; }
     if (d_mask && mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < width");
     s = kfs_orb_ensure(o, w, h, batch, d_mask != nullptr);
@@ -2106,7 +2125,7 @@ kfs_status kfs_orb_fetch_results(kfs_orb *o, kfs_keypoint *kp_out, uint8_t *desc
     const int B = o->last_batch;
     if (B == 0) return KFS_OK;
     if ((!kp_out || !desc_out) && capacity > 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     const int cp = capacity < o->cap_out ? capacity : o->cap_out;
     KFS_CUDA_TRY(cudaMemcpyAsync(o->h_counts, o->g.n_out, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, o->stream));
     if (cp > 0) {
@@ -2170,22 +2189,24 @@ static kfs_status kfs_h2d_frames(uint8_t *d, size_t dpitch, size_t dfs, const ui
 // still work, the copies just serialise inside the driver).  The call returns when everything is on the host.
 } // extern "C"  (the two functions below are library-internal: kfs_replay.cu drives them)
 
-// Enqueues the whole host-buffer pipeline (chunked H2D | kernel chain | D2H of keypoints, descriptors and the
-// per-frame counts) WITHOUT synchronising.  Results are complete once the handle's copy-out stream has drained;
-// kfs_orb_finish_host_batch then hands out the counts.
-kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const uint8_t *gray, size_t step, size_t frame_stride, int w, int h, int batch,
-                                      const uint8_t *mask, size_t mask_step, size_t mask_frame_stride,
-                                      kfs_keypoint *kp_out, uint8_t *desc_out, int capacity)
+// Enqueues the whole host-buffer pipeline (chunked H2D | [colour -> gray] | kernel chain | D2H of keypoints, descriptors and
+// the per-frame counts) WITHOUT synchronising.  Results are complete once the handle's copy-out stream has drained;
+// kfs_orb_finish_host_batch then hands out the counts (and fetches the rows past out_rows of a tie-rich frame).
+kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const KfsHostBatch &hb)
 {
-    kfs_status s = kfs_orb_check_frame_args(o, gray, step, w, h, batch);
+    const int w = hb.w, h = hb.h, batch = hb.batch, capacity = hb.capacity, ch = hb.channels;
+    if (ch != 1 && ch != 3) KFS_FAIL(KFS_ERR_UNSUPPORTED, "%d channels (the reference handles 1 or 3, VisualOdometry.cpp:27)", ch);
+    kfs_status s = kfs_orb_check_frame_args(o, hb.image, hb.step / (size_t)ch, w, h, batch);
     if (s) return s;
+    if (hb.step < (size_t)w * ch) KFS_FAIL(KFS_ERR_INVALID_ARG, "step %zu < width %d x %d channels", hb.step, w, ch);
     if (capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "capacity < 0");
     if (w == 0 || h == 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "empty image");
-    if (mask && mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < width");
-    if ((!kp_out || !desc_out) && capacity > 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
-    KfsDeviceGuard guard(o->device);
+    if (hb.mask && hb.mask_step < (size_t)w) KFS_FAIL(KFS_ERR_INVALID_ARG, "mask_step < width");
+    if ((!hb.kp_out || !hb.desc_out) && capacity > 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
+    KFS_DEVICE_GUARD(o->device);
     o->launches = 0;
-    s = kfs_orb_ensure(o, w, h, batch, mask != nullptr);
+    o->alias_valid = false;
+    s = kfs_orb_ensure(o, w, h, batch, hb.mask != nullptr);
     if (s) return s;
     int chunk = o->pipeline_chunk > 0 ? o->pipeline_chunk : (batch >= 8 ? kfs_div_up(batch, 4) : batch);
     if (chunk > batch) chunk = batch;
@@ -2193,13 +2214,19 @@ kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const uint8_t *gray, size_t st
     const int nchunks = kfs_div_up(batch, chunk);
     s = kfs_orb_pipeline_init(o, nchunks);
     if (s) return s;
-    if (mask) {
+    if (hb.mask) {
         const size_t need = (size_t)o->lfs[0] * batch;
         if (need > o->mask_stage_bytes) {
             if (o->mask_stage) { cudaFree(o->mask_stage); o->mask_stage = nullptr; o->mask_stage_bytes = 0; }
             KFS_CUDA_TRY(cudaMalloc((void **)&o->mask_stage, need));
             o->mask_stage_bytes = need;
         }
+    }
+    const size_t ipitch = kfs_align_up((size_t)w * 3, 16), ifs = ipitch * (size_t)h; // colour staging: [batch][h][ipitch]
+    if (ch == 3 && ifs * batch > o->rgb_stage_bytes) {
+        if (o->rgb_stage) { KFS_CUDA_TRY(cudaStreamSynchronize(o->stream)); cudaFree(o->rgb_stage); o->rgb_stage = nullptr; o->rgb_stage_bytes = 0; }
+        KFS_CUDA_TRY(cudaMalloc((void **)&o->rgb_stage, ifs * batch));
+        o->rgb_stage_bytes = ifs * batch;
     }
     if (kfs_stage_mark(o, KFS_STAGE_INGEST)) return KFS_ERR_CUDA;
     LevelDev &L0 = o->g.lv[0];
@@ -2212,49 +2239,83 @@ kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const uint8_t *gray, size_t st
         KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_out, o->ev_start, 0));
     }
     const int cp = capacity < o->cap_out ? capacity : o->cap_out;
+    int rows = hb.out_rows > 0 ? hb.out_rows : cp;
+    if (rows > cp) rows = cp;
     for (int c = 0; c < nchunks; c++) {
         const int f0 = c * chunk, nb = (f0 + chunk <= batch) ? chunk : batch - f0;
-        s = kfs_h2d_frames(o->pyr[0], (size_t)o->lpitch[0], (size_t)o->lfs[0], gray, step, frame_stride, w, h, f0, nb, o->s_in);
+        if (ch == 3) s = kfs_h2d_frames(o->rgb_stage, ipitch, ifs, hb.image, hb.step, hb.frame_stride, 3 * w, h, f0, nb, o->s_in);
+        else s = kfs_h2d_frames(o->pyr[0], (size_t)o->lpitch[0], (size_t)o->lfs[0], hb.image, hb.step, hb.frame_stride, w, h, f0, nb, o->s_in);
         if (s) return s;
-        if (mask) {
-            s = kfs_h2d_frames(o->mask_stage, (size_t)o->lpitch[0], (size_t)o->lfs[0], mask, mask_step, mask_frame_stride, w, h, f0, nb, o->s_in);
+        if (hb.mask) {
+            s = kfs_h2d_frames(o->mask_stage, (size_t)o->lpitch[0], (size_t)o->lfs[0], hb.mask, hb.mask_step, hb.mask_frame_stride, w, h, f0, nb, o->s_in);
             if (s) return s;
         }
         KFS_CUDA_TRY(cudaEventRecord(o->ev_in[c], o->s_in));
         KFS_CUDA_TRY(cudaStreamWaitEvent(o->stream, o->ev_in[c], 0));
+        if (ch == 3) { // VisualOdometry.cpp:25-28 for the whole chunk in one launch, straight into level 0
+            s = kfs_launch_rgb2gray(o->rgb_stage + (size_t)f0 * ifs, (long long)ipitch, (long long)ifs, o->pyr[0] + (size_t)f0 * o->lfs[0], o->lpitch[0],
+                                    o->lfs[0], w, h, nb, o->stream);
+            if (s) return s;
+            o->launches++;
+        }
         if (c == 0 && kfs_stage_mark(o, KFS_STAGE_PYRAMID)) return KFS_ERR_CUDA;
-        s = kfs_orb_run(o, f0, nb, mask ? o->mask_stage + (size_t)f0 * o->lfs[0] : nullptr, (size_t)o->lpitch[0], (size_t)o->lfs[0], c == 0);
+        s = kfs_orb_run(o, f0, nb, hb.mask ? o->mask_stage + (size_t)f0 * o->lfs[0] : nullptr, (size_t)o->lpitch[0], (size_t)o->lfs[0], c == 0);
         if (s) return s;
         KFS_CUDA_TRY(cudaEventRecord(o->ev_cmp[c], o->stream));
         KFS_CUDA_TRY(cudaStreamWaitEvent(o->s_out, o->ev_cmp[c], 0));
-        if (cp > 0 && capacity == o->cap_out) { // same row pitch on both sides: linear copies
-            KFS_CUDA_TRY(cudaMemcpyAsync(kp_out + (size_t)f0 * capacity, o->g.kp + (size_t)f0 * o->cap_out,
-                                         (size_t)nb * capacity * sizeof(kfs_keypoint), cudaMemcpyDeviceToHost, o->s_out));
-            KFS_CUDA_TRY(cudaMemcpyAsync(desc_out + (size_t)f0 * capacity * 32, o->g.desc + (size_t)f0 * o->cap_out * 32,
-                                         (size_t)nb * capacity * 32, cudaMemcpyDeviceToHost, o->s_out));
-        } else if (cp > 0) {
-            KFS_CUDA_TRY(cudaMemcpy2DAsync(kp_out + (size_t)f0 * capacity, (size_t)capacity * sizeof(kfs_keypoint),
-                                           o->g.kp + (size_t)f0 * o->cap_out, (size_t)o->cap_out * sizeof(kfs_keypoint),
-                                           (size_t)cp * sizeof(kfs_keypoint), (size_t)nb, cudaMemcpyDeviceToHost, o->s_out));
-            KFS_CUDA_TRY(cudaMemcpy2DAsync(desc_out + (size_t)f0 * capacity * 32, (size_t)capacity * 32,
-                                           o->g.desc + (size_t)f0 * o->cap_out * 32, (size_t)o->cap_out * 32,
-                                           (size_t)cp * 32, (size_t)nb, cudaMemcpyDeviceToHost, o->s_out));
+        // rows [0, rows) of every wanted frame: runs of consecutive wanted frames travel as one (2-D) copy each
+        for (int a = f0; rows > 0 && a < f0 + nb;) {
+            if (hb.skip_rows && hb.skip_rows[a]) { a++; continue; }
+            int b = a + 1;
+            while (b < f0 + nb && !(hb.skip_rows && hb.skip_rows[b])) b++;
+            const size_t n = (size_t)(b - a);
+            if (rows == capacity && capacity == o->cap_out) { // same row pitch on both sides, whole rows: linear copies
+                KFS_CUDA_TRY(cudaMemcpyAsync(hb.kp_out + (size_t)a * capacity, o->g.kp + (size_t)a * o->cap_out,
+                                             n * capacity * sizeof(kfs_keypoint), cudaMemcpyDeviceToHost, o->s_out));
+                KFS_CUDA_TRY(cudaMemcpyAsync(hb.desc_out + (size_t)a * capacity * 32, o->g.desc + (size_t)a * o->cap_out * 32,
+                                             n * capacity * 32, cudaMemcpyDeviceToHost, o->s_out));
+            } else {
+                KFS_CUDA_TRY(cudaMemcpy2DAsync(hb.kp_out + (size_t)a * capacity, (size_t)capacity * sizeof(kfs_keypoint),
+                                               o->g.kp + (size_t)a * o->cap_out, (size_t)o->cap_out * sizeof(kfs_keypoint),
+                                               (size_t)rows * sizeof(kfs_keypoint), n, cudaMemcpyDeviceToHost, o->s_out));
+                KFS_CUDA_TRY(cudaMemcpy2DAsync(hb.desc_out + (size_t)a * capacity * 32, (size_t)capacity * 32,
+                                               o->g.desc + (size_t)a * o->cap_out * 32, (size_t)o->cap_out * 32,
+                                               (size_t)rows * 32, n, cudaMemcpyDeviceToHost, o->s_out));
+            }
+            a = b;
         }
     }
     KFS_CUDA_TRY(cudaMemcpyAsync(o->h_counts, o->g.n_out, sizeof(int) * (size_t)batch, cudaMemcpyDeviceToHost, o->s_out));
-    o->pending_capacity = capacity;
+    o->pending = hb;
+    o->pending_rows = rows;
     return KFS_OK;
 }
 
+// After the copy-out stream has drained: counts to the caller, and for a frame that kept more than `out_rows` keypoints (ties on
+// a selection threshold) the remaining rows in a second, blocking copy — rare, and never wrong.
 kfs_status kfs_orb_finish_host_batch(kfs_orb *o, int batch, int *n_out)
 {
-    const int capacity = o->pending_capacity;
+    const KfsHostBatch &hb = o->pending;
+    const int capacity = hb.capacity;
     const int cp = capacity < o->cap_out ? capacity : o->cap_out;
     kfs_status rc = KFS_OK;
+    bool late = false;
     for (int f = 0; f < batch; f++) {
         n_out[f] = o->h_counts[f];
         if (n_out[f] > cp) rc = KFS_ERR_CAPACITY;
+        const int live = n_out[f] < cp ? n_out[f] : cp;
+        if (live > o->pending_rows && !(hb.skip_rows && hb.skip_rows[f])) {
+            const size_t r0 = (size_t)o->pending_rows, n = (size_t)(live - o->pending_rows);
+            KFS_CUDA_TRY(cudaMemcpyAsync(hb.kp_out + (size_t)f * capacity + r0, o->g.kp + (size_t)f * o->cap_out + r0, n * sizeof(kfs_keypoint),
+                                         cudaMemcpyDeviceToHost, o->s_out));
+            KFS_CUDA_TRY(cudaMemcpyAsync(hb.desc_out + ((size_t)f * capacity + r0) * 32, o->g.desc + ((size_t)f * o->cap_out + r0) * 32, n * 32,
+                                         cudaMemcpyDeviceToHost, o->s_out));
+            late = true;
+        }
     }
+    if (late) KFS_CUDA_TRY(cudaStreamSynchronize(o->s_out));
+    o->alias_valid = true;
+    o->pending.batch = batch;
     if (rc == KFS_ERR_CAPACITY) kfs_set_error("output capacity %d too small (handle capacity %d); n_out holds the required counts", capacity, o->cap_out);
     if (o->profiling && o->ev_made) {
         for (int i = 0; i < KFS_STAGE_COUNT; i++) {
@@ -2264,6 +2325,24 @@ kfs_status kfs_orb_finish_host_batch(kfs_orb *o, int batch, int *n_out)
         }
     }
     return rc;
+}
+
+// Device copy of descriptor rows the last host-buffer extraction delivered to `host` (row 0 of one of its frames, at most that
+// frame's keypoint count of rows), or nullptr: lets an attached matcher (kfs_bf_attach_orb) skip the upload of rows that never
+// left the device.
+const uint8_t *kfs_orb_alias_desc(const kfs_orb *o, const uint8_t *host, int rows, int device)
+{
+    if (!o || !o->alias_valid || !o->arena || o->device != device || !host || rows <= 0) return nullptr;
+    const KfsHostBatch &hb = o->pending;
+    if (!hb.desc_out || hb.capacity <= 0 || host < hb.desc_out) return nullptr;
+    const size_t off = (size_t)(host - hb.desc_out), fs = (size_t)hb.capacity * 32;
+    if (off % fs) return nullptr;
+    const size_t f = off / fs;
+    if (f >= (size_t)hb.batch || (hb.skip_rows && hb.skip_rows[f])) return nullptr;
+    const int cp = hb.capacity < o->cap_out ? hb.capacity : o->cap_out;
+    const int live = o->h_counts[f] < cp ? o->h_counts[f] : cp;
+    if (rows > live) return nullptr;
+    return o->g.desc + f * (size_t)o->cap_out * 32;
 }
 
 void kfs_orb_internal_start_fence(kfs_orb *o, bool on) { o->start_fence = on; }
@@ -2286,9 +2365,14 @@ kfs_status kfs_orb_detect_and_compute_batch(kfs_orb *o, const uint8_t *gray, siz
     if (!n_out || capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "n_out is NULL or capacity < 0");
     for (int f = 0; f < batch; f++) n_out[f] = 0;
     if (w == 0 || h == 0) return KFS_OK; // OpenCV returns early on an empty image
-    s = kfs_orb_enqueue_host_batch(o, gray, step, frame_stride, w, h, batch, mask, mask_step, mask_frame_stride, kp_out, desc_out, capacity);
+    KfsHostBatch hb = {};
+    hb.image = gray; hb.step = step; hb.frame_stride = frame_stride; hb.w = w; hb.h = h; hb.channels = 1; hb.batch = batch;
+    hb.mask = mask; hb.mask_step = mask_step; hb.mask_frame_stride = mask_frame_stride;
+    hb.kp_out = kp_out; hb.desc_out = desc_out; hb.capacity = capacity;
+    hb.out_rows = o->p.nfeatures; // rows past nfeatures exist only after ties: fetched by finish() when a count says so
+    s = kfs_orb_enqueue_host_batch(o, hb);
     if (s) return s;
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     KFS_CUDA_TRY(cudaStreamSynchronize(o->s_out));
     KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
     return kfs_orb_finish_host_batch(o, batch, n_out);
@@ -2324,7 +2408,7 @@ kfs_status kfs_orb_download_level(kfs_orb *o, int frame, int level, uint8_t *out
 {
     if (!o || !o->arena || !out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_download_level: bad arguments");
     if (level < 0 || level >= o->nlevels_active || frame < 0 || frame >= o->last_batch) KFS_FAIL(KFS_ERR_INVALID_ARG, "frame/level out of range");
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     const LevelDev &L = o->g.lv[level];
     KFS_CUDA_TRY(cudaMemcpy2DAsync(out, out_step, L.img + (size_t)frame * L.img_fs, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost, o->stream));
     KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
@@ -2335,7 +2419,7 @@ kfs_status kfs_orb_set_blur_fma(kfs_orb *o, int fma)
 {
     if (!o) KFS_FAIL(KFS_ERR_INVALID_ARG, "orb handle is NULL");
     if (o->blur_fma != (fma != 0)) {
-        KfsDeviceGuard guard(o->device);
+        KFS_DEVICE_GUARD(o->device);
         KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
         kfs_orb_drop_graphs(o); // the captured chains hold the other kernel
         o->blur_fma = fma != 0;
@@ -2347,7 +2431,7 @@ kfs_status kfs_orb_download_blurred_level(kfs_orb *o, int frame, int level, uint
 {
     if (!o || !o->arena || !out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_download_blurred_level: bad arguments");
     if (level < 0 || level >= o->nlevels_active || frame < 0 || frame >= o->last_batch) KFS_FAIL(KFS_ERR_INVALID_ARG, "frame/level out of range");
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     const LevelDev &L = o->g.lv[level];
     if (!L.blur) KFS_FAIL(KFS_ERR_INVALID_ARG, "level %d has no blurred copy (too small to hold a keypoint)", level);
     KFS_CUDA_TRY(cudaMemcpy2DAsync(out, out_step, L.blur + (size_t)frame * L.img_fs_blur, (size_t)L.pitch_blur, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost, o->stream));
@@ -2359,7 +2443,7 @@ kfs_status kfs_orb_download_fast_corners(kfs_orb *o, int frame, int level, uint3
 {
     if (!o || !o->arena || !n_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_download_fast_corners: bad arguments");
     if (level < 0 || level >= o->nlevels_active || frame < 0 || frame >= o->last_batch) KFS_FAIL(KFS_ERR_INVALID_ARG, "frame/level out of range");
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     const LevelDev &L = o->g.lv[level];
     int n = 0;
     KFS_CUDA_TRY(cudaMemcpyAsync(&n, o->g.raw_count + frame * KFS_MAX_LEVELS + level, sizeof(int), cudaMemcpyDeviceToHost, o->stream));
@@ -2384,7 +2468,7 @@ kfs_status kfs_orb_set_profiling(kfs_orb *o, int on)
 kfs_status kfs_orb_stage_times(kfs_orb *o, float *ms)
 {
     if (!o || !ms) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_orb_stage_times: bad arguments");
-    KfsDeviceGuard guard(o->device);
+    KFS_DEVICE_GUARD(o->device);
     if (o->profiling && o->ev_made) {
         KFS_CUDA_TRY(cudaStreamSynchronize(o->stream));
         for (int i = 0; i < KFS_STAGE_COUNT; i++) {

@@ -16,7 +16,8 @@
 #include <vector>
 #include <new>
 
-constexpr int RP_ARENAS = 3; // batches in flight: one uploading, one in the kernels, one downloading
+constexpr int RP_ARENAS_DEFAULT = 3; // batches in flight: one uploading, one in the kernels, one downloading
+constexpr int RP_MAX_ARENAS = KFS_REPLAY_MAX_ARENAS;
 
 struct ReplaySlot {
     bool in_flight = false;
@@ -28,15 +29,18 @@ struct ReplaySlot {
     int *h_small = nullptr;   // pinned mirror
     BfPairDev *d_table = nullptr, *h_table = nullptr; // device / pinned
     std::vector<BfPairDev> last_table;
+    std::vector<uint8_t> skip;  // per frame: keypoints / descriptors not wanted on the host
+    int rows = 0;               // kNN / survivor rows per frame the eager copies carried
 };
 
 struct kfs_replay {
     kfs_replay_params p;
     int device = 0;
-    kfs_orb *orb[RP_ARENAS] = {};
+    int arenas = RP_ARENAS_DEFAULT;
+    kfs_orb *orb[RP_MAX_ARENAS] = {};
     kfs_bf *bf = nullptr;
     cudaStream_t compute = nullptr;
-    ReplaySlot slot[RP_ARENAS];
+    ReplaySlot slot[RP_MAX_ARENAS];
     uint8_t *d_kf_desc = nullptr; // [slots][cap][32]
     int *d_kf_count = nullptr;    // [slots]
     int cap = 0;
@@ -61,11 +65,29 @@ static kfs_status replay_finish(kfs_replay *r, int b)
     KFS_CUDA_TRY(cudaEventSynchronize(S.ev_done));
     S.in_flight = false;
     kfs_status rc = kfs_orb_finish_host_batch(r->orb[b], S.batch, S.io.n_kp);
-    const int mb = r->p.max_batch;
+    const int mb = r->p.max_batch, cap = r->cap;
+    const int cp = S.io.capacity < cap ? S.io.capacity : cap;
+    cudaStream_t s_out;
+    kfs_orb_internal_streams(r->orb[b], nullptr, &s_out);
+    bool late = false;
     for (int i = 0; i < S.batch; i++) {
-        if (S.io.n_good) S.io.n_good[i] = S.h_small[i];
-        if (S.io.n_query) S.io.n_query[i] = S.h_small[mb + i];
+        const int ng = S.h_small[i], nq = S.h_small[mb + i];
+        if (S.io.n_good) S.io.n_good[i] = ng;
+        if (S.io.n_query) S.io.n_query[i] = nq;
+        // a keyframe that kept more rows than the eager copies carried (ties): the rest of its kNN rows / survivors now
+        const int lq = nq < cp ? nq : cp, lg = ng < cp ? ng : cp;
+        if (S.io.knn && lq > S.rows) {
+            KFS_CUDA_TRY(cudaMemcpyAsync(S.io.knn + ((size_t)i * S.io.capacity + S.rows) * 2, S.d_knn + ((size_t)i * cap + S.rows) * 2,
+                                         (size_t)(lq - S.rows) * 2 * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, s_out));
+            late = true;
+        }
+        if (S.io.good && r->p.ratio > 0.f && lg > S.rows) {
+            KFS_CUDA_TRY(cudaMemcpyAsync(S.io.good + (size_t)i * S.io.capacity + S.rows, S.d_good + (size_t)i * cap + S.rows,
+                                         (size_t)(lg - S.rows) * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, s_out));
+            late = true;
+        }
     }
+    if (late) KFS_CUDA_TRY(cudaStreamSynchronize(s_out));
     return rc;
 }
 
@@ -79,6 +101,7 @@ void kfs_replay_default_params(kfs_replay_params *p)
     p->keyframe_slots = 8;
     p->ratio = 0.6f; /* VisualOdometry.cpp:46 */
     p->chunk_frames = 0;
+    p->arenas = 0;
 }
 
 void kfs_replay_destroy(kfs_replay *r)
@@ -86,7 +109,7 @@ void kfs_replay_destroy(kfs_replay *r)
     if (!r) return;
     KfsDeviceGuard guard(r->device);
     if (r->compute) cudaStreamSynchronize(r->compute);
-    for (int b = 0; b < RP_ARENAS; b++) {
+    for (int b = 0; b < RP_MAX_ARENAS; b++) {
         ReplaySlot &S = r->slot[b];
         if (S.ev_done) { if (S.in_flight) cudaEventSynchronize(S.ev_done); cudaEventDestroy(S.ev_done); }
         if (S.ev_knn) cudaEventDestroy(S.ev_knn);
@@ -111,15 +134,19 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
     *out = nullptr;
     if (params->max_batch < 1 || params->max_batch > 65535 || params->keyframe_slots < 1 || params->chunk_frames < 0)
         KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_replay_create: 1 <= max_batch <= 65535 and keyframe_slots >= 1 required");
+    if (params->arenas != 0 && (params->arenas < 2 || params->arenas > RP_MAX_ARENAS))
+        KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_replay_create: arenas must be 0 (default) or 2..%d", RP_MAX_ARENAS);
     kfs_replay *r = new (std::nothrow) kfs_replay();
     if (!r) KFS_FAIL(KFS_ERR_INVALID_ARG, "out of host memory");
     r->p = *params;
     r->device = device;
+    r->arenas = params->arenas ? params->arenas : RP_ARENAS_DEFAULT;
     kfs_status s = KFS_OK;
-    for (int b = 0; b < RP_ARENAS && !s; b++) s = kfs_orb_create(&params->orb, device, &r->orb[b]);
+    for (int b = 0; b < r->arenas && !s; b++) s = kfs_orb_create(&params->orb, device, &r->orb[b]);
     if (!s) s = kfs_bf_create(KFS_NORM_HAMMING, 0, device, &r->bf);
     if (s) { kfs_replay_destroy(r); return s; }
     KfsDeviceGuard guard(device);
+    if (!guard.ok) { kfs_replay_destroy(r); KFS_FAIL(KFS_ERR_CUDA, "cudaSetDevice(%d) failed", device); }
     r->cap = kfs_orb_capacity(r->orb[0]);
     const size_t mb = (size_t)params->max_batch, cap = (size_t)r->cap;
 #define RP_TRY(expr)                                                                                       \
@@ -132,7 +159,7 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
         }                                                                                                  \
     } while (0)
     RP_TRY(cudaStreamCreateWithFlags(&r->compute, cudaStreamNonBlocking));
-    for (int b = 0; b < RP_ARENAS; b++) {
+    for (int b = 0; b < r->arenas; b++) {
         ReplaySlot &S = r->slot[b];
         kfs_orb_set_stream(r->orb[b], (void *)r->compute);
         kfs_orb_internal_start_fence(r->orb[b], false); // arena reuse is ordered by replay_finish instead
@@ -155,7 +182,7 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
 }
 
 int kfs_replay_capacity(const kfs_replay *r) { return r ? r->cap : 0; }
-int kfs_replay_arenas(const kfs_replay *r) { return r ? RP_ARENAS : 0; }
+int kfs_replay_arenas(const kfs_replay *r) { return r ? r->arenas : 0; }
 int kfs_replay_last_launches(const kfs_replay *r) { return r ? r->launches : 0; }
 
 kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_replay_frame *plan, int batch, int *ticket)
@@ -170,15 +197,28 @@ kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_r
             KFS_FAIL(KFS_ERR_INVALID_ARG, "plan[%d].keyframe = %d: not a frame of this batch nor a cache slot", i, k);
         if (plan[i].store_slot < -1 || plan[i].store_slot >= r->p.keyframe_slots)
             KFS_FAIL(KFS_ERR_INVALID_ARG, "plan[%d].store_slot = %d out of range", i, plan[i].store_slot);
+        if (plan[i].flags & ~KFS_REPLAY_SKIP_ROWS) KFS_FAIL(KFS_ERR_INVALID_ARG, "plan[%d].flags = %d: unknown bits", i, plan[i].flags);
     }
-    KfsDeviceGuard guard(r->device);
-    const int b = r->seq % RP_ARENAS;
+    if (io->channels != 0 && io->channels != 1 && io->channels != 3)
+        KFS_FAIL(KFS_ERR_UNSUPPORTED, "io->channels = %d (the reference handles 1 or 3, VisualOdometry.cpp:27)", io->channels);
+    KFS_DEVICE_GUARD(r->device);
+    const int b = r->seq % r->arenas;
     ReplaySlot &S = r->slot[b];
     kfs_status s = replay_finish(r, b); // the arena is reused: its previous batch must be complete (results already delivered)
     if (s && s != KFS_ERR_CAPACITY) return s;
     kfs_orb *o = r->orb[b];
     // 1. upload + extraction (+ D2H of keypoints / descriptors / counts), nothing synchronises
-    s = kfs_orb_enqueue_host_batch(o, io->gray, io->step, io->frame_stride, io->w, io->h, batch, nullptr, 0, 0, io->kp, io->desc, io->capacity);
+    bool any_skip = false;
+    S.skip.assign((size_t)batch, 0);
+    for (int i = 0; i < batch; i++) if (plan[i].flags & KFS_REPLAY_SKIP_ROWS) { S.skip[(size_t)i] = 1; any_skip = true; }
+    KfsHostBatch hb = {};
+    hb.image = io->gray; hb.step = io->step; hb.frame_stride = io->frame_stride; hb.w = io->w; hb.h = io->h;
+    hb.channels = io->channels == 3 ? 3 : 1; hb.batch = batch;
+    hb.mask = io->mask; hb.mask_step = io->mask_step; hb.mask_frame_stride = io->mask_frame_stride;
+    hb.kp_out = io->kp; hb.desc_out = io->desc; hb.capacity = io->capacity;
+    hb.out_rows = r->p.orb.nfeatures;
+    hb.skip_rows = any_skip ? S.skip.data() : nullptr;
+    s = kfs_orb_enqueue_host_batch(o, hb);
     if (s) return s;
     r->launches = kfs_orb_last_launches(o);
     const kfs_keypoint *d_kp; const uint8_t *d_desc; const int *d_cnt; int cap = 0, nb = 0;
@@ -230,18 +270,17 @@ kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_r
     }
     KFS_CUDA_TRY(cudaEventRecord(S.ev_knn, r->compute));
     KFS_CUDA_TRY(cudaStreamWaitEvent(s_out, S.ev_knn, 0));
+    S.rows = 0;
     if (want_knn) {
         const int cp = io->capacity < cap ? io->capacity : cap;
-        if (io->knn && cp > 0 && io->capacity == cap)
-            KFS_CUDA_TRY(cudaMemcpyAsync(io->knn, S.d_knn, (size_t)batch * cap * 2 * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, s_out));
-        else if (io->knn && cp > 0)
+        const int rows = r->p.orb.nfeatures < cp ? r->p.orb.nfeatures : cp; // what a keyframe without ties can fill; the rest: replay_finish
+        S.rows = rows;
+        if (io->knn && rows > 0)
             KFS_CUDA_TRY(cudaMemcpy2DAsync(io->knn, (size_t)io->capacity * 2 * sizeof(kfs_dmatch), S.d_knn, (size_t)cap * 2 * sizeof(kfs_dmatch),
-                                           (size_t)cp * 2 * sizeof(kfs_dmatch), (size_t)batch, cudaMemcpyDeviceToHost, s_out));
-        if (io->good && cp > 0 && r->p.ratio > 0.f && io->capacity == cap)
-            KFS_CUDA_TRY(cudaMemcpyAsync(io->good, S.d_good, (size_t)batch * cap * sizeof(kfs_dmatch), cudaMemcpyDeviceToHost, s_out));
-        else if (io->good && cp > 0 && r->p.ratio > 0.f)
+                                           (size_t)rows * 2 * sizeof(kfs_dmatch), (size_t)batch, cudaMemcpyDeviceToHost, s_out));
+        if (io->good && rows > 0 && r->p.ratio > 0.f)
             KFS_CUDA_TRY(cudaMemcpy2DAsync(io->good, (size_t)io->capacity * sizeof(kfs_dmatch), S.d_good, (size_t)cap * sizeof(kfs_dmatch),
-                                           (size_t)cp * sizeof(kfs_dmatch), (size_t)batch, cudaMemcpyDeviceToHost, s_out));
+                                           (size_t)rows * sizeof(kfs_dmatch), (size_t)batch, cudaMemcpyDeviceToHost, s_out));
         KFS_CUDA_TRY(cudaMemcpyAsync(S.h_small, S.d_small, 2 * sizeof(int) * (size_t)r->p.max_batch, cudaMemcpyDeviceToHost, s_out));
     } else {
         memset(S.h_small, 0, 2 * sizeof(int) * (size_t)r->p.max_batch);
@@ -259,8 +298,8 @@ kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_r
 kfs_status kfs_replay_wait(kfs_replay *r, int ticket)
 {
     if (!r) KFS_FAIL(KFS_ERR_INVALID_ARG, "replay handle is NULL");
-    KfsDeviceGuard guard(r->device);
-    for (int b = 0; b < RP_ARENAS; b++)
+    KFS_DEVICE_GUARD(r->device);
+    for (int b = 0; b < r->arenas; b++)
         if (r->slot[b].in_flight && r->slot[b].ticket == ticket) return replay_finish(r, b);
     if (ticket >= 0 && ticket < r->seq) return KFS_OK; // already delivered (its arena was reused, or waited before)
     KFS_FAIL(KFS_ERR_INVALID_ARG, "unknown ticket %d", ticket);

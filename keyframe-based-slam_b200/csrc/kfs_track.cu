@@ -18,11 +18,13 @@
 __device__ __forceinline__ uint32_t kfs_gray15(uint32_t r, uint32_t g, uint32_t b) { return (r * 9798u + g * 19235u + b * 3735u + 16384u) >> 15; }
 
 __global__ void __launch_bounds__(256)
-k_rgb2gray(const uint8_t *__restrict__ src, long long sstep, uint8_t *__restrict__ dst, int dpitch, int w, int h, int aligned)
+k_rgb2gray(const uint8_t *__restrict__ src, long long sstep, long long sfs, uint8_t *__restrict__ dst, int dpitch, long long dfs, int w, int h, int aligned)
 {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
     const int y = blockIdx.y * 8 + threadIdx.y;
     if (x4 >= dpitch || y >= h) return;
+    src += (long long)blockIdx.z * sfs; // blockIdx.z = frame of the batch
+    dst += (long long)blockIdx.z * dfs;
     const uint8_t *row = src + (long long)y * sstep;
     uint32_t out = 0;
     if (aligned && x4 + 4 <= w) {
@@ -40,6 +42,18 @@ k_rgb2gray(const uint8_t *__restrict__ src, long long sstep, uint8_t *__restrict
         }
     }
     *reinterpret_cast<uint32_t *>(dst + (long long)y * dpitch + x4) = out;
+}
+
+// nframes colour frames (sfs bytes apart) -> gray frames (dfs bytes apart); src rows 4-byte aligned and sstep % 4 == 0 take the
+// three-word path.  Shared with the ORB handle's host-batch pipeline (kfs_orb.cu) and the replay executor.
+kfs_status kfs_launch_rgb2gray(const uint8_t *src, long long sstep, long long sfs, uint8_t *dst, int dpitch, long long dfs, int w, int h, int nframes,
+                               cudaStream_t st)
+{
+    const int aligned = ((uintptr_t)src % 4 == 0) && (sstep % 4 == 0) && (sfs % 4 == 0);
+    k_rgb2gray<<<dim3(kfs_div_up(dpitch, 128), kfs_div_up(h, 8), nframes), dim3(32, 8), 0, st>>>(src, sstep, sfs, dst, dpitch, dfs, w, h, aligned);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_rgb2gray launch: %s", cudaGetErrorString(e));
+    return KFS_OK;
 }
 
 // ---- MatchFeatures :45-59 --------------------------------------------------------------------------------------
@@ -218,6 +232,23 @@ static kfs_status fe_alloc_ring(kfs_frontend *fe, int window)
     return KFS_OK;
 }
 
+// Buffers with one row per keypoint: sized from the extractor's capacity (kfs_orb_capacity), rebuilt by kfs_frontend_set_capacity.
+static kfs_status fe_alloc_rows(kfs_frontend *fe)
+{
+    void **bufs[] = {(void **)&fe->d_up_desc, (void **)&fe->d_up_kp, (void **)&fe->d_knn, (void **)&fe->d_good, (void **)&fe->d_p3d, (void **)&fe->d_p2d};
+    for (void **b : bufs) if (*b) { cudaFree(*b); *b = nullptr; }
+    fe->cap = kfs_orb_capacity(fe->orb);
+    const size_t n = (size_t)fe->cap;
+    cudaError_t e = cudaMalloc(&fe->d_up_desc, n * 32);
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_up_kp, n * sizeof(kfs_keypoint));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_knn, n * 2 * sizeof(kfs_dmatch));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_good, n * sizeof(kfs_dmatch));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_p3d, n * 3 * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_p2d, n * 2 * sizeof(double));
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "kfs_frontend: row buffers for capacity %d: %s", fe->cap, cudaGetErrorString(e));
+    return KFS_OK;
+}
+
 // Slot the next keyframe goes into (committed by fe_commit_slot once its uploads are enqueued).
 static KfSlot *fe_next_slot(kfs_frontend *fe) { return fe->window > 0 ? &fe->ring[(size_t)((fe->head + 1) % fe->window)] : nullptr; }
 static void fe_commit_slot(kfs_frontend *fe)
@@ -260,24 +291,18 @@ kfs_status kfs_frontend_create(const kfs_orb_params *params, int device, kfs_fro
     if (!s) s = kfs_bf_create(KFS_NORM_HAMMING, 0, device, &fe->bf);
     if (s) { kfs_frontend_destroy(fe); return s; }
     KfsDeviceGuard guard(device);
+    if (!guard.ok) { kfs_frontend_destroy(fe); KFS_FAIL(KFS_ERR_CUDA, "cudaSetDevice(%d) failed", device); }
     fe->stream = (cudaStream_t)kfs_orb_get_stream(fe->orb);
     kfs_bf_set_stream(fe->bf, (void *)fe->stream);
-    fe->cap = kfs_orb_capacity(fe->orb);
-    const size_t n = (size_t)fe->cap;
-    cudaError_t e = cudaSuccess;
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_up_desc, n * 32);
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_up_kp, n * sizeof(kfs_keypoint));
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_knn, n * 2 * sizeof(kfs_dmatch));
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_good, n * sizeof(kfs_dmatch));
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_p3d, n * 3 * sizeof(double));
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_p2d, n * 2 * sizeof(double));
-    if (e == cudaSuccess) e = cudaMalloc(&fe->d_nout, sizeof(int));
-    if (e == cudaSuccess) e = cudaMallocHost(&fe->h_nout, 2 * sizeof(int));
+    cudaError_t e = cudaMallocHost(&fe->h_nout, 2 * sizeof(int));
     if (e == cudaSuccess) e = cudaMallocHost(&fe->h_wn, KFS_MAX_WINDOW * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&fe->d_nout, sizeof(int));
     if (e != cudaSuccess) {
         kfs_frontend_destroy(fe);
         KFS_FAIL(KFS_ERR_CUDA, "kfs_frontend_create: %s", cudaGetErrorString(e));
     }
+    s = fe_alloc_rows(fe);
+    if (s) { kfs_frontend_destroy(fe); return s; }
     s = fe_alloc_ring(fe, 1);
     if (s) { kfs_frontend_destroy(fe); return s; }
     *out = fe;
@@ -285,6 +310,22 @@ kfs_status kfs_frontend_create(const kfs_orb_params *params, int device, kfs_fro
 }
 
 int kfs_frontend_capacity(const kfs_frontend *fe) { return fe ? fe->cap : 0; }
+
+// Rows per frame the handle can hold (kfs_orb_set_capacity of the extractor + every per-row buffer + the keyframe ring).  The
+// cached keyframes and the current frame are dropped, like kfs_frontend_set_window: call it before tracking starts, or after
+// KFS_ERR_CAPACITY told how many rows a tie-rich frame needs.
+kfs_status kfs_frontend_set_capacity(kfs_frontend *fe, int capacity)
+{
+    if (!fe || capacity < 1) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_frontend_set_capacity: bad arguments");
+    KFS_DEVICE_GUARD(fe->device);
+    KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream));
+    kfs_status s = kfs_orb_set_capacity(fe->orb, capacity);
+    if (s) return s;
+    fe->cur_n = -1; fe->d_cur_desc = nullptr; fe->d_cur_kp = nullptr; fe->d_cur_count = nullptr;
+    s = fe_alloc_rows(fe);
+    if (s) return s;
+    return fe_alloc_ring(fe, fe->window > 0 ? fe->window : 1);
+}
 int kfs_frontend_last_launches(const kfs_frontend *fe) { return fe ? fe->launches : 0; }
 
 // Validates the frame, uploads it (+ mask), converts colour and runs the ORB chain; nothing synchronises.  On return the
@@ -306,9 +347,8 @@ static kfs_status fe_enqueue_extract(kfs_frontend *fe, const uint8_t *image, siz
         s = fe_reserve(&fe->d_img, &fe->img_bytes, ipitch * h);
         if (s) return s;
         KFS_CUDA_TRY(cudaMemcpy2DAsync(fe->d_img, ipitch, image, step, (size_t)w * 3, h, cudaMemcpyHostToDevice, st));
-        k_rgb2gray<<<dim3(kfs_div_up((int)gpitch, 128), kfs_div_up(h, 8)), dim3(32, 8), 0, st>>>(fe->d_img, (long long)ipitch, fe->d_gray, (int)gpitch, w, h, 1);
-        cudaError_t e = cudaGetLastError();
-        if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_rgb2gray launch: %s", cudaGetErrorString(e));
+        s = kfs_launch_rgb2gray(fe->d_img, (long long)ipitch, 0, fe->d_gray, (int)gpitch, 0, w, h, 1, st);
+        if (s) return s;
         fe->launches++;
     } else {
         KFS_CUDA_TRY(cudaMemcpy2DAsync(fe->d_gray, gpitch, image, step, (size_t)w, h, cudaMemcpyHostToDevice, st));
@@ -340,7 +380,7 @@ kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t *image,
     if (w < 0 || h < 0 || capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "negative size");
     if (w == 0 || h == 0) { fe->cur_n = 0; return KFS_OK; }
     if (capacity > 0 && (!kp_out || !desc_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
-    KfsDeviceGuard guard(fe->device);
+    KFS_DEVICE_GUARD(fe->device);
     kfs_status s = fe_enqueue_extract(fe, image, step, w, h, channels, mask, mask_step, "ExtractFeatures");
     if (s) return s;
     s = kfs_orb_fetch_results(fe->orb, kp_out, desc_out, capacity, n_out);
@@ -366,7 +406,7 @@ kfs_status kfs_frontend_promote_keyframe(kfs_frontend *fe, const uint16_t *depth
 {
     if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
     if (fe->cur_n < 0 || !fe->d_cur_desc) KFS_FAIL(KFS_ERR_INVALID_ARG, "promote_keyframe: no frame has been extracted on this handle yet");
-    KfsDeviceGuard guard(fe->device);
+    KFS_DEVICE_GUARD(fe->device);
     KfSlot *k = fe_next_slot(fe);
     kfs_status s = fe_upload_depth(fe, k, depth, depth_step, fe->cur_w, fe->cur_h);
     if (s) return s;
@@ -374,6 +414,8 @@ kfs_status kfs_frontend_promote_keyframe(kfs_frontend *fe, const uint16_t *depth
         KFS_CUDA_TRY(cudaMemcpyAsync(k->desc, fe->d_cur_desc, (size_t)fe->cur_n * 32, cudaMemcpyDeviceToDevice, fe->stream));
         KFS_CUDA_TRY(cudaMemcpyAsync(k->kp, fe->d_cur_kp, (size_t)fe->cur_n * sizeof(kfs_keypoint), cudaMemcpyDeviceToDevice, fe->stream));
     }
+    // the caller may reuse its depth buffer for the next frame right away (a pinned buffer makes the upload truly asynchronous)
+    KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream));
     k->n = fe->cur_n;
     fe_commit_slot(fe);
     return KFS_OK;
@@ -385,7 +427,7 @@ kfs_status kfs_frontend_set_keyframe(kfs_frontend *fe, const uint8_t *desc, cons
     if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
     if (n < 0 || n > fe->cap) KFS_FAIL(KFS_ERR_CAPACITY, "set_keyframe: %d rows, handle capacity %d", n, fe->cap);
     if (n > 0 && (!desc || !kp)) KFS_FAIL(KFS_ERR_INVALID_ARG, "desc or kp is NULL");
-    KfsDeviceGuard guard(fe->device);
+    KFS_DEVICE_GUARD(fe->device);
     KfSlot *k = fe_next_slot(fe);
     kfs_status s = fe_upload_depth(fe, k, depth, depth_step, w, h);
     if (s) return s;
@@ -449,7 +491,7 @@ kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc
     if (!kf) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_features: no keyframe cached (promote_keyframe / set_keyframe first)");
     if (capacity < 0 || (capacity > 0 && (!matches_out || !points3d_out || !points2d_out))) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers");
     if (intrinsics[0] == 0.0 || intrinsics[1] == 0.0) KFS_FAIL(KFS_ERR_INVALID_ARG, "fx or fy is zero");
-    KfsDeviceGuard guard(fe->device);
+    KFS_DEVICE_GUARD(fe->device);
     cudaStream_t st = fe->stream;
     const kfs_keypoint *d_kp;
     const uint8_t *d_desc;
@@ -492,7 +534,7 @@ kfs_status kfs_frontend_track(kfs_frontend *fe, const uint8_t *image, size_t ste
     if (capacity > 0 && (!kp_out || !desc_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
     if (match_capacity > 0 && (!matches_out || !points3d_out || !points2d_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "match output buffers are NULL");
     if (intrinsics[0] == 0.0 || intrinsics[1] == 0.0) KFS_FAIL(KFS_ERR_INVALID_ARG, "fx or fy is zero");
-    KfsDeviceGuard guard(fe->device);
+    KFS_DEVICE_GUARD(fe->device);
     cudaStream_t st = fe->stream;
     kfs_status s = fe_enqueue_extract(fe, image, step, w, h, channels, mask, mask_step, "Track");
     if (s) return s;
@@ -534,7 +576,7 @@ kfs_status kfs_frontend_set_window(kfs_frontend *fe, int window)
 {
     if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
     if (window < 1 || window > KFS_MAX_WINDOW) KFS_FAIL(KFS_ERR_INVALID_ARG, "set_window: %d not in [1, %d]", window, KFS_MAX_WINDOW);
-    KfsDeviceGuard guard(fe->device);
+    KFS_DEVICE_GUARD(fe->device);
     KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream));
     return fe_alloc_ring(fe, window);
 }
@@ -548,7 +590,7 @@ kfs_status kfs_frontend_match_window(kfs_frontend *fe, const uint8_t *cur_desc, 
     if (!fe || !n_kf_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle or n_kf_out is NULL");
     *n_kf_out = 0;
     if (capacity < 0 || knn_rows < 0 || (capacity > 0 && !good_out) || !n_good_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_window: output buffers");
-    KfsDeviceGuard guard(fe->device);
+    KFS_DEVICE_GUARD(fe->device);
     cudaStream_t st = fe->stream;
     const uint8_t *d_desc;
     const int *d_cnt = nullptr;

@@ -259,12 +259,12 @@ class Replay:
     NO_MATCH = N.REPLAY_NO_MATCH
 
     def __init__(self, nfeatures=500, scaleFactor=1.2, nlevels=8, fastThreshold=20, max_batch=64, keyframe_slots=8,
-                 ratio=0.6, chunk_frames=0, device=0):
+                 ratio=0.6, chunk_frames=0, device=0, arenas=0):
         self._h = C.c_void_p()
         p = N.ReplayParams()
         N.lib().kfs_replay_default_params(C.byref(p))
         p.orb.nfeatures, p.orb.scale_factor, p.orb.nlevels, p.orb.fast_threshold = nfeatures, scaleFactor, nlevels, fastThreshold
-        p.max_batch, p.keyframe_slots, p.ratio, p.chunk_frames = max_batch, keyframe_slots, ratio, chunk_frames
+        p.max_batch, p.keyframe_slots, p.ratio, p.chunk_frames, p.arenas = max_batch, keyframe_slots, ratio, chunk_frames, arenas
         N.check(N.lib().kfs_replay_create(C.byref(p), device, C.byref(self._h)))
         self.max_batch = max_batch
         self._keep = {}
@@ -292,16 +292,25 @@ class Replay:
                     knn=mk((batch, cap, 2), DM_DTYPE), n_query=mk((batch,), np.int32),
                     good=mk((batch, cap), DM_DTYPE), n_good=mk((batch,), np.int32))
 
-    def submit(self, frames, plan, out):
-        """frames uint8 [B,H,W] (host, C-contiguous); plan: list of (keyframe, store_slot); out: alloc_outputs()."""
-        B, H, W = frames.shape
-        assert frames.dtype == np.uint8 and frames.flags.c_contiguous
-        io = N.ReplayIO(frames.ctypes.data, W, W * H, W, H, out["kp"].ctypes.data, out["desc"].ctypes.data, out["kp"].shape[1],
-                        out["n_kp"].ctypes.data, _ptr(out.get("knn")), _ptr(out.get("n_query")), _ptr(out.get("good")), _ptr(out.get("n_good")))
-        pl = (N.ReplayFrame * B)(*[N.ReplayFrame(int(k), int(s)) for k, s in plan])
+    @property
+    def arenas(self):
+        return N.lib().kfs_replay_arenas(self._h)
+
+    def submit(self, frames, plan, out, masks=None):
+        """frames uint8 [B,H,W] gray or [B,H,W,3] R,G,B (host, C-contiguous); plan: list of (keyframe, store_slot) or
+        (keyframe, store_slot, flags); out: alloc_outputs(); masks: None or uint8 [B,H,W], non-zero = keep."""
+        B, H, W = frames.shape[:3]
+        ch = 3 if frames.ndim == 4 else 1
+        assert frames.dtype == np.uint8 and frames.flags.c_contiguous and (frames.ndim == 3 or frames.shape[3] == 3)
+        if masks is not None:
+            assert masks.dtype == np.uint8 and masks.flags.c_contiguous and masks.shape == (B, H, W)
+        io = N.ReplayIO(frames.ctypes.data, W * ch, W * H * ch, W, H, out["kp"].ctypes.data, out["desc"].ctypes.data, out["kp"].shape[1],
+                        out["n_kp"].ctypes.data, _ptr(out.get("knn")), _ptr(out.get("n_query")), _ptr(out.get("good")), _ptr(out.get("n_good")),
+                        _ptr(masks), W, W * H, ch)
+        pl = (N.ReplayFrame * B)(*[N.ReplayFrame(int(e[0]), int(e[1]), int(e[2]) if len(e) > 2 else 0) for e in plan])
         t = C.c_int(-1)
         N.check(N.lib().kfs_replay_submit(self._h, C.byref(io), pl, B, C.byref(t)))
-        self._keep[t.value] = (frames, out, io, pl)
+        self._keep[t.value] = (frames, out, io, pl, masks)
         return t.value
 
     def wait(self, ticket):

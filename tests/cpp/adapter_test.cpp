@@ -84,6 +84,17 @@ int main(int argc, char **argv)
     // --- MatchFeatures (VisualOdometry.cpp:35-62): query = keyframe, train = current; ratio 0.6
     std::vector<std::vector<cv::DMatch>> knnMatches;
     ptrMatcher->knnMatch(dpA, dpB, knnMatches, 2);
+    // the same call with the matcher attached to the extractor: dpCurrImg (the frame just extracted) is matched where it
+    // still is on the device, the keyframe's rows (an older extraction) are uploaded as before; identical rows come back
+    ptrMatcher->attach(ptrExtractor);
+    std::vector<std::vector<cv::DMatch>> knnAttached;
+    ptrMatcher->knnMatch(dpA, dpB, knnAttached, 2);
+    const int aliased = kfs_bf_last_aliased(ptrMatcher->handle());
+    bool attached_same = knnAttached.size() == knnMatches.size();
+    for (size_t i = 0; attached_same && i < knnMatches.size(); i++)
+        attached_same = knnAttached[i].size() == knnMatches[i].size() &&
+                        !std::memcmp(knnAttached[i].data(), knnMatches[i].data(), knnMatches[i].size() * sizeof(cv::DMatch));
+    ptrMatcher->attach(nullptr);
     std::vector<cv::DMatch> matches;
     for (size_t i = 0; i < knnMatches.size(); i++)
         if (knnMatches[i].size() >= 2 && knnMatches[i][0].distance < 0.6f * knnMatches[i][1].distance) matches.push_back(knnMatches[i][0]);
@@ -98,7 +109,8 @@ int main(int argc, char **argv)
 
     std::ofstream out(argv[6], std::ios::binary);
     auto put32 = [&](int v) { out.write((const char *)&v, 4); };
-    put32((int)kpA.size()); put32((int)kpB.size()); put32((int)knnMatches.size()); put32((int)matches.size()); put32(threw);
+    put32((int)kpA.size()); put32((int)kpB.size()); put32((int)knnMatches.size()); put32((int)matches.size());
+    put32(threw + 16 * aliased + (attached_same ? 256 : 0)); // bits 0-3: exceptions seen, 4-7: matrices matched in place, 8: attached == plain
     out.write((const char *)kpA.data(), (std::streamsize)(kpA.size() * sizeof(cv::KeyPoint)));
     for (int r = 0; r < dpA.rows; r++) out.write((const char *)dpA.ptr(r), 32);
     out.write((const char *)kpB.data(), (std::streamsize)(kpB.size() * sizeof(cv::KeyPoint)));
