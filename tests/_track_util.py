@@ -23,3 +23,18 @@ def make_depth(h, w, seed):
     d = 800 + 3 * xx + 2 * yy + rng.integers(0, 50, (h, w))
     d[rng.random((h, w)) < 0.02] = 0
     return d.astype(np.uint16)
+
+
+def make_refset_mask(h, w, seed):
+    """A mask like the one the reference's camera feed delivers with every frame (main.cpp:31-34): a valid region with holes
+    and a ragged border; values 0 / 255."""
+    rng = np.random.default_rng(seed)
+    m = np.full((h, w), 255, np.uint8)
+    m[:, :40] = 0
+    m[:25, :] = 0
+    for _ in range(30):
+        x0, y0 = int(rng.integers(0, w - 80)), int(rng.integers(0, h - 60))
+        m[y0:y0 + int(rng.integers(8, 60)), x0:x0 + int(rng.integers(8, 80))] = 0
+    yy, xx = np.mgrid[0:h, 0:w]
+    m[(yy - h * 0.6) ** 2 + (xx - w * 0.7) ** 2 < (h * 0.12) ** 2] = 0
+    return m

@@ -110,3 +110,29 @@ def test_argument_validation_without_device():
     with pytest.raises(kfs.KfsError) as e:
         kfs.BFMatcher_create(4)
     assert e.value.status == 2
+
+
+@pytest.mark.parametrize("n,world,batch", [(10000, 1, 128), (10000, 8, 128), (95, 2, 7), (45, 2, 16), (45, 2, 5), (33, 1, 4), (200, 3, 10)])
+def test_plan_shard_resolves_every_keyframe(n, world, batch):
+    """replay.plan_shard: every owned frame is matched against keyframe_of(frame) — through an in-submit index or a cache slot an
+    EARLIER submit stored (simulated here) — the halo leads the first submit unmatched, owned frames cover the shard in order."""
+    for r in range(world):
+        lo, hi, halo = replay.shard_frames(n, world, r)
+        subs = replay.plan_shard(lo, hi, halo, batch)
+        cache, seen = {}, []
+        for s in subs:
+            assert 0 < len(s["frames"]) <= batch
+            for f, (kf, st, fl), own in zip(s["frames"], s["plan"], s["owned"]):
+                if own:
+                    seen.append(f)
+                    got = s["frames"][kf] if kf >= 0 else cache[-(kf + 1)]
+                    assert got == replay.keyframe_of(f) and fl == 0
+                else:
+                    assert f == halo and kf == replay.NO_MATCH and fl == replay.SKIP_ROWS
+            for f, (kf, st, fl) in zip(s["frames"], s["plan"]):
+                assert st in (-1, 0, 1)
+                if st >= 0:
+                    cache[st] = f
+        assert seen == list(range(lo, hi))
+    rows = replay.plan_shard(0, 30, -1, 16, keyframes_only_rows=True)
+    assert [fl for s in rows for (_, _, fl) in s["plan"]] == [0 if f % 10 == 0 else replay.SKIP_ROWS for f in range(30)]
