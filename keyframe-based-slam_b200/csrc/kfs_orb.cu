@@ -177,11 +177,14 @@ k_mask_binarise(const uint8_t *__restrict__ src, long long sfs, long long sstep,
 // ======================================================================================================
 // a1.3 / a1.4  FAST-9/16 score + 3x3 NMS + border / mask filter -> per-(frame, level) corner list
 // ======================================================================================================
-// One CTA = one 112x62 tile of the keepable region [31, W-31) x [31, H-31) of one level of one frame
+// One CTA = one 124x62 tile of the keepable region [31, W-31) x [31, H-31) of one level of one frame
 // (tile -> (level, tix, tiy) through a table, so one launch covers every level of every frame).
-//   source tile 128 x 70 bytes, origin (tx0-4, ty0-4): rows are 16-byte aligned in HBM -> one 128-byte line per
-//               row, 8 LDG.128 per row
-//   score  tile 128 x 64 bytes, origin (tx0-4, ty0-1)  (same x origin as the source tile)
+//   score  tile 128 x 64 bytes: column sx <-> image x = tx0 - 1 + sx, row sy <-> y = ty0 - 1 + sy.  Columns 0 .. FT_W + 1 = 125 are
+//               needed (the owned 124 + one NMS neighbour on each side): 126 of the 128 columns a warp computes are useful
+//               (FT_W = 112 with its 16-byte aligned tile origins left 114 of 128: 388 instead of 345 tiles per 720p frame)
+//   source tile 160 x 70 bytes, one TMA box whose x origin xa is the 16-byte aligned address at or below x0 = tx0 - 5; the tile's
+//               own column 0 sits sh = x0 - xa bytes into the box (sh is a multiple of 4 because FAST_X0 = 5 mod 4 and FT_W = 0
+//               mod 4, so every lane's centre word stays 4-byte aligned).  Score column sx has its centre at box column sx + 4 + sh.
 // phase 1: each warp owns score rows w, w+8, ...; a lane tests 4 horizontally adjacent pixels with the
 //          necessary condition kfs_fast_quick2 (u16x2 SIMD, two pixels per op, conflict-free LDS.32); the
 //          pass flags of a row leave the warp as 4 ballots = one 128-bit mask row in shared memory
@@ -190,10 +193,12 @@ k_mask_binarise(const uint8_t *__restrict__ src, long long sfs, long long sstep,
 // phase 2: exact score of the queued pixels (both polarities in one u16x2 word, VIMNMX3 trees)
 // phase 3: 3x3 NMS on the score tile, border/mask predicate; survivors are gathered in shared memory and
 //          appended to the (frame, level) list with ONE global atomic per tile
-constexpr int FT_W = 112, FT_H = 62;
-constexpr int FS_ROWB = 128, FS_P = 144, FS_H = FT_H + 8; // rows 144 B apart: vertically adjacent pixels sit 4 banks apart (byte gathers of phase 2)
+constexpr int FT_W = 124, FT_H = 62;
+constexpr int FS_ROWB = 160, FS_P = 160, FS_H = FT_H + 8; // box row = 4 + 128 + 4 columns + up to 12 bytes of alignment slack
 constexpr int SC_W = 128, SC_H = FT_H + 2;
-constexpr int FAST_X0 = 20; // interior x origin of tile column 0; source origin 16 (+112k) keeps rows 16B-aligned
+constexpr int FAST_X0 = 29; // interior x origin of tile column 0 (owned columns below 31 fall to the border filter)
+static_assert(FT_W % 4 == 0 && (FAST_X0 - 5) % 4 == 0 && FT_W + 2 <= SC_W, "4-byte aligned centre words; owned columns + NMS neighbours fit the score tile");
+static_assert(SC_W + 8 + 12 <= FS_P && FS_P % 16 == 0, "the source box holds the tile at every alignment shift");
 constexpr int FAST_THREADS = 256;
 constexpr int FAST_MAXOUT = (FT_W / 2) * (FT_H / 2); // strict 3x3 maxima: at most one per 2x2 block
 constexpr int FT_HH = 31;      // tile height of the low-latency variant (k_fast<FT_HH>)
@@ -383,7 +388,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     __shared__ uint16_t s_q[SC_W * SC_H];
     __shared__ __align__(16) uint32_t s_mask[FAST_THREADS]; // rows past SC_H stay zero
     __shared__ int s_wsum[FAST_THREADS / 32];
-    __shared__ int s_nout, s_gbase, s_ncorner;
+    __shared__ int s_nout, s_gbase;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int f = blockIdx.y + g.frame0;
@@ -392,7 +397,9 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     const LevelDev &L = g.lv[l];
     const int W = L.w, H = L.h, pitch = L.pitch;
     const int tx0 = FAST_X0 + FT_W * tix, ty0 = KFS_BORDER + FT_H * tiy;
-    const int ox = tx0 - 4, sy0 = ty0 - 4;
+    const int ox = tx0 - 1, sy0 = ty0 - 4;          // image x of score column 0; image y of source row 0
+    const int xa = (tx0 - 5) & ~15;                 // 16-byte aligned x origin of the source box
+    const uint8_t *s_tile = s_src + (tx0 - 5 - xa) + 4; // + r * FS_P + sx = centre of score column sx on source row r
     const uint8_t *img = L.img + (long long)f * L.img_fs;
     const int thr = g.fast_thr;
 
@@ -404,12 +411,12 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     if (tma) {
         if (tid == 0) {
             kfs_mbar_expect_tx(&s_bar, FS_P * FS_H);
-            kfs_tma_load_3d(s_src, &maps.m[l], ox, sy0, f, &s_bar);
+            kfs_tma_load_3d(s_src, &maps.m[l], xa, sy0, f, &s_bar);
         }
     } else {
         for (int i = tid; i < FS_H * (FS_ROWB / 16); i += FAST_THREADS) {
-            const int r = i >> 3, c = i & 7;
-            const int gy = min(max(sy0 + r, 0), H - 1), gx = ox + 16 * c;
+            const int r = i / (FS_ROWB / 16), c = i % (FS_ROWB / 16);
+            const int gy = min(max(sy0 + r, 0), H - 1), gx = xa + 16 * c;
             uint4 v = make_uint4(0, 0, 0, 0);
             if (gx + 16 <= pitch) v = __ldg(reinterpret_cast<const uint4 *>(img + (long long)gy * pitch + gx));
             *reinterpret_cast<uint4 *>(s_src + r * FS_P + 16 * c) = v;
@@ -417,7 +424,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     }
     for (int i = tid; i < SC_W * SC_H / 16; i += FAST_THREADS) reinterpret_cast<uint4 *>(s_sc)[i] = make_uint4(0, 0, 0, 0);
     s_mask[tid] = 0;
-    if (tid == 0) { s_nout = 0; s_ncorner = 0; }
+    if (tid == 0) s_nout = 0;
     if (tma) kfs_mbar_wait(&s_bar, 0);
     __syncthreads();
 
@@ -436,7 +443,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     const int sy_lo = max(ylo - (ty0 - 1), 0), sy_hi = min(yhi - (ty0 - 1), SC_H - 1);
 #pragma unroll 2
     for (int sy = sy_lo + warp; sy <= sy_hi; sy += FAST_THREADS / 32) {
-        const uint8_t *rowc = s_src + (sy + 3) * FS_P + 4 * lane;
+        const uint8_t *rowc = s_tile + (sy + 3) * FS_P + 4 * lane;
         const uint32_t B = *reinterpret_cast<const uint32_t *>(rowc);
         const uint32_t A = *reinterpret_cast<const uint32_t *>(rowc - 4);
         const uint32_t C = *reinterpret_cast<const uint32_t *>(rowc + 4);
@@ -485,12 +492,20 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     }
     __syncthreads();
 
-    // ---- phase 2: exact score of queued pixels; the corners among them (about half) are appended to a second queue
-    //      (upper half of s_q; warp-aggregated shared atomic: the order inside a tile is free, the lists are re-ordered
-    //      by k_select_sort) so that phase 3 walks corners only.  Tiles with more than half of their pixels queued keep
-    //      the full queue for phase 3.
+    // ---- phase 2: exact score of queued pixels; the corners among them (about half) go to a second queue so that phase 3 walks
+    //      corners only.  Every WARP owns a private segment of that queue (upper half of s_q, CQ_SEG entries per warp: a warp never
+    //      sees more than ceil(nq / 256) * 32 <= CQ_SEG entries when nq <= CQ_MAX) and keeps its fill count in a register: one ballot,
+    //      two POPC and a store per iteration instead of a shared-memory atomic + shuffle round trip (the order inside a tile is
+    //      free, the lists are re-ordered by k_select_sort).  Tiles with more than half of their pixels queued (dense-corner images)
+    //      keep the full queue for phase 3.
     constexpr int CQ_OFF = SC_W * SC_H / 2;
-    const bool compact = nq <= CQ_OFF;
+    constexpr int CQ_SEG = (SC_W * SC_H - CQ_OFF) / (FAST_THREADS / 32) / 32 * 32; // 512 (TH = 62), 256 (TH = 31)
+    constexpr int CQ_MAX = CQ_SEG / 32 * FAST_THREADS;                             // queue lengths the segments can take
+    static_assert(CQ_OFF + (FAST_THREADS / 32) * CQ_SEG <= SC_W * SC_H && CQ_MAX <= CQ_OFF, "per-warp corner segments fit the upper half of the queue");
+    const bool compact = nq <= CQ_MAX;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    uint16_t *s_cq = s_q + CQ_OFF + warp * CQ_SEG;
+    int wc = 0; // corners this warp has queued (warp-uniform)
     for (int e0 = 0; e0 < nq; e0 += FAST_THREADS) {
         const int e = e0 + tid;
         bool corner = false;
@@ -498,7 +513,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
         if (e < nq) {
             pi = s_q[e];
             const int sy = pi >> 7, sx = pi & (SC_W - 1);
-            const uint8_t *c = s_src + (sy + 3) * FS_P + sx;
+            const uint8_t *c = s_tile + (sy + 3) * FS_P + sx;
             const uint32_t cv = kfs_fast_cv(c[0]);
             uint32_t ek[16];
             ek[0] = kfs_fast_e(cv, c[3 * FS_P + 0]);   ek[1] = kfs_fast_e(cv, c[3 * FS_P + 1]);
@@ -515,45 +530,70 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
         }
         if (compact) {
             const uint32_t bc = __ballot_sync(0xffffffffu, corner);
-            if (bc) {
-                int base = 0;
-                if (lane == 0) base = kfs_atoms_add(&s_ncorner, __popc(bc));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (corner) s_q[CQ_OFF + base + __popc(bc & ((1u << lane) - 1u))] = (uint16_t)pi;
-            }
+            if (corner) s_cq[wc + __popc(bc & lt_mask)] = (uint16_t)pi;
+            wc += __popc(bc);
         }
     }
     __syncthreads();
 
-    // ---- phase 3: NMS + border/mask filter -> survivor list in shared memory (aliases the source tile)
+    // ---- phase 3: NMS + border/mask filter.  compact: a warp walks its own corner segment and gathers its survivors in a private
+    //      segment as well (warps 0-3 in the dead lower half of s_q, warps 4-7 in the dead source tile), so the phase needs no
+    //      atomic either; the eight counts meet in s_wsum.  Otherwise: the full queue, block-wide, survivors through a shared counter.
     const uint8_t *mask = L.mask ? L.mask + (long long)f * L.mask_fs : nullptr;
+    auto nms_keep = [&](int pi, uint32_t &packed) -> bool {
+        const int s = s_sc[pi];
+        const int sy = pi >> 7, sx = pi & (SC_W - 1);
+        const int x = ox + sx, y = ty0 - 1 + sy;
+        if (!(s > 0 && sx >= 1 && sx <= FT_W && sy >= 1 && sy <= FT_H &&
+              x >= KFS_BORDER && x < W - KFS_BORDER && y >= KFS_BORDER && y < H - KFS_BORDER)) return false;
+        const uint8_t *p = s_sc + pi;
+        bool keep = s > p[-1] && s > p[1] && s > p[-SC_W - 1] && s > p[-SC_W] && s > p[-SC_W + 1] &&
+                    s > p[SC_W - 1] && s > p[SC_W] && s > p[SC_W + 1];
+        if (keep && mask) keep = __ldg(mask + (long long)y * L.mask_pitch + x) != 0;
+        packed = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+        return keep;
+    };
+    uint32_t *out = g.raw + (long long)f * g.list_fs + L.list_off;
+    if (compact) {
+        static_assert((FAST_THREADS / 64) * CQ_SEG * 4 <= CQ_OFF * 2 && (FAST_THREADS / 64) * CQ_SEG * 4 <= FS_P * FS_H, "survivor segments fit");
+        uint32_t *s_seg = (warp < FAST_THREADS / 64 ? reinterpret_cast<uint32_t *>(s_q) : reinterpret_cast<uint32_t *>(s_src)) + (warp & (FAST_THREADS / 64 - 1)) * CQ_SEG;
+        int wk = 0; // survivors of this warp (warp-uniform)
+        for (int e0 = 0; e0 < wc; e0 += 32) {
+            const int e = e0 + lane;
+            uint32_t packed = 0;
+            const bool keep = e < wc && nms_keep(s_cq[e], packed);
+            const uint32_t bk = __ballot_sync(0xffffffffu, keep);
+            if (keep) s_seg[wk + __popc(bk & lt_mask)] = packed;
+            wk += __popc(bk);
+        }
+        if (lane == 0) s_wsum[warp] = wk;
+        __syncthreads();
+        int before = 0, nout = 0;
+#pragma unroll
+        for (int j = 0; j < FAST_THREADS / 32; j++) {
+            const int t = s_wsum[j];
+            if (j < warp) before += t;
+            nout += t;
+        }
+        if (nout == 0) return;
+        if (tid == 0) s_gbase = atomicAdd(g.raw_count + f * KFS_MAX_LEVELS + l, nout);
+        __syncthreads();
+        const int gbase = s_gbase + before;
+        for (int i = lane; i < wk; i += 32)
+            if (gbase + i < L.list_cap) out[gbase + i] = s_seg[i];
+        return;
+    }
     uint32_t *s_out = reinterpret_cast<uint32_t *>(s_src);
-    const uint16_t *s_list = compact ? s_q + CQ_OFF : s_q;
-    const int nlist = compact ? s_ncorner : nq;
-    for (int e0 = 0; e0 < nlist; e0 += FAST_THREADS) {
+    for (int e0 = 0; e0 < nq; e0 += FAST_THREADS) {
         const int e = e0 + tid;
         uint32_t packed = 0;
-        bool keep = false;
-        if (e < nlist) {
-            const int pi = s_list[e];
-            const int s = s_sc[pi];
-            const int sy = pi >> 7, sx = pi & (SC_W - 1);
-            const int x = ox + sx, y = ty0 - 1 + sy;
-            if (s > 0 && sx >= 4 && sx < 4 + FT_W && sy >= 1 && sy <= FT_H &&
-                x >= KFS_BORDER && x < W - KFS_BORDER && y >= KFS_BORDER && y < H - KFS_BORDER) {
-                const uint8_t *p = s_sc + pi;
-                keep = s > p[-1] && s > p[1] && s > p[-SC_W - 1] && s > p[-SC_W] && s > p[-SC_W + 1] &&
-                       s > p[SC_W - 1] && s > p[SC_W] && s > p[SC_W + 1];
-                if (keep && mask) keep = __ldg(mask + (long long)y * L.mask_pitch + x) != 0;
-                packed = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
-            }
-        }
+        const bool keep = e < nq && nms_keep(s_q[e], packed);
         const uint32_t bk = __ballot_sync(0xffffffffu, keep);
         if (bk) {
             int base = 0;
             if (lane == 0) base = kfs_atoms_add(&s_nout, __popc(bk));
             base = __shfl_sync(0xffffffffu, base, 0);
-            if (keep) s_out[base + __popc(bk & ((1u << lane) - 1u))] = packed;
+            if (keep) s_out[base + __popc(bk & lt_mask)] = packed;
         }
     }
     __syncthreads();
@@ -562,7 +602,6 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     if (tid == 0) s_gbase = atomicAdd(g.raw_count + f * KFS_MAX_LEVELS + l, nout);
     __syncthreads();
     const int gbase = s_gbase;
-    uint32_t *out = g.raw + (long long)f * g.list_fs + L.list_off;
     for (int i = tid; i < nout; i += FAST_THREADS)
         if (gbase + i < L.list_cap) out[gbase + i] = s_out[i];
 }
@@ -1634,8 +1673,12 @@ static cudaError_t kfs_orb_raise_smem_limits(int device)
     if (device >= 0 && device < 64 && done[device]) return cudaSuccess;
     int optin = 0;
     cudaError_t e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+    // the opt-in maximum covers static + dynamic shared memory of a block: what a kernel may ask for dynamically is the rest
+    cudaFuncAttributes fa;
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, k_pyramid);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, k_select_sort);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
     if (e == cudaSuccess && device >= 0 && device < 64) done[device] = true;
     return e;
 }
