@@ -724,11 +724,16 @@ def run_ours(args):
     subs = RP.plan_shard(lo, hi, halo, B, KF_EVERY)
     c_plans = [((N.ReplayFrame * len(sb["frames"]))(*[N.ReplayFrame(*e) for e in sb["plan"]]), len(sb["frames"])) for sb in subs]
 
+    cfg3_stamps = []
+
     def cfg3_run(nsub):
+        del cfg3_stamps[:]
         for j in range(nsub):
             pl, nb_ = c_plans[j]
             rr.submit(pinned[j % nrot].data_ptr(), W, H, pl, nb_)   # frame i of the sequence = frame of the rotating synthetic pool
+            cfg3_stamps.append(time.perf_counter())
         rr.drain()
+        cfg3_stamps.append(time.perf_counter())
     cfg3_run(min(len(c_plans), n_arena + 1))
     barrier()
     t0 = time.perf_counter()
@@ -741,6 +746,10 @@ def run_ours(args):
                         % (args.cfg3_frames, NF, KF_EVERY, world),
             "frames": args.cfg3_frames, "frames_per_s": round(args.cfg3_frames / cfg3_s, 1), "seconds": round(cfg3_s, 4), "scaling": "strong",
             "rank0_shard": [lo, hi, halo], "rank0_submits": len(c_plans), "batch": B,
+            "rank0_submit_ms": {"median": round(float(np.median(np.diff(cfg3_stamps))) * 1e3, 3) if len(cfg3_stamps) > 2 else None,
+                                "max": round(float(np.max(np.diff(cfg3_stamps))) * 1e3, 3) if len(cfg3_stamps) > 2 else None,
+                                "first8": [round(float(x) * 1e3, 2) for x in np.diff(cfg3_stamps)[:8]],
+                                "last4": [round(float(x) * 1e3, 2) for x in np.diff(cfg3_stamps)[-4:]]},
             "api": "kfs_replay_submit/wait, plans from replay.plan_shard (halo keyframe extracted locally and unmatched, last keyframe of a submit parked "
                    "in the device keyframe cache for the next); pinned host frames in, keypoints + descriptors + kNN rows + survivors out; wall clock, max over ranks",
             "data": "frame i of the sequence is frame (i mod %d) of this rank's synthetic pool" % (nrot * B)}

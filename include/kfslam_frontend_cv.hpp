@@ -17,7 +17,7 @@
 #include <opencv2/core.hpp>
 #define KFS_HAVE_OPENCV 1
 #else
-#include "kfslam_cv_mock.hpp"
+#include "kfslam_cv_mock.hpp" // test scaffolding (tests/cpp/, add -I tests/cpp): stand-ins for the OpenCV types when its headers are absent
 #define KFS_HAVE_OPENCV 0
 #endif
 #include "kfslam_frontend.h"

@@ -69,9 +69,15 @@ __device__ __forceinline__ void bf_top2_insert(uint32_t key, uint32_t &b1, uint3
 }
 
 // grid (ceil(max_nq / BF_QTILE), npairs, S).  S > 1 splits the TRAIN rows of every (pair, query tile) over S CTAs so that
-// small batches still fill the 148 SMs and large ones end in many short waves instead of a few long ones; the
-// partial top-2 lists go through `scratch`, and the CTA that arrives last at the tile's counter merges them and
-// writes the cv::DMatch rows (the counter is left at zero for the next launch).
+// small batches still fill the 148 SMs and large ones end in many short waves instead of a few long ones.  The S partial
+// top-2 lists of a tile meet in one of two ways:
+//   CLUSTER  the S CTAs are one thread-block cluster (1, 1, S): every CTA stores its list straight into the shared memory of
+//            the cluster's rank 0 (mapa + st.shared::cluster), one cluster barrier, rank 0 merges and writes the rows — no
+//            global scratch, no fence, no atomic, no read-back (the launch sizes the dynamic shared memory: S x 1 KB)
+//   !CLUSTER the lists go through `scratch`, and the CTA that arrives last at the tile's counter merges them (the counter is
+//            left at zero for the next launch); used when S = 1 and as the fallback when a cluster launch is refused
+extern __shared__ __align__(16) uint2 s_bf_part[]; // CLUSTER, rank 0: [S][BF_QTILE] partial lists
+template <bool CLUSTER>
 __global__ void __launch_bounds__(BF_THREADS, 3)
 k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ scratch, int *__restrict__ counters)
 {
@@ -171,7 +177,26 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
             bf_top2_insert(s_m[(s * BF_QTILE + tid) * 2 + 1], m1, m2);
         }
     }
-    if (S > 1) {
+    if (CLUSTER) {
+        // blockIdx.z is the rank inside the (1, 1, S) cluster.  Rank 0's s_bf_part is written by nobody but this exchange, so the
+        // faster CTAs do not wait for it to finish its own rows; the barrier (release / acquire) publishes the remote stores.
+        if (tid < BF_QTILE) {
+            const uint32_t mine = (uint32_t)__cvta_generic_to_shared(&s_bf_part[split * BF_QTILE + tid]);
+            uint32_t dst;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(dst) : "r"(mine), "r"(0));
+            asm volatile("st.shared::cluster.v2.u32 [%0], {%1, %2};" ::"r"(dst), "r"(m1), "r"(m2) : "memory");
+        }
+        asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (split != 0) return;
+        if (tid < BF_QTILE) {
+            m1 = m2 = BF_INF;
+            for (int s = 0; s < S; s++) {
+                const uint2 v = s_bf_part[s * BF_QTILE + tid];
+                bf_top2_insert(v.x, m1, m2);
+                bf_top2_insert(v.y, m1, m2);
+            }
+        }
+    } else if (S > 1) {
         const int tile = blockIdx.y * gridDim.x + blockIdx.x;
         uint2 *part = scratch + (size_t)tile * S * BF_QTILE;
         if (tid < BF_QTILE) __stcg(part + split * BF_QTILE + tid, make_uint2(m1, m2));
@@ -273,6 +298,9 @@ struct kfs_bf {
     int *d_counters = nullptr;    // [tiles] arrival counters (zero between launches)
     size_t scratch_tiles = 0, scratch_elems = 0;
     int force_split = 0;          // KFS_BF_SPLIT (tests / experiments): 0 = automatic
+    int cluster = 1;              // KFS_BF_CLUSTER: 0 (or a refused cluster launch) = splits merge through global scratch, 1 = clusters for
+                                  // single-wave launches, 2 = clusters for every split launch
+    int cluster_max = 8;          // largest cluster the device schedules for this kernel (16 once the non-portable size is allowed)
     const kfs_orb *attached = nullptr; // kfs_bf_attach_orb: host rows this extractor just delivered are matched on the device
     int aliased = 0;              // descriptor matrices of the last host-buffer call that were found on the device
 };
@@ -325,8 +353,26 @@ static kfs_status bf_launch_kernel(kfs_bf *b, const BfPairDev *d_table, int npai
     const int S = bf_choose_split(b, qtiles * npairs, max_nt);
     kfs_status s = bf_reserve_split(b, (size_t)qtiles * npairs, S);
     if (s) return s;
-    k_hamming_knn2<<<dim3(qtiles, npairs, S), BF_THREADS, 0, st>>>(d_table, k, b->d_scratch, b->d_counters);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = cudaErrorUnknown;
+    // a cluster's CTAs are scheduled together on one GPC: right for a launch that is a single wave (one pair, 2000 x 2000: 16 tiles x
+    // 16 splits = 256 CTAs, 21.6 instead of 22.5 us), wrong for one that runs in several waves (config 4's one frame, 10 pairs x 16 tiles x
+    // 4 splits = 640 CTAs: 81 instead of 73 us measured with clusters)
+    const bool one_wave = (long long)qtiles * npairs * S <= 3LL * (b->sm_count > 0 ? b->sm_count : 148);
+    if (S > 1 && b->cluster && S <= b->cluster_max && (one_wave || b->cluster == 2)) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(qtiles, npairs, S); cfg.blockDim = dim3(BF_THREADS); cfg.stream = st;
+        cfg.dynamicSmemBytes = (size_t)S * BF_QTILE * sizeof(uint2);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = (unsigned)S;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        e = cudaLaunchKernelEx(&cfg, k_hamming_knn2<true>, d_table, k, b->d_scratch, b->d_counters);
+        if (e != cudaSuccess) { cudaGetLastError(); b->cluster = 0; } // refused (size / co-scheduling): global merge from now on
+    }
+    if (e != cudaSuccess) {
+        k_hamming_knn2<false><<<dim3(qtiles, npairs, S), BF_THREADS, 0, st>>>(d_table, k, b->d_scratch, b->d_counters);
+        e = cudaGetLastError();
+    }
     if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_hamming_knn2 launch: %s", cudaGetErrorString(e));
     b->launches++;
     return KFS_OK;
@@ -432,6 +478,15 @@ kfs_status kfs_bf_create(int norm_type, int cross_check, int device, kfs_bf **ou
     if (e != cudaSuccess) { delete b; KFS_FAIL(KFS_ERR_CUDA, "kfs_bf_create on device %d: %s", device, cudaGetErrorString(e)); }
     cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
     if (const char *fs = getenv("KFS_BF_SPLIT")) b->force_split = atoi(fs);
+    if (const char *fc = getenv("KFS_BF_CLUSTER")) b->cluster = atoi(fc); // 0 never, 1 single-wave launches (default), 2 every split launch
+    if (b->cluster) {
+        // static 32 KB + up to 16 KB of partial lists: above the 48 KB default, and 16 CTAs per cluster is a non-portable size
+        const cudaError_t e1 = cudaFuncSetAttribute(k_hamming_knn2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BF_MAX_SPLIT * BF_QTILE * (int)sizeof(uint2));
+        const cudaError_t e2 = cudaFuncSetAttribute(k_hamming_knn2<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e1 != cudaSuccess) { b->cluster = 0; cudaGetLastError(); }
+        b->cluster_max = e2 == cudaSuccess ? BF_MAX_SPLIT : 8;
+        if (e2 != cudaSuccess) cudaGetLastError();
+    }
     b->stream = b->own_stream;
     *out = b;
     return KFS_OK;

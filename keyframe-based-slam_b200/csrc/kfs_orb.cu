@@ -250,6 +250,33 @@ __device__ __forceinline__ void kfs_mbar_wait(uint64_t *bar, uint32_t phase)
 // against 57.7 us without PDL and 54.5 us with the implicit trigger at grid completion).
 __device__ __forceinline__ void kfs_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// Shared-memory accesses through a 32-bit shared address + immediate offset: the address arithmetic of the hot loops stays one
+// register (a generic pointer into a __shared__ array makes the compiler rebuild the window base inside the loop).  volatile keeps
+// the accesses on their side of the barriers; ptxas still schedules them freely in between.
+template <int OFF> __device__ __forceinline__ uint32_t kfs_lds_u8(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1+%2];" : "=r"(v) : "r"(a), "n"(OFF));
+    return v;
+}
+__device__ __forceinline__ uint32_t kfs_lds_u16(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void kfs_sts_u8(uint32_t a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void kfs_sts_u16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void kfs_sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+// the empty asm makes the address an opaque register value: the compiler keeps it instead of rebuilding the shared-window base
+// (S2R SR_CgaCtaId + LEA) next to every use
+__device__ __forceinline__ uint32_t kfs_smem_u32(const void *p)
+{
+    uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+    asm volatile("" : "+r"(a));
+    return a;
+}
+
 __device__ __forceinline__ int kfs_atoms_add(int *p, int v)
 {
     int r;
@@ -457,7 +484,7 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
         const uint32_t mo = kfs_fast_quick2m(__byte_perm(B, 0, 0x4341), __byte_perm(U, 0, 0x4341), __byte_perm(D, 0, 0x4341),
                                              __byte_perm(Rw, 0, 0x4341), __byte_perm(Lw, 0, 0x4341), thr, vmo);
         const uint32_t b0 = __ballot_sync(0xffffffffu, me & 0x00008000u), b1 = __ballot_sync(0xffffffffu, mo & 0x00008000u);
-        const uint32_t b2 = __ballot_sync(0xffffffffu, me & 0x80000000u), b3 = __ballot_sync(0xffffffffu, mo & 0x80000000u);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, (int)me < 0), b3 = __ballot_sync(0xffffffffu, (int)mo < 0);
         if (lane == 0) *reinterpret_cast<uint4 *>(s_mask + 4 * sy) = make_uint4(b0, b1, b2, b3);
     }
     __syncthreads();
@@ -505,32 +532,33 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     const bool compact = nq <= CQ_MAX;
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint16_t *s_cq = s_q + CQ_OFF + warp * CQ_SEG;
+    const uint32_t a_q = kfs_smem_u32(s_q), a_sc = kfs_smem_u32(s_sc), a_cq = kfs_smem_u32(s_cq);
+    const uint32_t a_ctr = kfs_smem_u32(s_tile) + 3 * FS_P; // centre of score pixel (sx, sy) = a_ctr + sy * FS_P + sx
     int wc = 0; // corners this warp has queued (warp-uniform)
-    for (int e0 = 0; e0 < nq; e0 += FAST_THREADS) {
-        const int e = e0 + tid;
+    for (int e0 = warp * 32; e0 < nq; e0 += FAST_THREADS) { // warp-uniform bounds: the ballot below sees whole warps
+        const int e = e0 + lane;
         bool corner = false;
-        int pi = 0;
+        uint32_t pi = 0;
         if (e < nq) {
-            pi = s_q[e];
-            const int sy = pi >> 7, sx = pi & (SC_W - 1);
-            const uint8_t *c = s_tile + (sy + 3) * FS_P + sx;
-            const uint32_t cv = kfs_fast_cv(c[0]);
+            pi = kfs_lds_u16(a_q + 2 * e);
+            const uint32_t c = a_ctr + pi + (pi >> 7) * (FS_P - SC_W);
+            const uint32_t cv = kfs_fast_cv((int)kfs_lds_u8<0>(c));
             uint32_t ek[16];
-            ek[0] = kfs_fast_e(cv, c[3 * FS_P + 0]);   ek[1] = kfs_fast_e(cv, c[3 * FS_P + 1]);
-            ek[2] = kfs_fast_e(cv, c[2 * FS_P + 2]);   ek[3] = kfs_fast_e(cv, c[1 * FS_P + 3]);
-            ek[4] = kfs_fast_e(cv, c[3]);              ek[5] = kfs_fast_e(cv, c[-1 * FS_P + 3]);
-            ek[6] = kfs_fast_e(cv, c[-2 * FS_P + 2]);  ek[7] = kfs_fast_e(cv, c[-3 * FS_P + 1]);
-            ek[8] = kfs_fast_e(cv, c[-3 * FS_P + 0]);  ek[9] = kfs_fast_e(cv, c[-3 * FS_P - 1]);
-            ek[10] = kfs_fast_e(cv, c[-2 * FS_P - 2]); ek[11] = kfs_fast_e(cv, c[-1 * FS_P - 3]);
-            ek[12] = kfs_fast_e(cv, c[-3]);            ek[13] = kfs_fast_e(cv, c[1 * FS_P - 3]);
-            ek[14] = kfs_fast_e(cv, c[2 * FS_P - 2]);  ek[15] = kfs_fast_e(cv, c[3 * FS_P - 1]);
+            ek[0] = kfs_fast_e(cv, kfs_lds_u8<3 * FS_P + 0>(c));   ek[1] = kfs_fast_e(cv, kfs_lds_u8<3 * FS_P + 1>(c));
+            ek[2] = kfs_fast_e(cv, kfs_lds_u8<2 * FS_P + 2>(c));   ek[3] = kfs_fast_e(cv, kfs_lds_u8<1 * FS_P + 3>(c));
+            ek[4] = kfs_fast_e(cv, kfs_lds_u8<3>(c));              ek[5] = kfs_fast_e(cv, kfs_lds_u8<-1 * FS_P + 3>(c));
+            ek[6] = kfs_fast_e(cv, kfs_lds_u8<-2 * FS_P + 2>(c));  ek[7] = kfs_fast_e(cv, kfs_lds_u8<-3 * FS_P + 1>(c));
+            ek[8] = kfs_fast_e(cv, kfs_lds_u8<-3 * FS_P + 0>(c));  ek[9] = kfs_fast_e(cv, kfs_lds_u8<-3 * FS_P - 1>(c));
+            ek[10] = kfs_fast_e(cv, kfs_lds_u8<-2 * FS_P - 2>(c)); ek[11] = kfs_fast_e(cv, kfs_lds_u8<-1 * FS_P - 3>(c));
+            ek[12] = kfs_fast_e(cv, kfs_lds_u8<-3>(c));            ek[13] = kfs_fast_e(cv, kfs_lds_u8<1 * FS_P - 3>(c));
+            ek[14] = kfs_fast_e(cv, kfs_lds_u8<2 * FS_P - 2>(c));  ek[15] = kfs_fast_e(cv, kfs_lds_u8<3 * FS_P - 1>(c));
             const int m = kfs_fast9_m(ek);
             corner = m > thr;
-            if (corner) s_sc[pi] = (uint8_t)(m - 1);
+            if (corner) kfs_sts_u8(a_sc + pi, (uint32_t)(m - 1));
         }
         if (compact) {
             const uint32_t bc = __ballot_sync(0xffffffffu, corner);
-            if (corner) s_cq[wc + __popc(bc & lt_mask)] = (uint16_t)pi;
+            if (corner) kfs_sts_u16(a_cq + 2 * (wc + __popc(bc & lt_mask)), pi);
             wc += __popc(bc);
         }
     }
@@ -540,17 +568,24 @@ k_fast(const __grid_constant__ OrbDev g, const uint32_t *__restrict__ tile_tab, 
     //      segment as well (warps 0-3 in the dead lower half of s_q, warps 4-7 in the dead source tile), so the phase needs no
     //      atomic either; the eight counts meet in s_wsum.  Otherwise: the full queue, block-wide, survivors through a shared counter.
     const uint8_t *mask = L.mask ? L.mask + (long long)f * L.mask_fs : nullptr;
-    auto nms_keep = [&](int pi, uint32_t &packed) -> bool {
-        const int s = s_sc[pi];
+    // keepable score coordinates: owned (1 <= sx <= FT_W, 1 <= sy <= FT_H) and inside the border ([31, W-31) x [31, H-31)), folded
+    // into one unsigned range test per axis; the 8 neighbours are then read back to back and reduced with three max3 + one max
+    const int nx_lo = max(1, KFS_BORDER - ox), nx_n = min(FT_W, W - KFS_BORDER - 1 - ox) - nx_lo;
+    const int ny_lo = max(1, KFS_BORDER - (ty0 - 1)), ny_n = min(FT_H, H - KFS_BORDER - 1 - (ty0 - 1)) - ny_lo;
+    const uint32_t a_nms = kfs_smem_u32(s_sc);
+    auto nms_keep = [&](uint32_t pi, uint32_t &packed) -> bool {
         const int sy = pi >> 7, sx = pi & (SC_W - 1);
         const int x = ox + sx, y = ty0 - 1 + sy;
-        if (!(s > 0 && sx >= 1 && sx <= FT_W && sy >= 1 && sy <= FT_H &&
-              x >= KFS_BORDER && x < W - KFS_BORDER && y >= KFS_BORDER && y < H - KFS_BORDER)) return false;
-        const uint8_t *p = s_sc + pi;
-        bool keep = s > p[-1] && s > p[1] && s > p[-SC_W - 1] && s > p[-SC_W] && s > p[-SC_W + 1] &&
-                    s > p[SC_W - 1] && s > p[SC_W] && s > p[SC_W + 1];
+        packed = 0;
+        if (!((uint32_t)(sx - nx_lo) <= (uint32_t)nx_n && (uint32_t)(sy - ny_lo) <= (uint32_t)ny_n && (nx_n | ny_n) >= 0)) return false;
+        const uint32_t p = a_nms + pi; // 1 <= sx <= FT_W, 1 <= sy <= FT_H: all eight neighbours are inside the score tile
+        const uint32_t s = kfs_lds_u8<0>(p);
+        const uint32_t n0 = kfs_lds_u8<-1>(p), n1 = kfs_lds_u8<1>(p), n2 = kfs_lds_u8<-SC_W - 1>(p), n3 = kfs_lds_u8<-SC_W>(p);
+        const uint32_t n4 = kfs_lds_u8<-SC_W + 1>(p), n5 = kfs_lds_u8<SC_W - 1>(p), n6 = kfs_lds_u8<SC_W>(p), n7 = kfs_lds_u8<SC_W + 1>(p);
+        const uint32_t nmax = max(__vimax3_u32(n0, n1, n2), __vimax3_u32(n3, n4, __vimax3_u32(n5, n6, n7)));
+        bool keep = s > nmax; // implies s > 0
         if (keep && mask) keep = __ldg(mask + (long long)y * L.mask_pitch + x) != 0;
-        packed = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+        packed = (s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
         return keep;
     };
     uint32_t *out = g.raw + (long long)f * g.list_fs + L.list_off;
@@ -1318,6 +1353,180 @@ k_describe(const __grid_constant__ OrbDev g, int kpw)
     asm volatile("cp.async.wait_group 0;\n" ::: "memory"); // nothing may still be landing in shared memory at exit
 }
 
+// ------------------------------------------------------------------------------------------------------
+// k_describe2: the same arithmetic in TWO PASSES per warp, no block-level barrier.
+//   pass A  the warp's kpw keypoints one after the other: IC moments from the un-blurred window (double-buffered cp.async); the
+//           sums of keypoint i stay in lane i
+//   between lanes 0 .. kpw-1 run fastAtan2 and the fp64 sincos of THEIR keypoint side by side (one latency for kpw keypoints, where
+//           k_describe pays one per keypoint and parks both warps of the CTA at two barriers around it) and write the cv::KeyPoint
+//   pass B  rotated BRIEF of the kpw keypoints from the blurred windows (double-buffered as well; the first two fly during the end of
+//           pass A), cos / sin / centre broadcast from lane i
+// Slots: warp w of CTA b owns slots (b * DK + w) * kpw .. + kpw - 1, so a warp walks neighbouring keypoints of the (level, y, x) order.
+__global__ void __launch_bounds__(32 * DK)
+k_describe2(const __grid_constant__ OrbDev g, int kpw)
+{
+    __shared__ __align__(16) uint8_t s_ic[DK][2][IC_BYTES];
+    __shared__ __align__(16) uint8_t s_wb[DK][2][WB_BYTES];
+    kfs_pdl_wait();
+    const int f = blockIdx.y + g.frame0, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int cnt = 0;
+    if (lane < g.nlevels) cnt = min(g.kept_count[f * KFS_MAX_LEVELS + lane], g.lv[lane].list_cap);
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < KFS_MAX_LEVELS; d <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += v;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, KFS_MAX_LEVELS - 1);
+    if (blockIdx.x == 0 && threadIdx.x == 0) g.n_out[f] = total;
+    const int nvalid = min(total, g.cap_out);
+    const int slot0 = (blockIdx.x * DK + warp) * kpw; // this warp's first slot
+    if (slot0 >= nvalid) return;                      // warp-uniform; no block-level barrier below
+    const int nk = min(kpw, nvalid - slot0);          // keypoints of this warp (>= 1)
+    const int q = lane & 3, rq = lane >> 2;
+
+    // lane i < nk: its keypoint's level, list entry
+    int level_l = 0;
+    uint32_t xy_l = 0xffffffffu;
+    float resp_l = 0.f;
+    {
+        const int slot = slot0 + lane;
+        int lv = 0, excl = 0;
+        for (int l = 0; l < g.nlevels; l++) {
+            const int v = __shfl_sync(0xffffffffu, incl, l);
+            if (v <= slot) { lv = l + 1; excl = v; }
+        }
+        if (lane < nk) {
+            level_l = lv;
+            const long long li = (long long)f * g.list_fs + g.lv[lv].list_off + (slot - excl);
+            xy_l = g.kept_xy[li];
+            resp_l = g.kept_resp[li];
+        }
+    }
+    // job s of the warp: s < nk -> un-blurred window of keypoint s, else blurred window of keypoint s - nk; one commit group per job
+    auto issue = [&](int s) {
+        if (s < 2 * nk) {
+            const int i = s < nk ? s : s - nk;
+            const uint32_t xy = __shfl_sync(0xffffffffu, xy_l, i);
+            const int level = __shfl_sync(0xffffffffu, level_l, i);
+            const LevelDev &L = g.lv[level];
+            const int x = xy & 0xfff, y = (xy >> 12) & 0xfff;
+            if (s < nk) {
+                uint8_t *ic = s_ic[warp][i & 1];
+                const int ax = (x - 15) & ~15;
+                const bool in_i = ax + 16 * q + 16 <= L.pitch;
+                const uint8_t *srci = L.img + (long long)f * L.img_fs + (long long)(y - 15 + rq) * L.pitch + ax + (in_i ? 16 * q : 0);
+                if (q < 3) {
+#pragma unroll
+                    for (int r = 0; r < 4; r++)
+                        if (rq + 8 * r < 31) kfs_cp_async16_zfill(ic + (rq + 8 * r) * 48 + 16 * q, srci + (long long)(8 * r) * L.pitch, in_i);
+                }
+            } else {
+                uint8_t *wb = s_wb[warp][i & 1];
+                const int axb = (x - 18) & ~15;
+                const bool in_b = axb + 16 * q + 16 <= L.pitch_blur;
+                const uint8_t *srb = L.blur + (long long)f * L.img_fs_blur + (long long)(y - 18 + rq) * L.pitch_blur + axb + (in_b ? 16 * q : 0);
+#pragma unroll
+                for (int r = 0; r < 5; r++)
+                    if (rq + 8 * r < 37) kfs_cp_async16_zfill(wb + (rq + 8 * r) * BW_P + 16 * q, srb + (long long)(8 * r) * L.pitch_blur, in_b);
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    issue(0);
+    issue(1);
+
+    // ---- pass A: IC moments (a1.7), 2 x 4 IDP.4A per 16-byte chunk against the (shift, |v|, word) weight table
+    int m10_l = 0, m01_l = 0;
+#pragma unroll 1
+    for (int i = 0; i < nk; i++) {
+        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        __syncwarp();
+        const int x = __shfl_sync(0xffffffffu, xy_l, i) & 0xfff;
+        const uint8_t *ic = s_ic[warp][i & 1];
+        const int shi = (x - 15) & 15;
+        int m10 = 0, m01 = 0;
+        const int qc = min(q, 2);
+#pragma unroll
+        for (int r4 = 0; r4 < 4; r4++) {
+            const int r = rq + 8 * r4, v = r - 15, a = min(v < 0 ? -v : v, 15);
+            uint4 px = make_uint4(0, 0, 0, 0);
+            if (q < 3 && r < 31) px = *reinterpret_cast<const uint4 *>(ic + r * 48 + 16 * q);
+            const int ti = (shi * 16 + a) * 12 + 4 * qc;
+            const uint4 tu = __ldg(reinterpret_cast<const uint4 *>(d_ictab.wu + ti));
+            const uint4 t1 = __ldg(reinterpret_cast<const uint4 *>(d_ictab.w1 + ti));
+            m10 = kfs_dp4a_us(px.x, tu.x, m10); m10 = kfs_dp4a_us(px.y, tu.y, m10);
+            m10 = kfs_dp4a_us(px.z, tu.z, m10); m10 = kfs_dp4a_us(px.w, tu.w, m10);
+            int rs = kfs_dp4a_us(px.x, t1.x, 0); rs = kfs_dp4a_us(px.y, t1.y, rs);
+            rs = kfs_dp4a_us(px.z, t1.z, rs); rs = kfs_dp4a_us(px.w, t1.w, rs);
+            m01 += v * rs; // lanes with q == 3 or row > 30 hold zero pixels
+        }
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        m01 = __reduce_add_sync(0xffffffffu, m01);
+        if (lane == i) { m10_l = m10; m01_l = m01; }
+        __syncwarp();      // every lane has read this buffer before job i + 2 lands in it
+        issue(i + 2);
+    }
+
+    // ---- between the passes: lane i owns keypoint i
+    float cs_l = 1.f, sn_l = 0.f;
+    if (lane < nk) {
+        const float angle = kfs_fast_atan2((float)m01_l, (float)m10_l);
+        const float rad = kfs_mul(angle, (float)(3.1415926535897932384626433832795 / 180.f));
+        double sn, cs;
+        sincos((double)rad, &sn, &cs);
+        cs_l = (float)cs; sn_l = (float)sn;
+        const float sc = g.lv[level_l].scale;
+        const int x = xy_l & 0xfff, y = (xy_l >> 12) & 0xfff;
+        kfs_keypoint kp;
+        kp.x = kfs_mul((float)x, sc);
+        kp.y = kfs_mul((float)y, sc);
+        kp.size = kfs_mul(31.f, sc);
+        kp.angle = angle;
+        kp.response = resp_l;
+        kp.octave = level_l;
+        kp.class_id = -1;
+        g.kp[(long long)f * g.cap_out + slot0 + lane] = kp;
+    }
+    __syncwarp();
+
+    // ---- pass B: rotated BRIEF (a1.10).  This lane's 8 sample pairs (pair 32h + lane) serve all nk keypoints.
+    float4 pat[8];
+#pragma unroll
+    for (int h = 0; h < 8; h++) pat[h] = __ldg(reinterpret_cast<const float4 *>(d_patf) + 32 * h + lane);
+#pragma unroll 1
+    for (int i = 0; i < nk; i++) {
+        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        __syncwarp();
+        const int x = __shfl_sync(0xffffffffu, xy_l, i) & 0xfff;
+        const float2 ab = make_float2(__shfl_sync(0xffffffffu, cs_l, i), __shfl_sync(0xffffffffu, sn_l, i));
+        const uint8_t *wb = s_wb[warp][i & 1];
+        // see k_describe: the magic-add constants carry the window origin and the shared-memory address of wb
+        const int shb = (x - 18) & 15;
+        const int cx = 18 + shb + (int)__cvta_generic_to_shared(wb);
+        const float mx = 12582912.f + (float)(cx & ~1), my = 12582912.f + 18.f;
+        const uint32_t kfold = 0x4B400000u * 65u - (uint32_t)(cx & 1);
+        uint32_t word = 0;
+#pragma unroll
+        for (int h = 0; h < 8; h++) {
+            const float4 pt = pat[h];
+            const uint32_t bx0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.x, ab.x), __fmul_rn(pt.y, ab.y)), mx));
+            const uint32_t by0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.x, ab.y), __fmul_rn(pt.y, ab.x)), my));
+            const uint32_t bx1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.z, ab.x), __fmul_rn(pt.w, ab.y)), mx));
+            const uint32_t by1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.z, ab.y), __fmul_rn(pt.w, ab.x)), my));
+            uint32_t v0, v1;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v0) : "r"(by0 * 64u + bx0 - kfold));
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v1) : "r"(by1 * 64u + bx1 - kfold));
+            const uint32_t b = __ballot_sync(0xffffffffu, v0 < v1);
+            if (lane == h) word = b;
+        }
+        if (lane < 8) reinterpret_cast<uint32_t *>(g.desc + ((long long)f * g.cap_out + slot0 + i) * 32)[lane] = word;
+        __syncwarp();      // (the ballots already ordered every read of this buffer before the next job lands in it)
+        issue(nk + i + 2);
+    }
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory"); // nothing may still be landing in shared memory at exit
+}
+
 // ======================================================================================================
 // host side
 // ======================================================================================================
@@ -1386,6 +1595,7 @@ struct kfs_orb {
     std::vector<uint32_t> h_xtab[KFS_MAX_LEVELS], h_ytab[KFS_MAX_LEVELS];
     bool pyr_fused = false;
     bool use_pdl = !(getenv("KFS_ORB_PDL") && atoi(getenv("KFS_ORB_PDL")) == 0);
+    bool describe2 = !(getenv("KFS_ORB_DESCRIBE2") && atoi(getenv("KFS_ORB_DESCRIBE2")) == 0); // two-pass k_describe2 (0: k_describe)
     int pyr_mode = 1;               // KFS_ORB_FUSED_PYRAMID: 0 = never, 1 = calls of at most PYR_FUSED_MAX_FRAMES frames, 2 = always
     PyrDev pyr_dev;
     short *d_rects = nullptr;
@@ -1941,7 +2151,8 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
     }
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
     const int kpw = std::max(1, std::min(KPW, nb));
-    kfs_launch_pdl(pdl, k_describe, dim3(kfs_div_up(g.cap_out, DK * kpw), nb), dim3(32 * DK), 0, st, g, kpw);
+    if (o->describe2) kfs_launch_pdl(pdl, k_describe2, dim3(kfs_div_up(g.cap_out, DK * kpw), nb), dim3(32 * DK), 0, st, g, kpw);
+    else kfs_launch_pdl(pdl, k_describe, dim3(kfs_div_up(g.cap_out, DK * kpw), nb), dim3(32 * DK), 0, st, g, kpw);
     KFS_LAUNCH_CHECK(o);
     if (kfs_stage_mark(o, KFS_STAGE_COUNT)) return KFS_ERR_CUDA;
     o->last_batch = f0 + nb;

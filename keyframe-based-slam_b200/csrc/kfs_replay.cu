@@ -27,8 +27,9 @@ struct ReplaySlot {
     kfs_dmatch *d_knn = nullptr, *d_good = nullptr;
     int *d_small = nullptr;   // [2][max_batch]: n_good | n_query
     int *h_small = nullptr;   // pinned mirror
-    BfPairDev *d_table = nullptr, *h_table = nullptr; // device / pinned
-    std::vector<BfPairDev> last_table;
+    BfPairDev *d_table = nullptr;     // device: built by k_replay_table
+    std::vector<int> last_plan;       // plan keyframes (+ capacity) d_table was built from
+    const uint8_t *last_desc = nullptr;
     std::vector<uint8_t> skip;  // per frame: keypoints / descriptors not wanted on the host
     int rows = 0;               // kNN / survivor rows per frame the eager copies carried
 };
@@ -47,6 +48,35 @@ struct kfs_replay {
     int seq = 0;
     int launches = 0;
 };
+
+// The pair table of a submit, built ON the device from the plan.  The plan travels as kernel arguments (RP_PLAN_CHUNK frames per
+// launch), never as a host-to-device copy: a small cudaMemcpyAsync on the compute stream is ordered behind this batch's kernels and
+// sits in the copy engine's queue in front of the NEXT batch's frame upload, which then cannot overlap those kernels (cfg3: 3.1 ms per
+// submit instead of 2.2).  query = keyframe descriptors (same batch or cache slot), train = the frame's own (VisualOdometry.cpp:39).
+constexpr int RP_PLAN_CHUNK = 512;
+struct RpPlanArg { int keyframe[RP_PLAN_CHUNK]; };
+__global__ void k_replay_table(const __grid_constant__ RpPlanArg plan, int i0, int n, BfPairDev *__restrict__ table, const uint8_t *d_desc,
+                               const int *d_cnt, int cap, const uint8_t *d_kf_desc, const int *d_kf_count, kfs_dmatch *d_knn)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int i = i0 + j, k = plan.keyframe[j];
+    BfPairDev P;
+    P.train = d_desc + (size_t)i * cap * 32; P.nt = cap; P.d_nt = d_cnt + i;
+    P.out = d_knn + (size_t)i * cap * 2; P.counts = nullptr;
+    if (k == KFS_REPLAY_NO_MATCH) { P.query = d_desc; P.nq = 0; P.d_nq = nullptr; P.nt = 0; }
+    else if (k >= 0) { P.query = d_desc + (size_t)k * cap * 32; P.nq = cap; P.d_nq = d_cnt + k; }
+    else { const int sl = -(k + 1); P.query = d_kf_desc + (size_t)sl * cap * 32; P.nq = cap; P.d_nq = d_kf_count + sl; }
+    table[i] = P;
+}
+
+// A frame that becomes a keyframe for later submits: its descriptors and count into a cache slot (a kernel for the same reason: a
+// device-to-device cudaMemcpyAsync may be served by a copy engine and queue in front of an upload or a download)
+__global__ void k_replay_store(const uint4 *__restrict__ src, const int *__restrict__ src_cnt, uint4 *__restrict__ dst, int *__restrict__ dst_cnt, int n16)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += gridDim.x * blockDim.x) dst[i] = src[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) *dst_cnt = *src_cnt;
+}
 
 __global__ void k_replay_nquery(const BfPairDev *__restrict__ pairs, int npairs, int *__restrict__ n_query)
 {
@@ -118,7 +148,6 @@ void kfs_replay_destroy(kfs_replay *r)
         if (S.d_small) cudaFree(S.d_small);
         if (S.h_small) cudaFreeHost(S.h_small);
         if (S.d_table) cudaFree(S.d_table);
-        if (S.h_table) cudaFreeHost(S.h_table);
         if (r->orb[b]) kfs_orb_destroy(r->orb[b]);
     }
     if (r->bf) kfs_bf_destroy(r->bf);
@@ -171,7 +200,6 @@ kfs_status kfs_replay_create(const kfs_replay_params *params, int device, kfs_re
         RP_TRY(cudaMalloc((void **)&S.d_small, 2 * mb * sizeof(int)));
         RP_TRY(cudaMallocHost((void **)&S.h_small, 2 * mb * sizeof(int)));
         RP_TRY(cudaMalloc((void **)&S.d_table, mb * sizeof(BfPairDev)));
-        RP_TRY(cudaMallocHost((void **)&S.h_table, mb * sizeof(BfPairDev)));
     }
     RP_TRY(cudaMalloc((void **)&r->d_kf_desc, (size_t)params->keyframe_slots * cap * 32));
     RP_TRY(cudaMalloc((void **)&r->d_kf_count, (size_t)params->keyframe_slots * sizeof(int)));
@@ -228,21 +256,25 @@ kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_r
     kfs_orb_internal_streams(o, nullptr, &s_out);
     const bool want_knn = io->knn != nullptr || io->good != nullptr;
     if (want_knn) {
-        // 2. pair table: query = keyframe descriptors (same batch or cache), train = the frame's own
-        for (int i = 0; i < batch; i++) {
-            BfPairDev P;
-            const int k = plan[i].keyframe;
-            P.train = d_desc + (size_t)i * cap * 32; P.nt = cap; P.d_nt = d_cnt + i;
-            P.out = S.d_knn + (size_t)i * cap * 2; P.counts = nullptr;
-            if (k == KFS_REPLAY_NO_MATCH) { P.query = d_desc; P.nq = 0; P.d_nq = nullptr; P.nt = 0; }
-            else if (k >= 0) { P.query = d_desc + (size_t)k * cap * 32; P.nq = cap; P.d_nq = d_cnt + k; }
-            else { const int sl = -(k + 1); P.query = r->d_kf_desc + (size_t)sl * cap * 32; P.nq = cap; P.d_nq = r->d_kf_count + sl; }
-            S.h_table[i] = P;
-        }
-        const bool same = (int)S.last_table.size() == batch && memcmp(S.last_table.data(), S.h_table, sizeof(BfPairDev) * (size_t)batch) == 0;
+        // 2. pair table: query = keyframe descriptors (same batch or cache), train = the frame's own; rebuilt (by a kernel, from
+        //    the plan in its arguments) only when the plan or the arena's buffers changed
+        std::vector<int> &key = S.last_plan;
+        bool same = (int)key.size() == batch + 1 && key[(size_t)batch] == cap && S.last_desc == d_desc;
+        for (int i = 0; same && i < batch; i++) same = key[(size_t)i] == plan[i].keyframe;
         if (!same) {
-            KFS_CUDA_TRY(cudaMemcpyAsync(S.d_table, S.h_table, sizeof(BfPairDev) * (size_t)batch, cudaMemcpyHostToDevice, r->compute));
-            S.last_table.assign(S.h_table, S.h_table + batch);
+            for (int i0 = 0; i0 < batch; i0 += RP_PLAN_CHUNK) {
+                RpPlanArg pa;
+                const int n = batch - i0 < RP_PLAN_CHUNK ? batch - i0 : RP_PLAN_CHUNK;
+                for (int j = 0; j < n; j++) pa.keyframe[j] = plan[i0 + j].keyframe;
+                for (int j = n; j < RP_PLAN_CHUNK; j++) pa.keyframe[j] = KFS_REPLAY_NO_MATCH;
+                k_replay_table<<<kfs_div_up(n, 128), 128, 0, r->compute>>>(pa, i0, n, S.d_table, d_desc, d_cnt, cap, r->d_kf_desc, r->d_kf_count, S.d_knn);
+                if (cudaGetLastError() != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_replay_table launch failed");
+                r->launches++;
+            }
+            key.resize((size_t)batch + 1);
+            for (int i = 0; i < batch; i++) key[(size_t)i] = plan[i].keyframe;
+            key[(size_t)batch] = cap;
+            S.last_desc = d_desc;
         }
         // 3. matching (+ ratio test) on the device-resident descriptors
         s = kfs_bf_launch_table(r->bf, S.d_table, batch, cap, 2, r->compute);
@@ -265,8 +297,10 @@ kfs_status kfs_replay_submit(kfs_replay *r, const kfs_replay_io *io, const kfs_r
     for (int i = 0; i < batch; i++) {
         const int sl = plan[i].store_slot;
         if (sl < 0) continue;
-        KFS_CUDA_TRY(cudaMemcpyAsync(r->d_kf_desc + (size_t)sl * cap * 32, d_desc + (size_t)i * cap * 32, (size_t)cap * 32, cudaMemcpyDeviceToDevice, r->compute));
-        KFS_CUDA_TRY(cudaMemcpyAsync(r->d_kf_count + sl, d_cnt + i, sizeof(int), cudaMemcpyDeviceToDevice, r->compute));
+        k_replay_store<<<kfs_div_up(cap * 2, 256), 256, 0, r->compute>>>(reinterpret_cast<const uint4 *>(d_desc + (size_t)i * cap * 32), d_cnt + i,
+                                                                         reinterpret_cast<uint4 *>(r->d_kf_desc + (size_t)sl * cap * 32), r->d_kf_count + sl, cap * 2);
+        if (cudaGetLastError() != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_replay_store launch failed");
+        r->launches++;
     }
     KFS_CUDA_TRY(cudaEventRecord(S.ev_knn, r->compute));
     KFS_CUDA_TRY(cudaStreamWaitEvent(s_out, S.ev_knn, 0));

@@ -38,7 +38,11 @@ class ORB:
             N.lib().kfs_orb_destroy(self._h)
             self._h = C.c_void_p()
 
-    __del__ = close
+    def __del__(self):   # at interpreter shutdown module globals may already be gone: nothing to free then
+        try:
+            self.close()
+        except Exception:
+            pass
 
     # -- cv2-shaped calls ---------------------------------------------------------------------------
     def detectAndCompute(self, image, mask=None, capacity=None):
@@ -177,7 +181,11 @@ class BFMatcher:
             N.lib().kfs_bf_destroy(self._h)
             self._h = C.c_void_p()
 
-    __del__ = close
+    def __del__(self):   # at interpreter shutdown module globals may already be gone: nothing to free then
+        try:
+            self.close()
+        except Exception:
+            pass
 
     @staticmethod
     def _desc(a):
@@ -274,7 +282,11 @@ class Replay:
             N.lib().kfs_replay_destroy(self._h)
             self._h = C.c_void_p()
 
-    __del__ = close
+    def __del__(self):   # at interpreter shutdown module globals may already be gone: nothing to free then
+        try:
+            self.close()
+        except Exception:
+            pass
 
     @property
     def capacity(self):
@@ -337,7 +349,11 @@ class TrackerFrontEnd:
             N.lib().kfs_frontend_destroy(self._h)
             self._h = C.c_void_p()
 
-    __del__ = close
+    def __del__(self):   # at interpreter shutdown module globals may already be gone: nothing to free then
+        try:
+            self.close()
+        except Exception:
+            pass
 
     @property
     def capacity(self):

@@ -9,7 +9,7 @@ from _util import synth
 
 pytestmark = pytest.mark.gpu
 
-SWITCHES = ["KFS_ORB_GRAPHS", "KFS_ORB_TMA", "KFS_ORB_FUSED_PYRAMID", "KFS_ORB_FAST_HALF", "KFS_ORB_PDL"]
+SWITCHES = ["KFS_ORB_GRAPHS", "KFS_ORB_TMA", "KFS_ORB_FUSED_PYRAMID", "KFS_ORB_FAST_HALF", "KFS_ORB_PDL", "KFS_ORB_DESCRIBE2"]
 
 
 @pytest.fixture(scope="module")
@@ -58,3 +58,42 @@ def test_switches_do_not_change_results(kfs):
     same(ref, got)
     got, _ = extract(kfs, frames, {"KFS_ORB_FUSED_PYRAMID": "2"})     # one-launch pyramid for the batch as well
     same(ref, got)
+
+
+def _knn_with_env(kfs, q, t, env):
+    saved = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        bf = kfs.BFMatcher_create(kfs.NORM_HAMMING)      # KFS_BF_SPLIT / KFS_BF_CLUSTER are read when the handle is created
+        out = [bf.knnMatch(q, t, 2) for _ in range(2)]   # twice: the arrival counters of the global merge must return to zero
+        out.append(bf.knnMatchPairs([(q, t), (q[:130], t), (q, t[:129])], 2))
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    return out
+
+
+@pytest.mark.parametrize("nq,nt", [(300, 2000), (2000, 2000), (700, 100), (129, 1025)])
+def test_knn_split_and_cluster_merge_do_not_change_results(kfs, nq, nt):
+    """Train-row splits over CTAs (KFS_BF_SPLIT = 1..16) and both ways of merging them — a thread-block cluster's distributed
+    shared memory (default) or global scratch + last arriver (KFS_BF_CLUSTER=0) — return the oracle's rows."""
+    from oracle import oracle as O
+    q = synth.random_descriptors(nq, seed=3 * nq + 1)
+    t = synth.random_descriptors(nt, seed=5 * nt + 2)
+    rm, rc = O.knn_match(q, t, 2)
+    for cluster in ("2", "1", "0"):
+        for split in (None, "1", "2", "3", "5", "8", "13", "16"):
+            env = {"KFS_BF_CLUSTER": cluster}
+            if split:
+                env["KFS_BF_SPLIT"] = split
+            a, b, pairs = _knn_with_env(kfs, q, t, env)
+            for m, c in (a, b, pairs[0]):
+                assert np.array_equal(c, rc), (cluster, split)
+                assert np.array_equal(m["trainIdx"], rm["trainIdx"]) and np.array_equal(m["distance"], rm["distance"]), (cluster, split)
+            m1, c1 = pairs[1]
+            assert np.array_equal(m1["trainIdx"], rm["trainIdx"][:130]) and np.array_equal(m1["distance"], rm["distance"][:130])
+            r2, _ = O.knn_match(q, t[:129], 2)
+            assert np.array_equal(pairs[2][0]["trainIdx"], r2["trainIdx"]) and np.array_equal(pairs[2][0]["distance"], r2["distance"])
