@@ -61,6 +61,19 @@ __device__ __forceinline__ uint32_t bf_carry(uint32_t a, uint32_t b, uint32_t s)
     return r;
 }
 
+__device__ __forceinline__ uint32_t bf_andn(uint32_t a, uint32_t b) // a & ~b
+{
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %2, 0x30;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+__device__ __forceinline__ uint32_t bf_mad(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+
 __device__ __forceinline__ void bf_top2_insert(uint32_t key, uint32_t &b1, uint32_t &b2)
 {
     const uint32_t hi = max(key, b1);
@@ -93,7 +106,7 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
     const int qgroup = warp % BF_QWARPS, tsplit = warp / BF_QWARPS;
 
     // query descriptors -> registers (clamped index for the ragged tail; results of clamped rows are dropped).
-    // Kept per query: words 0, 1, 3, 4, 7 and the three XOR-linear combinations the carry-save sums need (see the loop).
+    // Kept per query: words 0, 1, 3, 4 and the four XOR-linear combinations the carry-save sums need (see the loop).
     uint32_t q[BF_QPT][8];
     uint32_t b1[BF_QPT], b2[BF_QPT];
 #pragma unroll
@@ -101,13 +114,16 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
         const int qi = min(q0 + qgroup * (32 * BF_QPT) + r * 32 + lane, nq - 1);
         const uint4 *src = reinterpret_cast<const uint4 *>(P.query + (size_t)qi * 32);
         const uint4 a = __ldg(src), b = __ldg(src + 1);
-        q[r][0] = a.x; q[r][1] = a.y; q[r][3] = a.w; q[r][4] = b.x; q[r][7] = b.w;
+        q[r][0] = a.x; q[r][1] = a.y; q[r][3] = a.w; q[r][4] = b.x;
         q[r][2] = bf_xor3(a.x, a.y, a.z);            // Q012
         q[r][5] = bf_xor3(a.w, b.x, b.y);            // Q345
         q[r][6] = bf_xor3(q[r][2], q[r][5], b.z);    // Q0..6
+        q[r][7] = q[r][6] ^ b.w;                     // Q0..7
         b1[r] = BF_INF; b2[r] = BF_INF;
     }
 
+    uint32_t k18 = 1u << 18, k19 = 1u << 19, k20 = 1u << 20; // key = dist << 18 | trainIdx, built by IMADs (see the loop)
+    asm volatile("" : "+r"(k18), "+r"(k19), "+r"(k20));
     // this CTA's train rows [t0, t1)
     const int S = gridDim.z, split = blockIdx.z;
     const int seg = S > 1 ? ((nt + BF_GRAN - 1) / BF_GRAN + S - 1) / S * BF_GRAN : nt; // whole granules per split
@@ -137,24 +153,29 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
             const uint4 ta = tp[2 * j], tb = tp[2 * j + 1];
             const uint32_t tkey = (uint32_t)(base + j);
             // XOR-linear combinations of the train row, shared by this thread's BF_QPT queries
-            const uint32_t t012 = bf_xor3(ta.x, ta.y, ta.z), t345 = bf_xor3(ta.w, tb.x, tb.y), t06 = bf_xor3(t012, t345, tb.z);
+            const uint32_t t012 = bf_xor3(ta.x, ta.y, ta.z), t345 = bf_xor3(ta.w, tb.x, tb.y), t06 = bf_xor3(t012, t345, tb.z), t07 = t06 ^ tb.w;
 #pragma unroll
             for (int r = 0; r < BF_QPT; r++) {
-                // 256-bit Hamming distance with a carry-save (Harley-Seal) front end: the 8 XOR words x_i = q_i ^ t_i are
-                // compressed by three full adders so that only 5 POPC are needed:
-                //   x0+x1+x2 = s0 + 2 c0;  x3+x4+x5 = s1 + 2 c1;  s0+s1+x6 = s2 + 2 c2
-                //   popc(all) = popc(s2) + popc(x7) + 2 (popc(c0) + popc(c1) + popc(c2))
+                // 256-bit Hamming distance with a carry-save (Harley-Seal) front end: the 8 XOR words x_i = q_i ^ t_i are compressed
+                // into bit planes so that only FOUR POPC are needed (the XU pipe, 16 lanes per clock and SM, is the kernel's bound):
+                //   x0+x1+x2 = s0 + 2 c0;  x3+x4+x5 = s1 + 2 c1;  s0+s1+x6 = s2 + 2 c2;  s2+x7 = u + 2 h;  c0+c1+c2 = t + 2 f
+                //   popc(all) = popc(u) + 2 (popc(t) + popc(h)) + 4 popc(f)
                 // The SUM words are XOR-linear, so each is ONE xor of a precombined query word and a precombined train word
-                // (s0 = Q012 ^ T012, s1 = Q345 ^ T345, s2 = Q0..6 ^ T0..6), and a CARRY is a 3-input function of two addends
-                // and the sum (the third addend is their xor): c = maj(a, b, a^b^s) = LOP3 0xd4.  x2, x5, x6 are never
-                // formed: 11 LOP3 + 5 POPC per compare (+ 3 LOP3 per train row per thread) instead of 14 + 5.
-                const uint32_t s0 = q[r][2] ^ t012, s1 = q[r][5] ^ t345, s2 = q[r][6] ^ t06;
-                const uint32_t x0 = q[r][0] ^ ta.x, x1 = q[r][1] ^ ta.y, x3 = q[r][3] ^ ta.w, x4 = q[r][4] ^ tb.x, x7 = q[r][7] ^ tb.w;
+                // (s0 = Q012 ^ T012, s1 = Q345 ^ T345, s2 = Q0..6 ^ T0..6, u = Q0..7 ^ T0..7), a CARRY of a full adder is a 3-input
+                // function of two addends and the sum (the third addend is their xor): c = maj(a, b, a^b^s) = LOP3 0xd4, and the half
+                // adder's carry is h = s2 & x7 = s2 & ~u.  x2, x5, x6, x7 are never formed: 14 LOP3 + 4 POPC per compare (+ 4 LOP3 per
+                // train row per thread).  The weighted sum is an IMAD chain whose multipliers sit in registers, so that it stays on
+                // the FMA pipe (with immediates ptxas turns it into LEA / IADD3 on the ALU pipe, which the LOP3s already fill).
+                // Round 1's form (11 LOP3 + 5 POPC) ran at 783 Gcmp/s in tools/lab/knn_lab.cu, this one at 822.
+                const uint32_t s0 = q[r][2] ^ t012, s1 = q[r][5] ^ t345, s2 = q[r][6] ^ t06, u = q[r][7] ^ t07;
+                const uint32_t x0 = q[r][0] ^ ta.x, x1 = q[r][1] ^ ta.y, x3 = q[r][3] ^ ta.w, x4 = q[r][4] ^ tb.x;
                 const uint32_t c0 = bf_carry(x0, x1, s0), c1 = bf_carry(x3, x4, s1), c2 = bf_carry(s0, s1, s2);
-                const uint32_t ones = __popc(s2) + __popc(x7);
-                const uint32_t twos = __popc(c0) + __popc(c1) + __popc(c2);
-                const uint32_t d = ones + 2u * twos;
-                bf_top2_insert(((uint32_t)d << 18) + tkey, b1[r], b2[r]);
+                const uint32_t h = bf_andn(s2, u), t = bf_xor3(c0, c1, c2), f = bf_maj(c0, c1, c2);
+                uint32_t key = bf_mad(__popc(u), k18, tkey);
+                key = bf_mad(__popc(t), k19, key);
+                key = bf_mad(__popc(h), k19, key);
+                key = bf_mad(__popc(f), k20, key);
+                bf_top2_insert(key, b1[r], b2[r]);
             }
         }
         __syncthreads(); // everyone done with this stage before it is refilled two iterations later

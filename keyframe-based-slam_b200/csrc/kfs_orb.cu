@@ -130,26 +130,18 @@ k_resize(const uint8_t *__restrict__ src, long long sfs, int spitch, int sh,
     const uint32_t *sf = reinterpret_cast<const uint32_t *>(src + (long long)blockIdx.z * sfs); // CTA-uniform base
     uint32_t *df = reinterpret_cast<uint32_t *>(dst + (long long)blockIdx.z * dfs);
     const uint32_t dpw = (uint32_t)dpitch >> 2;
-    // all table entries, then all 24 source words, then the arithmetic: the loads of the four rows are in flight together (with a
-    // per-row `break` the compiler kept each row's ytab -> source-word chain behind the previous row's store: long-scoreboard stalls
-    // were the kernel's top stall).  Rows past the level's end recompute the last row and skip the store.
-    uint32_t yt[RZ_ROWS];
-#pragma unroll
-    for (int r = 0; r < RZ_ROWS; r++) yt[r] = __ldg(ytab + min(ybase + r, dh - 1));
-    uint32_t a0[RZ_ROWS], a1[RZ_ROWS], a2[RZ_ROWS], b0[RZ_ROWS], b1[RZ_ROWS], b2[RZ_ROWS];
-#pragma unroll
-    for (int r = 0; r < RZ_ROWS; r++) {
-        const uint32_t y0 = yt[r] & 0xffffu, y1 = min(y0 + 1u, (uint32_t)sh - 1u);
-        const uint32_t o0 = y0 * spw, o1 = y1 * spw; // 32-bit word offsets from the uniform base
-        a0[r] = __ldg(sf + (o0 + w0)); a1[r] = __ldg(sf + (o0 + w1)); a2[r] = __ldg(sf + (o0 + w2));
-        b0[r] = __ldg(sf + (o1 + w0)); b1[r] = __ldg(sf + (o1 + w1)); b2[r] = __ldg(sf + (o1 + w2));
-    }
 #pragma unroll
     for (int r = 0; r < RZ_ROWS; r++) {
         const int y = ybase + r;
-        const uint32_t n1 = yt[r] >> 16, n0 = 256u - n1;
-        const uint32_t lo0 = __funnelshift_r(a0[r], a1[r], shb), hi0 = __funnelshift_r(a1[r], a2[r], shb);
-        const uint32_t lo1 = __funnelshift_r(b0[r], b1[r], shb), hi1 = __funnelshift_r(b1[r], b2[r], shb);
+        if (y >= dh) break;
+        const uint32_t yt = __ldg(ytab + y);
+        const uint32_t y0 = yt & 0xffffu, y1 = min(y0 + 1u, (uint32_t)sh - 1u);
+        const uint32_t n1 = yt >> 16, n0 = 256u - n1;
+        const uint32_t o0 = y0 * spw, o1 = y1 * spw; // 32-bit word offsets from the uniform base
+        const uint32_t a0 = __ldg(sf + (o0 + w0)), a1 = __ldg(sf + (o0 + w1)), a2 = __ldg(sf + (o0 + w2));
+        const uint32_t b0 = __ldg(sf + (o1 + w0)), b1 = __ldg(sf + (o1 + w1)), b2 = __ldg(sf + (o1 + w2));
+        const uint32_t lo0 = __funnelshift_r(a0, a1, shb), hi0 = __funnelshift_r(a1, a2, shb);
+        const uint32_t lo1 = __funnelshift_r(b0, b1, shb), hi1 = __funnelshift_r(b1, b2, shb);
         const uint32_t S0 = n0 * __dp2a_lo(tm.x, kfs_prmt(lo0, hi0, s0), 0u) + (n1 * __dp2a_lo(tm.x, kfs_prmt(lo1, hi1, s0), 0u) + 32768u);
         const uint32_t S1 = n0 * __dp2a_lo(tm.y, kfs_prmt(lo0, hi0, s1), 0u) + (n1 * __dp2a_lo(tm.y, kfs_prmt(lo1, hi1, s1), 0u) + 32768u);
         const uint32_t S2 = n0 * __dp2a_lo(tm.z, kfs_prmt(lo0, hi0, s2), 0u) + (n1 * __dp2a_lo(tm.z, kfs_prmt(lo1, hi1, s2), 0u) + 32768u);
@@ -159,7 +151,7 @@ k_resize(const uint8_t *__restrict__ src, long long sfs, int spitch, int sh,
             const uint32_t t = ((outw & 0x7f7f7f7fu) + 0x01010101u) & outw & 0x80808080u;
             outw = (t >> 7) * 255u;
         }
-        if (y < dh) df[(uint32_t)y * dpw + (uint32_t)gx] = outw;
+        df[(uint32_t)y * dpw + (uint32_t)gx] = outw;
     }
 }
 

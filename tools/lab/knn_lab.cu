@@ -52,6 +52,37 @@ __device__ __forceinline__ uint32_t keyof(const uint32_t *q, uint4 ta, uint4 tb,
     return mad(__popc(f), 1u << 20, kk);
 }
 
+// XOR-linear forms (the shipped compare, kfs_bf.cu): q = {q0, q1, Q012, q3, q4, Q345, Q0..6, q7}, qx = Q0..7; the train row's
+// combinations t012, t345, t06, t07 are formed once per row per thread.  carry(a, b, s) = maj(a, b, a ^ b ^ s) = LOP3 0xd4.
+__device__ __forceinline__ uint32_t carry(uint32_t a, uint32_t b, uint32_t s) { uint32_t r; asm("lop3.b32 %0, %1, %2, %3, 0xd4;" : "=r"(r) : "r"(a), "r"(b), "r"(s)); return r; }
+__device__ __forceinline__ uint32_t andn(uint32_t a, uint32_t b) { uint32_t r; asm("lop3.b32 %0, %1, %2, %2, 0x30;" : "=r"(r) : "r"(a), "r"(b)); return r; } // a & ~b
+// POPCV 25: 11 LOP3 + 5 POPC (shipped).  24: 14 LOP3 + 4 POPC: the two weight-1 words go through a half adder whose sum is XOR-linear
+// (Q0..7 ^ T0..7) and whose carry is s2 & ~sum; the three carries through one more full adder.  26: as 24, weighted sum as an IMAD
+// chain with the multipliers in registers (k18, k19, k20: opaque, so that ptxas keeps IMAD = FMA pipe instead of LEA / IADD3 = ALU).
+template <int POPCV>
+__device__ __forceinline__ uint32_t keylin(const uint32_t *q, uint32_t qx, uint4 ta, uint4 tb, uint32_t t012, uint32_t t345, uint32_t t06, uint32_t t07,
+                                           uint32_t tkey, uint32_t k18, uint32_t k19, uint32_t k20)
+{
+    const uint32_t s0 = q[2] ^ t012, s1 = q[5] ^ t345, s2 = q[6] ^ t06;
+    const uint32_t x0 = q[0] ^ ta.x, x1 = q[1] ^ ta.y, x3 = q[3] ^ ta.w, x4 = q[4] ^ tb.x;
+    const uint32_t c0 = carry(x0, x1, s0), c1 = carry(x3, x4, s1), c2 = carry(s0, s1, s2);
+    if (POPCV == 25) {
+        const uint32_t x7 = q[7] ^ tb.w;
+        const uint32_t ones = __popc(s2) + __popc(x7), twos = __popc(c0) + __popc(c1) + __popc(c2);
+        return ((ones + 2u * twos) << 18) + tkey;
+    }
+    const uint32_t sum1 = qx ^ t07, h = andn(s2, sum1);
+    const uint32_t t = xor3(c0, c1, c2), f = maj(c0, c1, c2);
+    if (POPCV == 24) {
+        const uint32_t twos = __popc(t) + __popc(h);
+        return ((__popc(sum1) + 2u * twos + 4u * __popc(f)) << 18) + tkey;
+    }
+    uint32_t kk = mad(__popc(sum1), k18, tkey);
+    kk = mad(__popc(t), k19, kk);
+    kk = mad(__popc(h), k19, kk);
+    return mad(__popc(f), k20, kk);
+}
+
 template <int POPCV, int BR, int QPT, int TSPLIT, int THREADS, int CHUNK, int UNR>
 __global__ void __launch_bounds__(THREADS) k_knn(const uint8_t *__restrict__ Q, const uint8_t *__restrict__ T, int nq, int nt, uint2 *__restrict__ out)
 {
@@ -61,15 +92,21 @@ __global__ void __launch_bounds__(THREADS) k_knn(const uint8_t *__restrict__ Q, 
     const int q0 = blockIdx.x * QTILE;
     if (q0 >= nq) return;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, qgroup = warp % QWARPS, tsplit = warp / QWARPS;
-    uint32_t q[QPT][8], b1[QPT], b2[QPT];
+    uint32_t q[QPT][8], qx[QPT], b1[QPT], b2[QPT];
 #pragma unroll
     for (int r = 0; r < QPT; r++) {
         const int qi = min(q0 + qgroup * (32 * QPT) + r * 32 + lane, nq - 1);
         const uint4 *src = reinterpret_cast<const uint4 *>(query + (size_t)qi * 32);
         const uint4 a = __ldg(src), b = __ldg(src + 1);
         q[r][0] = a.x; q[r][1] = a.y; q[r][2] = a.z; q[r][3] = a.w; q[r][4] = b.x; q[r][5] = b.y; q[r][6] = b.z; q[r][7] = b.w;
+        if (POPCV >= 20) {
+            q[r][2] = xor3(a.x, a.y, a.z); q[r][5] = xor3(a.w, b.x, b.y); q[r][6] = xor3(q[r][2], q[r][5], b.z);
+            qx[r] = q[r][6] ^ b.w;
+        }
         b1[r] = b2[r] = 0xffffffffu;
     }
+    uint32_t k18 = 1u << 18, k19 = 1u << 19, k20 = 1u << 20;
+    asm volatile("" : "+r"(k18), "+r"(k19), "+r"(k20));
     const int nchunks = (nt + CHUNK - 1) / CHUNK;
     auto issue = [&](int chunk, int stage) {
         const int base = chunk * CHUNK, rows = min(CHUNK, nt - base);
@@ -107,9 +144,11 @@ __global__ void __launch_bounds__(THREADS) k_knn(const uint8_t *__restrict__ Q, 
             const uint32_t tkey = (uint32_t)(base + j);
             uint32_t key[QPT];
             bool upd = false;
+            uint32_t t012 = 0, t345 = 0, t06 = 0, t07 = 0;
+            if (POPCV >= 20) { t012 = xor3(ta.x, ta.y, ta.z); t345 = xor3(ta.w, tb.x, tb.y); t06 = xor3(t012, t345, tb.z); t07 = t06 ^ tb.w; }
 #pragma unroll
             for (int r = 0; r < QPT; r++) {
-                key[r] = keyof<POPCV, BR>(q[r], ta, tb, tkey);
+                key[r] = POPCV >= 20 ? keylin<POPCV>(q[r], qx[r], ta, tb, t012, t345, t06, t07, tkey, k18, k19, k20) : keyof<POPCV, BR>(q[r], ta, tb, tkey);
                 if (BR == 1) upd |= key[r] < b2[r]; else ins(key[r], b1[r], b2[r]);
             }
             if (BR == 1 && upd) {
@@ -173,6 +212,14 @@ int main(int argc, char **argv)
     CK(cudaMemcpy(dQ, hq.data(), hq.size(), cudaMemcpyHostToDevice)); CK(cudaMemcpy(dT, ht.data(), ht.size(), cudaMemcpyHostToDevice));
     //  POPCV, BR, QPT, TSPLIT, THREADS, CHUNK, UNR
     RUN(5, 0, 4, 8, 256, 512, 2);
+    RUN(25, 0, 4, 8, 256, 512, 2);
+    RUN(24, 0, 4, 8, 256, 512, 2);
+    RUN(26, 0, 4, 8, 256, 512, 2);
+    RUN(26, 0, 4, 8, 256, 512, 1);
+    RUN(26, 0, 4, 8, 256, 512, 4);
+    RUN(26, 0, 3, 8, 256, 512, 2);
+    RUN(26, 0, 6, 8, 256, 512, 1);
+    RUN(26, 0, 4, 4, 128, 512, 2);
     RUN(15, 0, 4, 8, 256, 512, 2);
     RUN(16, 0, 4, 8, 256, 512, 2);
     RUN(4, 0, 4, 8, 256, 512, 2);
