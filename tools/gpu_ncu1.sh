@@ -8,6 +8,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -s 16 -c 64 --csv --lo
     python tools/ncu_step.py 2 8 1 > gpurun_out/${tag}_one_ncu.log 2>&1
 echo "one-frame launch list rc=$?"
 python tools/ncu_step.py 2 > gpurun_out/${tag}_plain3.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'k_describe|k_resize' -s 8 -c 3 -f -o gpurun_out/${tag}_prof_describe \
+ncu --set full --clock-control none --import-source on -k regex:k_describe -s 1 -c 1 -f -o gpurun_out/${tag}_prof_describe \
     python tools/ncu_step.py 2 > gpurun_out/${tag}_ncu3.log 2>&1
 echo "describe capture rc=$?"
