@@ -148,35 +148,52 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
         const int base = t0 + c * BF_CHUNK + tsplit * slice;
         const int rows = min(slice, t1 - base); // may be <= 0 for the last groups
         const uint4 *tp = &s_train[stage][tsplit * slice * 2];
+        // 256-bit Hamming distance with a carry-save (Harley-Seal) front end: the 8 XOR words x_i = q_i ^ t_i are compressed into bit
+        // planes so that only FOUR POPC are needed (the XU pipe, 16 lanes per clock and SM, is the kernel's bound):
+        //   x0+x1+x2 = s0 + 2 c0;  x3+x4+x5 = s1 + 2 c1;  s0+s1+x6 = s2 + 2 c2;  s2+x7 = u + 2 h;  c0+c1+c2 = t + 2 f
+        //   popc(all) = popc(u) + 2 (popc(t) + popc(h)) + 4 popc(f)
+        // The SUM words are XOR-linear, so each is ONE xor of a precombined query word and a precombined train word
+        // (s0 = Q012 ^ T012, s1 = Q345 ^ T345, s2 = Q0..6 ^ T0..6, u = Q0..7 ^ T0..7), a CARRY of a full adder is a 3-input function of
+        // two addends and the sum (the third addend is their xor): c = maj(a, b, a^b^s) = LOP3 0xd4, and the half adder's carry is
+        // h = s2 & x7 = s2 & ~u.  x2, x5, x6, x7 are never formed: 14 LOP3 + 4 POPC per compare (+ 4 LOP3 per train row per thread).
+        // The weighted sum is an IMAD chain whose multipliers sit in registers, so that it stays on the FMA pipe (with immediates
+        // ptxas turns it into LEA / IADD3 on the ALU pipe, which the LOP3s already fill).  Round 1's form (11 LOP3 + 5 POPC) ran at
+        // 783 Gcmp/s in tools/lab/knn_lab.cu, this one at 811, and at 833 with the two-row top-2 update below.
+        auto key_of = [&](const uint32_t (&qr)[8], const uint4 &ta, const uint4 &tb, uint32_t t012, uint32_t t345, uint32_t t06, uint32_t t07,
+                          uint32_t tkey) -> uint32_t {
+            const uint32_t s0 = qr[2] ^ t012, s1 = qr[5] ^ t345, s2 = qr[6] ^ t06, u = qr[7] ^ t07;
+            const uint32_t x0 = qr[0] ^ ta.x, x1 = qr[1] ^ ta.y, x3 = qr[3] ^ ta.w, x4 = qr[4] ^ tb.x;
+            const uint32_t c0 = bf_carry(x0, x1, s0), c1 = bf_carry(x3, x4, s1), c2 = bf_carry(s0, s1, s2);
+            const uint32_t h = bf_andn(s2, u), t = bf_xor3(c0, c1, c2), f = bf_maj(c0, c1, c2);
+            uint32_t key = bf_mad(__popc(u), k18, tkey);
+            key = bf_mad(__popc(t), k19, key);
+            key = bf_mad(__popc(h), k19, key);
+            return bf_mad(__popc(f), k20, key);
+        };
+        int j = 0;
+        // two train rows per step: the running (b1 <= b2) and the sorted pair (lo <= hi) of the two new keys merge in 5 min / max
+        // operations — b1' = min(b1, lo), b2' = min3(b2, max(b1, lo), hi) — instead of 2 x 3
 #pragma unroll 2
-        for (int j = 0; j < rows; j++) {
-            const uint4 ta = tp[2 * j], tb = tp[2 * j + 1];
+        for (; j + 1 < rows; j += 2) {
+            const uint4 ta = tp[2 * j], tb = tp[2 * j + 1], tc = tp[2 * j + 2], td = tp[2 * j + 3];
             const uint32_t tkey = (uint32_t)(base + j);
-            // XOR-linear combinations of the train row, shared by this thread's BF_QPT queries
-            const uint32_t t012 = bf_xor3(ta.x, ta.y, ta.z), t345 = bf_xor3(ta.w, tb.x, tb.y), t06 = bf_xor3(t012, t345, tb.z), t07 = t06 ^ tb.w;
+            const uint32_t a012 = bf_xor3(ta.x, ta.y, ta.z), a345 = bf_xor3(ta.w, tb.x, tb.y), a06 = bf_xor3(a012, a345, tb.z), a07 = a06 ^ tb.w;
+            const uint32_t c012 = bf_xor3(tc.x, tc.y, tc.z), c345 = bf_xor3(tc.w, td.x, td.y), c06 = bf_xor3(c012, c345, td.z), c07 = c06 ^ td.w;
 #pragma unroll
             for (int r = 0; r < BF_QPT; r++) {
-                // 256-bit Hamming distance with a carry-save (Harley-Seal) front end: the 8 XOR words x_i = q_i ^ t_i are compressed
-                // into bit planes so that only FOUR POPC are needed (the XU pipe, 16 lanes per clock and SM, is the kernel's bound):
-                //   x0+x1+x2 = s0 + 2 c0;  x3+x4+x5 = s1 + 2 c1;  s0+s1+x6 = s2 + 2 c2;  s2+x7 = u + 2 h;  c0+c1+c2 = t + 2 f
-                //   popc(all) = popc(u) + 2 (popc(t) + popc(h)) + 4 popc(f)
-                // The SUM words are XOR-linear, so each is ONE xor of a precombined query word and a precombined train word
-                // (s0 = Q012 ^ T012, s1 = Q345 ^ T345, s2 = Q0..6 ^ T0..6, u = Q0..7 ^ T0..7), a CARRY of a full adder is a 3-input
-                // function of two addends and the sum (the third addend is their xor): c = maj(a, b, a^b^s) = LOP3 0xd4, and the half
-                // adder's carry is h = s2 & x7 = s2 & ~u.  x2, x5, x6, x7 are never formed: 14 LOP3 + 4 POPC per compare (+ 4 LOP3 per
-                // train row per thread).  The weighted sum is an IMAD chain whose multipliers sit in registers, so that it stays on
-                // the FMA pipe (with immediates ptxas turns it into LEA / IADD3 on the ALU pipe, which the LOP3s already fill).
-                // Round 1's form (11 LOP3 + 5 POPC) ran at 783 Gcmp/s in tools/lab/knn_lab.cu, this one at 822.
-                const uint32_t s0 = q[r][2] ^ t012, s1 = q[r][5] ^ t345, s2 = q[r][6] ^ t06, u = q[r][7] ^ t07;
-                const uint32_t x0 = q[r][0] ^ ta.x, x1 = q[r][1] ^ ta.y, x3 = q[r][3] ^ ta.w, x4 = q[r][4] ^ tb.x;
-                const uint32_t c0 = bf_carry(x0, x1, s0), c1 = bf_carry(x3, x4, s1), c2 = bf_carry(s0, s1, s2);
-                const uint32_t h = bf_andn(s2, u), t = bf_xor3(c0, c1, c2), f = bf_maj(c0, c1, c2);
-                uint32_t key = bf_mad(__popc(u), k18, tkey);
-                key = bf_mad(__popc(t), k19, key);
-                key = bf_mad(__popc(h), k19, key);
-                key = bf_mad(__popc(f), k20, key);
-                bf_top2_insert(key, b1[r], b2[r]);
+                const uint32_t kA = key_of(q[r], ta, tb, a012, a345, a06, a07, tkey);
+                const uint32_t kB = key_of(q[r], tc, td, c012, c345, c06, c07, tkey + 1u);
+                const uint32_t lo = min(kA, kB), hi = max(kA, kB);
+                const uint32_t mx = max(b1[r], lo);
+                b1[r] = min(b1[r], lo);
+                b2[r] = __vimin3_u32(b2[r], mx, hi);
             }
+        }
+        if (j < rows) { // odd row count
+            const uint4 ta = tp[2 * j], tb = tp[2 * j + 1];
+            const uint32_t a012 = bf_xor3(ta.x, ta.y, ta.z), a345 = bf_xor3(ta.w, tb.x, tb.y), a06 = bf_xor3(a012, a345, tb.z), a07 = a06 ^ tb.w;
+#pragma unroll
+            for (int r = 0; r < BF_QPT; r++) bf_top2_insert(key_of(q[r], ta, tb, a012, a345, a06, a07, (uint32_t)(base + j)), b1[r], b2[r]);
         }
         __syncthreads(); // everyone done with this stage before it is refilled two iterations later
     }

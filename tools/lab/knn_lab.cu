@@ -128,9 +128,15 @@ __global__ void __launch_bounds__(THREADS) k_knn(const uint8_t *__restrict__ Q, 
             for (; jstart + 1 < rows; jstart += 2) {
                 const uint4 ta = tp[2 * jstart], tb = tp[2 * jstart + 1], tc = tp[2 * jstart + 2], td = tp[2 * jstart + 3];
                 const uint32_t tkey = (uint32_t)(base + jstart);
+                uint32_t a012 = 0, a345 = 0, a06 = 0, a07 = 0, c012 = 0, c345 = 0, c06 = 0, c07 = 0;
+                if (POPCV >= 20) {
+                    a012 = xor3(ta.x, ta.y, ta.z); a345 = xor3(ta.w, tb.x, tb.y); a06 = xor3(a012, a345, tb.z); a07 = a06 ^ tb.w;
+                    c012 = xor3(tc.x, tc.y, tc.z); c345 = xor3(tc.w, td.x, td.y); c06 = xor3(c012, c345, td.z); c07 = c06 ^ td.w;
+                }
 #pragma unroll
                 for (int r = 0; r < QPT; r++) {
-                    const uint32_t kA = keyof<POPCV, 0>(q[r], ta, tb, tkey), kB = keyof<POPCV, 0>(q[r], tc, td, tkey + 1);
+                    const uint32_t kA = POPCV >= 20 ? keylin<POPCV>(q[r], qx[r], ta, tb, a012, a345, a06, a07, tkey, k18, k19, k20) : keyof<POPCV, 0>(q[r], ta, tb, tkey);
+                    const uint32_t kB = POPCV >= 20 ? keylin<POPCV>(q[r], qx[r], tc, td, c012, c345, c06, c07, tkey + 1, k18, k19, k20) : keyof<POPCV, 0>(q[r], tc, td, tkey + 1);
                     const uint32_t lo = min(kA, kB), hi = max(kA, kB);
                     const uint32_t mx = max(b1[r], lo);
                     b1[r] = min(b1[r], lo);
@@ -215,6 +221,9 @@ int main(int argc, char **argv)
     RUN(25, 0, 4, 8, 256, 512, 2);
     RUN(24, 0, 4, 8, 256, 512, 2);
     RUN(26, 0, 4, 8, 256, 512, 2);
+    RUN(26, 2, 4, 8, 256, 512, 1);
+    RUN(26, 2, 4, 8, 256, 512, 2);
+    RUN(26, 2, 3, 8, 256, 512, 2);
     RUN(26, 0, 4, 8, 256, 512, 1);
     RUN(26, 0, 4, 8, 256, 512, 4);
     RUN(26, 0, 3, 8, 256, 512, 2);
