@@ -2462,10 +2462,23 @@ kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const KfsHostBatch &hb)
     o->alias_valid = false;
     s = kfs_orb_ensure(o, w, h, batch, hb.mask != nullptr);
     if (s) return s;
-    int chunk = o->pipeline_chunk > 0 ? o->pipeline_chunk : (batch >= 8 ? kfs_div_up(batch, 4) : batch);
-    if (chunk > batch) chunk = batch;
-    if (o->profiling) chunk = batch; // per-stage event timing describes one unchunked pass
-    const int nchunks = kfs_div_up(batch, chunk);
+    // Chunk schedule.  An explicit chunk size (kfs_orb_set_pipeline_chunk) cuts the batch evenly.  The automatic schedule is three
+    // quarters of the batch in quarter-size chunks and a TAPERED tail (1/8, 1/16, 1/16): what is left to do after the last byte of the
+    // upload has arrived — the kernel chain and the download of the last chunk — is then a sixteenth of the batch instead of a quarter.
+    std::vector<int> cstart, ccount;
+    auto add_chunk = [&](int f0, int n) { cstart.push_back(f0); ccount.push_back(n); return f0 + n; };
+    if (o->profiling || batch < 8 || o->pipeline_chunk >= batch) {
+        add_chunk(0, batch); // (profiling: per-stage event timing describes one unchunked pass)
+    } else if (o->pipeline_chunk > 0) {
+        for (int f0 = 0; f0 < batch;) f0 = add_chunk(f0, std::min(o->pipeline_chunk, batch - f0));
+    } else {
+        const int q = kfs_div_up(batch, 4);
+        int f0 = 0;
+        for (int i = 0; i < 3 && f0 < batch; i++) f0 = add_chunk(f0, std::min(q, batch - f0));
+        const int taper[3] = {kfs_div_up(batch, 8), kfs_div_up(batch, 16), batch};
+        for (int i = 0; i < 3 && f0 < batch; i++) f0 = add_chunk(f0, std::min(batch >= 32 ? taper[i] : batch, batch - f0));
+    }
+    const int nchunks = (int)cstart.size();
     s = kfs_orb_pipeline_init(o, nchunks);
     if (s) return s;
     if (hb.mask) {
@@ -2496,7 +2509,7 @@ kfs_status kfs_orb_enqueue_host_batch(kfs_orb *o, const KfsHostBatch &hb)
     int rows = hb.out_rows > 0 ? hb.out_rows : cp;
     if (rows > cp) rows = cp;
     for (int c = 0; c < nchunks; c++) {
-        const int f0 = c * chunk, nb = (f0 + chunk <= batch) ? chunk : batch - f0;
+        const int f0 = cstart[(size_t)c], nb = ccount[(size_t)c];
         if (ch == 3) s = kfs_h2d_frames(o->rgb_stage, ipitch, ifs, hb.image, hb.step, hb.frame_stride, 3 * w, h, f0, nb, o->s_in);
         else s = kfs_h2d_frames(o->pyr[0], (size_t)o->lpitch[0], (size_t)o->lfs[0], hb.image, hb.step, hb.frame_stride, w, h, f0, nb, o->s_in);
         if (s) return s;
