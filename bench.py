@@ -642,7 +642,7 @@ def run_ours(args):
                      "attached to the extractor (kfs_bf_attach_orb: rows just extracted are matched on the device, not uploaded again)",
               "ms_per_step_orb_call": round(orb_ms, 3), "ms_per_step_knn_call": round(knn_ms_call, 3),
               "detached": {"value": round(plain_value, 1), "h2d_bytes_per_step": int(plain_h2d), "ms_per_step_knn_call": round(plain_knn_ms, 3)},
-              "pipeline_chunk_frames": args.e2e_chunk or "auto (batch/4)"}
+              "pipeline_chunk_frames": args.e2e_chunk or "auto (3 x batch/4, then batch/8, batch/16, batch/16)"}
 
     # ---- e2e through the replay executor (kfs_replay_*): same host buffers in, keypoints + descriptors + kNN matches +
     # ratio-test survivors out, descriptors matched where they were produced; up to `arenas` batches in flight.
