@@ -1162,20 +1162,20 @@ def run_ours(args):
     ncmp = float(sum(counts[keyframe_of(i)] * counts[i] for i in range(B)))
     gcmp = ncmp / (knn_ms * 1e-3) / 1e9 if knn_ms > 0 else 0.0
     # the matcher's ceiling: the tighter of the POPC floor (the carry-save compare issues 4 POPC.32, kfs_bf.cu) and the ALU-dispatch
-    # floor (17.5 ALU-pipe slots per compare: 14 LOP3 + 4 per-row LOP3 / 4 queries + 2.5 VIMNMX of the two-row top-2 update, at the measured LOP3
+    # floor (16.5 ALU-pipe slots per compare: 14 LOP3 + 2.5 VIMNMX of the two-row top-2 update, at the measured LOP3
     # rate; the weighted sum runs as IMADs on the FMA pipe)
-    POPC_PER_CMP, ALU_PER_CMP = 4.0, 17.5
+    POPC_PER_CMP, ALU_PER_CMP = 4.0, 16.5
     peak_popc4 = popc / POPC_PER_CMP if popc else None
     peak_alu = lop3 / ALU_PER_CMP if lop3 else None
     peak_cmp = min(peak_popc4, peak_alu) if popc and lop3 else (peak_popc4 or peak_alu)
     roofline_popc = {"kernel": "k_hamming_knn2", "bound": "popc", "achieved": round(gcmp, 1), "unit": "Gcmp/s",
                      "peak": round(peak_cmp, 1) if peak_cmp else None, "frac": round(gcmp / peak_cmp, 4) if peak_cmp else None,
                      "peak_popc_floor_4_per_compare": round(peak_popc4, 1) if peak_popc4 else None,
-                     "peak_alu_floor_17.5_slots_per_compare": round(peak_alu, 1) if peak_alu else None,
+                     "peak_alu_floor_16.5_slots_per_compare": round(peak_alu, 1) if peak_alu else None,
                      "frac_of_survey_8_popc_definition": round(gcmp / (popc / 8.0), 4) if popc else None,
                      "popc_gops_measured": round(popc, 1) if popc else None, "lop3_gops_measured": round(lop3, 1) if lop3 else None,
                      "ms_per_batch": round(knn_ms, 4), "us_per_frame": round(knn_ms * 1e3 / B, 3),
-                     "note": "peak = min(measured POPC.32 rate / 4, measured LOP3 rate / 17.5): what this kernel's instruction mix allows (round 1's compare "
+                     "note": "peak = min(measured POPC.32 rate / 4, measured LOP3 rate / 16.5): what this kernel's instruction mix allows (round 1's compare "
                              "needed 5 POPC + 21.3 ALU slots: its ceiling was 863 Gcmp/s); SURVEY 8d's definition (8 POPC per compare) is kept beside it "
                              "and exceeds 1 because the compare needs only 4"}
 

@@ -155,13 +155,26 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
         // The SUM words are XOR-linear, so each is ONE xor of a precombined query word and a precombined train word
         // (s0 = Q012 ^ T012, s1 = Q345 ^ T345, s2 = Q0..6 ^ T0..6, u = Q0..7 ^ T0..7), a CARRY of a full adder is a 3-input function of
         // two addends and the sum (the third addend is their xor): c = maj(a, b, a^b^s) = LOP3 0xd4, and the half adder's carry is
-        // h = s2 & x7 = s2 & ~u.  x2, x5, x6, x7 are never formed: 14 LOP3 + 4 POPC per compare (+ 4 LOP3 per train row per thread).
+        // h = s2 & x7 = s2 & ~u.  x2, x5, x6, x7 are never formed: 14 LOP3 + 4 POPC per compare.
         // The weighted sum is an IMAD chain whose multipliers sit in registers, so that it stays on the FMA pipe (with immediates
         // ptxas turns it into LEA / IADD3 on the ALU pipe, which the LOP3s already fill).  Round 1's form (11 LOP3 + 5 POPC) ran at
         // 783 Gcmp/s in tools/lab/knn_lab.cu, this one at 811, and at 833 with the two-row top-2 update below.
-        auto key_of = [&](const uint32_t (&qr)[8], const uint4 &ta, const uint4 &tb, uint32_t t012, uint32_t t345, uint32_t t06, uint32_t t07,
-                          uint32_t tkey) -> uint32_t {
-            const uint32_t s0 = qr[2] ^ t012, s1 = qr[5] ^ t345, s2 = qr[6] ^ t06, u = qr[7] ^ t07;
+        // The four train-side combinations do not depend on the query: the warp that will scan a slice first rewrites its rows IN PLACE
+        // in shared memory, {t0 t1 t2 t3 | t4 t5 t6 t7} -> {t0 t1 T012 t3 | t4 T345 T0..6 T0..7} (t2, t5, t6, t7 enter the compare only
+        // through the combinations), one or two rows per lane, so that the scan below forms nothing per row.
+        static_assert(BF_QWARPS == 1, "a train slice is scanned by exactly one warp (the in-place rewrite is warp-local)");
+        {
+            uint4 *tw = &s_train[stage][tsplit * slice * 2];
+            for (int rr = lane; rr < rows; rr += 32) {
+                uint4 a = tw[2 * rr], b = tw[2 * rr + 1];
+                const uint32_t t012 = bf_xor3(a.x, a.y, a.z), t345 = bf_xor3(a.w, b.x, b.y), t06 = bf_xor3(t012, t345, b.z);
+                a.z = t012; b.y = t345; b.z = t06; b.w = t06 ^ b.w;
+                tw[2 * rr] = a; tw[2 * rr + 1] = b;
+            }
+            __syncwarp();
+        }
+        auto key_of = [&](const uint32_t (&qr)[8], const uint4 &ta, const uint4 &tb, uint32_t tkey) -> uint32_t {
+            const uint32_t s0 = qr[2] ^ ta.z, s1 = qr[5] ^ tb.y, s2 = qr[6] ^ tb.z, u = qr[7] ^ tb.w;
             const uint32_t x0 = qr[0] ^ ta.x, x1 = qr[1] ^ ta.y, x3 = qr[3] ^ ta.w, x4 = qr[4] ^ tb.x;
             const uint32_t c0 = bf_carry(x0, x1, s0), c1 = bf_carry(x3, x4, s1), c2 = bf_carry(s0, s1, s2);
             const uint32_t h = bf_andn(s2, u), t = bf_xor3(c0, c1, c2), f = bf_maj(c0, c1, c2);
@@ -177,12 +190,10 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
         for (; j + 1 < rows; j += 2) {
             const uint4 ta = tp[2 * j], tb = tp[2 * j + 1], tc = tp[2 * j + 2], td = tp[2 * j + 3];
             const uint32_t tkey = (uint32_t)(base + j);
-            const uint32_t a012 = bf_xor3(ta.x, ta.y, ta.z), a345 = bf_xor3(ta.w, tb.x, tb.y), a06 = bf_xor3(a012, a345, tb.z), a07 = a06 ^ tb.w;
-            const uint32_t c012 = bf_xor3(tc.x, tc.y, tc.z), c345 = bf_xor3(tc.w, td.x, td.y), c06 = bf_xor3(c012, c345, td.z), c07 = c06 ^ td.w;
 #pragma unroll
             for (int r = 0; r < BF_QPT; r++) {
-                const uint32_t kA = key_of(q[r], ta, tb, a012, a345, a06, a07, tkey);
-                const uint32_t kB = key_of(q[r], tc, td, c012, c345, c06, c07, tkey + 1u);
+                const uint32_t kA = key_of(q[r], ta, tb, tkey);
+                const uint32_t kB = key_of(q[r], tc, td, tkey + 1u);
                 const uint32_t lo = min(kA, kB), hi = max(kA, kB);
                 const uint32_t mx = max(b1[r], lo);
                 b1[r] = min(b1[r], lo);
@@ -191,9 +202,8 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
         }
         if (j < rows) { // odd row count
             const uint4 ta = tp[2 * j], tb = tp[2 * j + 1];
-            const uint32_t a012 = bf_xor3(ta.x, ta.y, ta.z), a345 = bf_xor3(ta.w, tb.x, tb.y), a06 = bf_xor3(a012, a345, tb.z), a07 = a06 ^ tb.w;
 #pragma unroll
-            for (int r = 0; r < BF_QPT; r++) bf_top2_insert(key_of(q[r], ta, tb, a012, a345, a06, a07, (uint32_t)(base + j)), b1[r], b2[r]);
+            for (int r = 0; r < BF_QPT; r++) bf_top2_insert(key_of(q[r], ta, tb, (uint32_t)(base + j)), b1[r], b2[r]);
         }
         __syncthreads(); // everyone done with this stage before it is refilled two iterations later
     }
