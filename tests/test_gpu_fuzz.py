@@ -1,0 +1,92 @@
+"""Randomised parity sweep: frame sizes (odd ones included), ORB parameters, masks, one frame per call and small batches — the GPU
+through the C ABI against the oracle, bit for bit, followed by the k=2 matcher on the descriptors just extracted (ragged row counts).
+The oracle is pinned to cv2 by tests/test_oracle_golden.py and tests/test_params_variants.py; with cv2 importable on the host
+(the GPU boxes have it) every fifth case is also checked against cv2 directly.
+KFS_FUZZ_CASES sets the number of cases (default 24; tools/fuzz_parity.py runs a few hundred and records the outcome)."""
+import os
+
+import numpy as np
+import pytest
+
+from _util import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _sorted(kp, desc):
+    o = np.lexsort((kp["x"], kp["y"], kp["octave"]))
+    return kp[o], desc[o]
+
+
+def run_cases(kfs, oracle, ncases, seed=2024, cv2=None, log=None):
+    rng = np.random.default_rng(seed)
+    bf = kfs.BFMatcher_create(kfs.NORM_HAMMING)
+    stats = dict(cases=0, frames=0, keypoints=0, knn_rows=0, cv2_checked=0, empty=0)
+    for c in range(ncases):
+        w, h = int(rng.integers(70, 900)), int(rng.integers(70, 700))
+        if c % 7 == 0:                                   # tiny frames: levels vanish, lists stay empty
+            w, h = int(rng.integers(16, 90)), int(rng.integers(16, 90))
+        nf = int(rng.choice([50, 300, 500, 1000, 2000, 3000]))
+        sf = float(rng.choice([1.1, 1.2, 1.2, 1.2, 1.3, 1.5, 2.0]))
+        nl = int(rng.integers(1, 11))
+        thr = int(rng.choice([5, 10, 20, 20, 20, 35]))
+        nb = int(rng.choice([1, 1, 2, 3, 5]))
+        frames = np.ascontiguousarray(synth.make_stream(nb, h, w, seed=int(rng.integers(1 << 30)), pad=8))
+        mask = None
+        if rng.random() < 0.35:
+            mask = np.zeros((h, w), np.uint8)
+            y0, x0 = int(rng.integers(0, h // 2)), int(rng.integers(0, w // 2))
+            mask[y0:y0 + int(rng.integers(h // 4, h)), x0:x0 + int(rng.integers(w // 4, w))] = int(rng.choice([255, 1, 77]))
+        P = oracle.orb_params(nfeatures=nf, scale_factor=sf, nlevels=nl, fast_threshold=thr)
+        orb = kfs.ORB_create(nf, sf, nl, 31, 0, 2, kfs.ORB_HARRIS_SCORE, 31, thr)
+        tag = "case %d: %dx%d nf=%d sf=%.1f nl=%d thr=%d nb=%d mask=%s" % (c, w, h, nf, sf, nl, thr, nb, mask is not None)
+        descs = []
+        if nb == 1 or mask is not None:
+            got = [orb.detectAndCompute(f, mask) for f in frames]
+        else:
+            kps, ds = orb.detectAndComputeBatch(frames)
+            got = list(zip(kps, ds))
+        for f, (kp, desc) in zip(frames, got):
+            rk, rd = oracle.detect_and_compute(f, mask, P)
+            assert len(kp) == len(rk), tag
+            if len(rk):
+                assert np.array_equal(kp, rk) and np.array_equal(desc, rd), tag
+            else:
+                stats["empty"] += 1
+            descs.append(rd if len(rk) else np.zeros((0, 32), np.uint8))
+            stats["frames"] += 1
+            stats["keypoints"] += len(rk)
+        if cv2 is not None and c % 5 == 0 and len(descs[0]):
+            ck, cd = cv2.ORB_create(nf, sf, nl, 31, 0, 2, cv2.ORB_HARRIS_SCORE, 31, thr).detectAndCompute(frames[0], mask)
+            a = np.array([(k.pt[0], k.pt[1], k.size, k.angle, k.response, k.octave, k.class_id) for k in ck], dtype=kfs.KP_DTYPE)
+            sk, sd = _sorted(a, cd)
+            gk, gd = _sorted(*got[0])
+            assert np.array_equal(sk, gk) and np.array_equal(sd, gd), tag + " (cv2)"
+            stats["cv2_checked"] += 1
+        orb.close()
+        q, t = descs[0], descs[-1][::-1].copy() if len(descs[-1]) else descs[-1]
+        if len(q) and len(t) >= 1:
+            m, cnt = bf.knnMatch(q, t, 2)
+            rm, rc = oracle.knn_match(q, t, 2)
+            kk = min(2, len(t))
+            assert np.array_equal(cnt, rc), tag
+            assert np.array_equal(m["trainIdx"][:, :kk], rm["trainIdx"][:, :kk]) and np.array_equal(m["distance"][:, :kk], rm["distance"][:, :kk]), tag
+            stats["knn_rows"] += len(q)
+        stats["cases"] += 1
+        if log:
+            log(tag + " ok")
+    bf.close()
+    return stats
+
+
+def test_random_parameter_and_size_sweep(oracle):
+    import kfslam_b200 as kfs
+    assert kfs.lib().kfs_device_count() >= 1, "no CUDA device: the product path has no CPU fallback"
+    try:
+        import cv2
+    except Exception:
+        cv2 = None
+    n = int(os.environ.get("KFS_FUZZ_CASES", "24"))
+    stats = run_cases(kfs, oracle, n, cv2=cv2)
+    print("\n[fuzz] %s" % stats)
+    assert stats["cases"] == n and stats["keypoints"] > 0

@@ -1,0 +1,24 @@
+#!/usr/bin/env python3
+"""A few hundred random (size, parameters, mask, batch) cases through tests/test_gpu_fuzz.py's sweep, on the GPU box:
+  python tools/fuzz_parity.py [cases] [seed] > gpurun_out/<tag>_fuzz.txt"""
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import kfslam_b200 as kfs  # noqa: E402
+from oracle import oracle as O  # noqa: E402  (the checker; never on the product path)
+import test_gpu_fuzz as F  # noqa: E402
+
+try:
+    import cv2
+except Exception:
+    cv2 = None
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 300
+seed = int(sys.argv[2]) if len(sys.argv) > 2 else 7
+t0 = time.time()
+stats = F.run_cases(kfs, O, n, seed=seed, cv2=cv2, log=lambda s: print(s, flush=True))
+print("fuzz: %d cases, %d frames, %d keypoints, %d kNN rows bit-exact against the oracle; %d cases also against cv2 %s directly; %d empty frames; %.0f s"
+      % (stats["cases"], stats["frames"], stats["keypoints"], stats["knn_rows"], stats["cv2_checked"], getattr(cv2, "__version__", "n/a"), stats["empty"], time.time() - t0))
