@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """A few hundred random (size, parameters, mask, batch) cases through tests/test_gpu_fuzz.py's sweep, on the GPU box:
-  python tools/fuzz_parity.py [cases] [seed] > gpurun_out/<tag>_fuzz.txt"""
+  python tools/fuzz_parity.py [cases] [seed] [size scale] > gpurun_out/<tag>_fuzz.txt"""
 import os
 import sys
 import time
@@ -18,7 +18,8 @@ except Exception:
     cv2 = None
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 300
 seed = int(sys.argv[2]) if len(sys.argv) > 2 else 7
+scale = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0
 t0 = time.time()
-stats = F.run_cases(kfs, O, n, seed=seed, cv2=cv2, log=lambda s: print(s, flush=True))
-print("fuzz: %d cases, %d frames, %d keypoints, %d kNN rows bit-exact against the oracle; %d cases also against cv2 %s directly; %d empty frames; %.0f s"
-      % (stats["cases"], stats["frames"], stats["keypoints"], stats["knn_rows"], stats["cv2_checked"], getattr(cv2, "__version__", "n/a"), stats["empty"], time.time() - t0))
+stats = F.run_cases(kfs, O, n, seed=seed, cv2=cv2, log=lambda s: print(s, flush=True), scale=scale)
+print("fuzz (seed %d, size scale %.1f): %d cases, %d frames, %d keypoints, %d kNN rows bit-exact against the oracle; %d cases also against cv2 %s directly (%d more rejected by cv2 itself: a level of zero size); %d empty frames; %.0f s"
+      % (seed, scale, stats["cases"], stats["frames"], stats["keypoints"], stats["knn_rows"], stats["cv2_checked"], getattr(cv2, "__version__", "n/a"), stats["cv2_rejected"], stats["empty"], time.time() - t0))
