@@ -95,3 +95,69 @@ def test_random_parameter_and_size_sweep(oracle):
     stats = run_cases(kfs, oracle, n, cv2=cv2)
     print("\n[fuzz] %s" % stats)
     assert stats["cases"] == n and stats["keypoints"] > 0
+
+
+def run_track_cases(kfs, oracle, ncases, seed=99, log=None):
+    """Random tracker sequences through kfs_frontend_track (one call per frame: R,G,B or gray in, keypoints + descriptors + ratio-test
+    survivors + back-projected points out), keyframe promotions at random frames, a random keyframe window matched at the end —
+    against detect_and_compute / knn_match / match_features / match_window of the oracle."""
+    from _track_util import make_depth, make_rgb
+    rng = np.random.default_rng(seed)
+    stats = dict(cases=0, frames=0, matches=0, window_pairs=0)
+    for c in range(ncases):
+        w, h = int(rng.integers(160, 520)), int(rng.integers(120, 420))
+        nf = int(rng.choice([300, 800, 1500]))
+        win = int(rng.integers(1, 5))
+        ratio = float(rng.choice([0.6, 0.75, 0.9]))
+        K = np.array([[500.0 + rng.random() * 50, 0, w / 2 + rng.random()], [0, 500.0 + rng.random() * 50, h / 2 + rng.random()], [0, 0, 1]])
+        gray_in = rng.random() < 0.3
+        mask = None
+        if rng.random() < 0.4:
+            mask = np.zeros((h, w), np.uint8)
+            mask[h // 8:h - h // 8, w // 10:w - w // 12] = 255
+        fe = kfs.TrackerFrontEnd(nfeatures=nf)
+        fe.setWindow(win)
+        P = oracle.orb_params(nfeatures=nf)
+        tag = "track case %d: %dx%d nf=%d win=%d ratio=%.2f gray=%s mask=%s" % (c, w, h, nf, win, ratio, gray_in, mask is not None)
+        s0 = int(rng.integers(1, 1 << 20))
+        kf, kfs_seen, shift = None, [], 0
+        nframes = int(rng.integers(3, 7))
+        for i in range(nframes):
+            shift += int(rng.integers(1, 5))
+            rgb = make_rgb(h, w, s0, shift=shift)
+            img = oracle.rgb2gray(rgb) if gray_in else rgb
+            kp, desc, p3, p2, m = fe.track(img, K, mask=mask, ratio=ratio)
+            rk, rd = oracle.detect_and_compute(oracle.rgb2gray(rgb), mask, P)
+            assert np.array_equal(kp, rk) and np.array_equal(desc, rd), tag
+            if kf is None:
+                assert m is None, tag
+            else:
+                knn, _ = oracle.knn_match(kf[1], rd, 2)
+                r3, r2, rm = oracle.match_features(knn, kf[0], rk, kf[2], K, ratio)
+                assert np.array_equal(m, rm) and np.array_equal(p3, r3) and np.array_equal(p2, r2), tag
+                stats["matches"] += len(rm)
+            if kf is None or rng.random() < 0.4:
+                depth = make_depth(h, w, int(rng.integers(1 << 20)))
+                fe.promoteKeyframe(depth)
+                kf = (rk, rd, depth)
+                kfs_seen.append(rd)
+            stats["frames"] += 1
+        good = fe.matchWindow(None, ratio)                 # the last frame against the window, oldest keyframe first
+        _, ref = oracle.match_window(kfs_seen, rd, win, ratio)
+        assert len(good) == len(ref), tag
+        for a, b in zip(good, ref):
+            assert np.array_equal(a, b), tag
+        stats["window_pairs"] += len(ref)
+        fe.close()
+        stats["cases"] += 1
+        if log:
+            log(tag + " ok")
+    return stats
+
+
+def test_random_tracker_sequences(oracle):
+    import kfslam_b200 as kfs
+    n = int(os.environ.get("KFS_FUZZ_TRACK_CASES", "6"))
+    stats = run_track_cases(kfs, oracle, n)
+    print("\n[fuzz track] %s" % stats)
+    assert stats["cases"] == n and stats["matches"] > 0

@@ -23,3 +23,8 @@ t0 = time.time()
 stats = F.run_cases(kfs, O, n, seed=seed, cv2=cv2, log=lambda s: print(s, flush=True), scale=scale)
 print("fuzz (seed %d, size scale %.1f): %d cases, %d frames, %d keypoints, %d kNN rows bit-exact against the oracle; %d cases also against cv2 %s directly (%d more rejected by cv2 itself: a level of zero size); %d empty frames; %.0f s"
       % (seed, scale, stats["cases"], stats["frames"], stats["keypoints"], stats["knn_rows"], stats["cv2_checked"], getattr(cv2, "__version__", "n/a"), stats["cv2_rejected"], stats["empty"], time.time() - t0))
+if len(sys.argv) > 4:   # fourth argument: number of random tracker sequences (kfs_frontend_track + promotions + window matching)
+    t0 = time.time()
+    ts = F.run_track_cases(kfs, O, int(sys.argv[4]), seed=seed + 1, log=lambda s: print(s, flush=True))
+    print("fuzz track (seed %d): %d sequences, %d frames, %d ratio-test survivors with back-projected points, %d window pairs bit-exact against the oracle; %.0f s"
+          % (seed + 1, ts["cases"], ts["frames"], ts["matches"], ts["window_pairs"], time.time() - t0))
