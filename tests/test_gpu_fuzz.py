@@ -161,3 +161,100 @@ def test_random_tracker_sequences(oracle):
     stats = run_track_cases(kfs, oracle, n)
     print("\n[fuzz track] %s" % stats)
     assert stats["cases"] == n and stats["matches"] > 0
+
+
+def run_replay_cases(kfs, oracle, ncases, seed=5, log=None):
+    """Random plans through the replay executor: several submits per case (batches of random length in flight over the arenas), every
+    frame matched against a random earlier frame of its submit, a random cache slot an earlier submit filled, or nothing
+    (KFS_REPLAY_NO_MATCH); random store_slot writes (a slot written in a submit must not affect that submit's own matches), random
+    KFS_REPLAY_SKIP_ROWS flags, gray or R,G,B frames, optional masks.  A host model of the cache gives the oracle its keyframes."""
+    from _track_util import make_rgb
+    rng = np.random.default_rng(seed)
+    stats = dict(cases=0, submits=0, frames=0, knn_rows=0, survivors=0)
+    for c in range(ncases):
+        w, h = int(rng.integers(120, 420)), int(rng.integers(100, 320))
+        nf = int(rng.choice([200, 500, 900]))
+        mb = int(rng.integers(2, 9))
+        slots = int(rng.integers(1, 4))
+        ratio = float(rng.choice([0.6, 0.75]))
+        arenas = int(rng.choice([0, 2, 3, 4]))
+        rgb = rng.random() < 0.3
+        use_mask = rng.random() < 0.3
+        rp = kfs.Replay(nfeatures=nf, max_batch=mb, keyframe_slots=slots, ratio=ratio, arenas=arenas)
+        P = oracle.orb_params(nfeatures=nf)
+        tag = "replay case %d: %dx%d nf=%d max_batch=%d slots=%d ratio=%.2f arenas=%d rgb=%s mask=%s" % (c, w, h, nf, mb, slots, ratio, arenas, rgb, use_mask)
+        cache = [None] * slots                       # host model: descriptors a slot holds
+        pending = []
+        nsub = int(rng.integers(2, 6))
+        for s_ in range(nsub):
+            B = int(rng.integers(1, mb + 1))
+            s0 = int(rng.integers(1 << 20))
+            if rgb:
+                frames = np.ascontiguousarray(np.stack([make_rgb(h, w, s0, shift=2 * i) for i in range(B)]))
+                grays = [oracle.rgb2gray(f) for f in frames]
+            else:
+                frames = np.ascontiguousarray(synth.make_stream(B, h, w, seed=s0, pad=8))
+                grays = list(frames)
+            masks = None
+            if use_mask:
+                masks = np.zeros((B, h, w), np.uint8)
+                masks[:, h // 10:h - h // 7, w // 9:w - w // 8] = 255
+            ref = [oracle.detect_and_compute(grays[i], masks[i] if use_mask else None, P) for i in range(B)]
+            plan, kf_desc = [], []
+            for i in range(B):
+                choices = ["none"] + (["batch"] if i > 0 else []) + (["cache"] if any(x is not None for x in cache) else [])
+                pick = str(rng.choice(choices))
+                if pick == "batch":
+                    k = int(rng.integers(0, i)); plan_k = k; q = ref[k][1]
+                elif pick == "cache":
+                    sl = int(rng.choice([j for j in range(slots) if cache[j] is not None])); plan_k = -(1 + sl); q = cache[sl]
+                else:
+                    plan_k = kfs.Replay.NO_MATCH; q = None
+                plan.append([plan_k, -1, 1 if rng.random() < 0.25 else 0])
+                kf_desc.append(q)
+            used = set()
+            for i in range(B):                          # stores take effect AFTER this submit's matching
+                if rng.random() < 0.3:
+                    sl = int(rng.integers(0, slots))
+                    if sl not in used:
+                        plan[i][1] = sl; used.add(sl)
+            out = rp.alloc_outputs(B)
+            pending.append((rp.submit(frames, [tuple(e) for e in plan], out, masks), out, ref, kf_desc, plan, B))
+            for i in range(B):
+                if plan[i][1] >= 0:
+                    cache[plan[i][1]] = ref[i][1]
+            stats["submits"] += 1
+        for t, out, ref, kf_desc, plan, B in pending:
+            assert rp.wait(t) == 0, tag
+            for i in range(B):
+                rk, rd = ref[i]
+                assert int(out["n_kp"][i]) == len(rk), tag
+                if not plan[i][2]:                      # rows of a SKIP_ROWS frame stay on the device
+                    assert np.array_equal(out["kp"][i, :len(rk)], rk) and np.array_equal(out["desc"][i, :len(rk)], rd), tag
+                q = kf_desc[i]
+                if q is None:
+                    assert out["n_query"][i] == 0 and out["n_good"][i] == 0, tag
+                    continue
+                rm, rc = oracle.knn_match(q, rd, 2)
+                assert out["n_query"][i] == len(q), tag
+                kk = min(2, len(rd))
+                if len(q) and kk:
+                    assert np.array_equal(out["knn"][i, :len(q)]["trainIdx"][:, :kk], rm["trainIdx"][:, :kk]), tag
+                    assert np.array_equal(out["knn"][i, :len(q)]["distance"][:, :kk], rm["distance"][:, :kk]), tag
+                good = oracle.ratio_test(rm, rc, ratio)
+                assert out["n_good"][i] == len(good) and np.array_equal(out["good"][i, :len(good)], good), tag
+                stats["knn_rows"] += len(q); stats["survivors"] += len(good)
+                stats["frames"] += 1
+        rp.close()
+        stats["cases"] += 1
+        if log:
+            log(tag + " ok")
+    return stats
+
+
+def test_random_replay_plans(oracle):
+    import kfslam_b200 as kfs
+    n = int(os.environ.get("KFS_FUZZ_REPLAY_CASES", "8"))
+    stats = run_replay_cases(kfs, oracle, n)
+    print("\n[fuzz replay] %s" % stats)
+    assert stats["cases"] == n and stats["knn_rows"] > 0

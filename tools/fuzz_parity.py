@@ -28,3 +28,8 @@ if len(sys.argv) > 4:   # fourth argument: number of random tracker sequences (k
     ts = F.run_track_cases(kfs, O, int(sys.argv[4]), seed=seed + 1, log=lambda s: print(s, flush=True))
     print("fuzz track (seed %d): %d sequences, %d frames, %d ratio-test survivors with back-projected points, %d window pairs bit-exact against the oracle; %.0f s"
           % (seed + 1, ts["cases"], ts["frames"], ts["matches"], ts["window_pairs"], time.time() - t0))
+if len(sys.argv) > 5:   # fifth argument: number of random replay-executor cases (plans, cache slots, skip flags, arenas)
+    t0 = time.time()
+    rs = F.run_replay_cases(kfs, O, int(sys.argv[5]), seed=seed + 2, log=lambda s: print(s, flush=True))
+    print("fuzz replay (seed %d): %d cases, %d submits, %d matched frames, %d kNN rows, %d ratio-test survivors bit-exact against the oracle; %.0f s"
+          % (seed + 2, rs["cases"], rs["submits"], rs["frames"], rs["knn_rows"], rs["survivors"], time.time() - t0))
