@@ -110,3 +110,20 @@ def test_chunked_host_pipeline_equals_unchunked(kfs, oracle, chunk):
         for f in range(B):
             rk, rd = oracle.detect_and_compute(frames[f], masks[f] if use_mask else None, P)
             assert np.array_equal(kps[f], rk) and np.array_equal(descs[f], rd), (chunk, use_mask, f)
+
+
+def test_tapered_chunk_schedule_of_large_batches(kfs, oracle):
+    """Batches of 32 frames and more take the tapered automatic schedule (three quarter-size chunks, then 1/8, 1/16, 1/16 of the
+    batch): same rows as the oracle for every frame, with and without masks, for a batch that the taper divides unevenly."""
+    nf = 200
+    P = oracle.orb_params(nfeatures=nf)
+    orb = kfs.ORB_create(nf)
+    for B in (32, 45):
+        frames = np.ascontiguousarray(synth.make_stream(B, 120, 173, seed=60 + B, pad=8))
+        masks = np.zeros_like(frames)
+        masks[:, 10:100, 20:160] = 255
+        for use_mask in (False, True):
+            kps, descs = orb.detectAndComputeBatch(frames, masks if use_mask else None)
+            for f in range(B):
+                rk, rd = oracle.detect_and_compute(frames[f], masks[f] if use_mask else None, P)
+                assert np.array_equal(kps[f], rk) and np.array_equal(descs[f], rd), (B, use_mask, f)
