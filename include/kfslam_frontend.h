@@ -22,7 +22,8 @@
  *
  * Environment switches (read when a handle is created or first sized; results are identical for every
  * setting, they select mechanisms for A/B measurements — DESIGN.md section 4): KFS_ORB_GRAPHS,
- * KFS_ORB_TMA, KFS_ORB_FUSED_PYRAMID, KFS_ORB_FAST_HALF, KFS_ORB_PDL, KFS_ORB_DESCRIBE2 (0 = off), KFS_BF_SPLIT (1..16),
+ * KFS_ORB_TMA, KFS_ORB_FUSED_PYRAMID, KFS_ORB_FAST_HALF, KFS_ORB_PDL, KFS_ORB_DESCRIBE2, KFS_ORB_RESIZE_TMA (0 = off),
+ * KFS_BF_SPLIT (1..16),
  * KFS_BF_CLUSTER (0 / 1 / 2).
  */
 #ifndef KFSLAM_FRONTEND_H

@@ -105,6 +105,10 @@ k_resize_generic(const uint8_t *__restrict__ src, long long sfs, int spitch, int
 // Table per 4-pixel group (2 x uint4, built on the host): {a0, sel[4 x 8 bit: rel_a | rel_b << 4], -, -},
 // {M0..M3} with M = m0 | m1 << 16.
 constexpr int RZ_ROWS = 4;
+#ifndef KFS_RZ_YT
+#define KFS_RZ_YT 2
+#endif
+constexpr int RZ_YT = KFS_RZ_YT; // k_resize_tma: a CTA's tile is 8 * RZ_ROWS * RZ_YT output rows high
 __device__ __forceinline__ uint32_t kfs_prmt(uint32_t a, uint32_t b, uint32_t sel)
 {
     uint32_t r;
@@ -282,6 +286,77 @@ __device__ __forceinline__ int kfs_atoms_add(int *p, int v)
     int r;
     asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
     return r;
+}
+
+// k_resize_tma: k_resize's arithmetic on a source tile that ONE TMA box brings into shared memory (k_resize's top stall is
+// long_scoreboard on its 4-byte LDGs).  CTA = 128 x 32 output pixels as before; the box starts at the 16-byte aligned byte at or
+// below the first tap of the tile's first pixel group and at the top source row of the tile's first output row; its size (bw x bh,
+// host-computed from the tables, kfs_orb_plan_resize_boxes) covers every tap of every tile of every level.  Bytes outside the level
+// arrive as zeros and are never among the taps that count (the clamped second row / clamped words of k_resize).
+__global__ void __launch_bounds__(256)
+k_resize_tma(const __grid_constant__ CUtensorMap map, int frame0, int sh, uint8_t *__restrict__ dst, long long dfs, int dpitch, int dw, int dh,
+             const uint4 *__restrict__ xt, const uint32_t *__restrict__ ytab, int mask_mode, int bw, int bh)
+{
+    extern __shared__ __align__(128) uint8_t s_rt[];
+    __shared__ __align__(8) uint64_t s_bar;
+    const int tid = threadIdx.y * 32 + threadIdx.x;
+    const int gx0 = blockIdx.x * 32, yb0 = blockIdx.y * 8 * RZ_ROWS * RZ_YT;
+    const int xa0 = (int)(__ldg(xt + 2 * gx0).x) & ~15;        // CTA-uniform: first tap byte of the tile, aligned down
+    const int ya0 = (int)(__ldg(ytab + yb0) & 0xffffu);          // top source row of the tile's first output row
+    if (tid == 0) kfs_mbar_init(&s_bar, 1);
+    __syncthreads();
+    kfs_pdl_wait(); // the source level is complete from here on
+    if (tid == 0) {
+        kfs_mbar_expect_tx(&s_bar, (uint32_t)(bw * bh));
+        kfs_tma_load_3d(s_rt, &map, xa0, ya0, (int)blockIdx.z + frame0, &s_bar);
+    }
+    const int gx = gx0 + threadIdx.x;
+    constexpr int NR = RZ_ROWS * RZ_YT;                          // output rows per thread: warp w owns rows yb0 + NR * w ...
+    const int ybase = yb0 + threadIdx.y * NR;
+    const bool live = gx * 4 < dw && ybase < dh;
+    // table entries travel while the box is in flight
+    uint4 ta = make_uint4(0, 0, 0, 0), tm = ta;
+    uint32_t yt[NR] = {};
+    if (live) {
+        ta = __ldg(xt + 2 * gx); tm = __ldg(xt + 2 * gx + 1);
+#pragma unroll
+        for (int r = 0; r < NR; r++) yt[r] = __ldg(ytab + min(ybase + r, dh - 1));
+    }
+    kfs_mbar_wait(&s_bar, 0);
+    if (!live) return;
+    const uint32_t off = ta.x - (uint32_t)xa0;                   // first tap byte inside the box
+    const int shb = (int)(off & 3u) * 8;
+    const uint32_t a_t = kfs_smem_u32(s_rt) + (off & ~3u);
+    const uint32_t s0 = ta.y, s1 = ta.y >> 8, s2 = ta.y >> 16, s3 = ta.y >> 24;
+    uint32_t *df = reinterpret_cast<uint32_t *>(dst + (long long)blockIdx.z * dfs);
+    const uint32_t dpw = (uint32_t)dpitch >> 2;
+#pragma unroll
+    for (int r = 0; r < NR; r++) {
+        const int y = ybase + r;
+        if (y >= dh) break;
+        const uint32_t y0 = yt[r] & 0xffffu, y1 = min(y0 + 1u, (uint32_t)sh - 1u);
+        const uint32_t n1 = yt[r] >> 16, n0 = 256u - n1;
+        const uint32_t pa = a_t + (y0 - (uint32_t)ya0) * (uint32_t)bw, pb = a_t + (y1 - (uint32_t)ya0) * (uint32_t)bw;
+        uint32_t a0, a1, a2, b0, b1, b2;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(a0) : "r"(pa));
+        asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(a1) : "r"(pa));
+        asm volatile("ld.shared.u32 %0, [%1+8];" : "=r"(a2) : "r"(pa));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(b0) : "r"(pb));
+        asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(b1) : "r"(pb));
+        asm volatile("ld.shared.u32 %0, [%1+8];" : "=r"(b2) : "r"(pb));
+        const uint32_t lo0 = __funnelshift_r(a0, a1, shb), hi0 = __funnelshift_r(a1, a2, shb);
+        const uint32_t lo1 = __funnelshift_r(b0, b1, shb), hi1 = __funnelshift_r(b1, b2, shb);
+        const uint32_t S0 = n0 * __dp2a_lo(tm.x, kfs_prmt(lo0, hi0, s0), 0u) + (n1 * __dp2a_lo(tm.x, kfs_prmt(lo1, hi1, s0), 0u) + 32768u);
+        const uint32_t S1 = n0 * __dp2a_lo(tm.y, kfs_prmt(lo0, hi0, s1), 0u) + (n1 * __dp2a_lo(tm.y, kfs_prmt(lo1, hi1, s1), 0u) + 32768u);
+        const uint32_t S2 = n0 * __dp2a_lo(tm.z, kfs_prmt(lo0, hi0, s2), 0u) + (n1 * __dp2a_lo(tm.z, kfs_prmt(lo1, hi1, s2), 0u) + 32768u);
+        const uint32_t S3 = n0 * __dp2a_lo(tm.w, kfs_prmt(lo0, hi0, s3), 0u) + (n1 * __dp2a_lo(tm.w, kfs_prmt(lo1, hi1, s3), 0u) + 32768u);
+        uint32_t outw = kfs_prmt(kfs_prmt(S0, S1, 0x0062u), kfs_prmt(S2, S3, 0x0062u), 0x5410u);
+        if (mask_mode) { // keep only bytes == 255
+            const uint32_t t = ((outw & 0x7f7f7f7fu) + 0x01010101u) & outw & 0x80808080u;
+            outw = (t >> 7) * 255u;
+        }
+        df[(uint32_t)y * dpw + (uint32_t)gx] = outw;
+    }
 }
 
 // ======================================================================================================
@@ -1591,6 +1666,9 @@ struct kfs_orb {
     bool blur_fma = true;           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
     // TMA descriptors of the levels for k_fast (re-encoded only when a level's address / pitch / size changes)
     MapCache fmaps, fmaps_h, bmaps; // k_fast's 144 x 70 (144 x 39 for half-height tiles) boxes, k_blur7's 160 x 64 boxes
+    MapCache rmaps, rmaps_m;        // k_resize_tma's source boxes over the image / mask pyramid (map l = level l as a SOURCE)
+    int rz_bw = 0, rz_bh = 0;       // box of k_resize_tma (0: not planned / does not fit -> k_resize)
+    bool resize_tma = !(getenv("KFS_ORB_RESIZE_TMA") && atoi(getenv("KFS_ORB_RESIZE_TMA")) == 0);
     // fused pyramid (k_pyramid): host copies of the resize tables, the region plan, level-0 tensor maps of image / mask
     std::vector<uint32_t> h_xtab[KFS_MAX_LEVELS], h_ytab[KFS_MAX_LEVELS];
     bool pyr_fused = false;
@@ -1659,6 +1737,8 @@ static void kfs_orb_free_arena(kfs_orb *o)
 }
 
 static kfs_status kfs_orb_plan_pyramid(kfs_orb *o);
+static void kfs_orb_plan_resize_boxes(kfs_orb *o);
+static void kfs_orb_tma_probe(kfs_orb *o);
 
 static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_mask)
 {
@@ -1818,6 +1898,8 @@ static kfs_status kfs_orb_ensure(kfs_orb *o, int w, int h, int batch, bool need_
     if (o->h_counts) { cudaFreeHost(o->h_counts); o->h_counts = nullptr; }
     KFS_CUDA_TRY(cudaMallocHost(&o->h_counts, sizeof(int) * (size_t)batch));
     o->W = w; o->H = h; o->B = batch; o->has_mask_alloc = need_mask;
+    kfs_orb_plan_resize_boxes(o);
+    o->rmaps = MapCache(); o->rmaps_m = MapCache();
     return kfs_orb_plan_pyramid(o);
 }
 
@@ -1891,6 +1973,63 @@ static cudaError_t kfs_orb_raise_smem_limits(int device)
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
     if (e == cudaSuccess && device >= 0 && device < 64) done[device] = true;
     return e;
+}
+
+// Box of k_resize_tma: the smallest (width, height) that holds the taps of every 128 x 32 output tile of every level, read off the
+// host copies of the resize tables.  A tile's box starts at the 16-byte aligned byte at or below the first tap of its first 4-pixel
+// group and at the top source row of its first output row; k_resize's arithmetic reads three aligned words from the word that holds a
+// group's first tap, and source rows y0 and min(y0 + 1, sh - 1).
+static void kfs_orb_plan_resize_boxes(kfs_orb *o)
+{
+    o->rz_bw = o->rz_bh = 0;
+    const int L = o->nlevels_active;
+    int bw = 0, bh = 0;
+    for (int l = 1; l < L; l++) {
+        if (!o->resize_fast[l]) return; // scale factor > 2: the generic kernel
+        const std::vector<uint32_t> &xt = o->h_xtab[l], &yt = o->h_ytab[l];
+        const int ngroups = (int)xt.size() / 4, dh = o->lh[l], sh = o->lh[l - 1];
+        for (int g0 = 0; g0 < ngroups; g0 += 32) {
+            const int g1 = std::min(g0 + 31, ngroups - 1);
+            const int xa0 = (int)(xt[(size_t)4 * g0] & 0xffffu) & ~15;
+            int last = 0;
+            for (int gi = g0; gi <= g1; gi++) last = std::max(last, ((int)(xt[(size_t)4 * gi] & 0xffffu) & ~3) + 12);
+            bw = std::max(bw, last - xa0);
+        }
+        for (int y0 = 0; y0 < dh; y0 += 8 * RZ_ROWS * RZ_YT) {
+            const int y1 = std::min(y0 + 8 * RZ_ROWS * RZ_YT - 1, dh - 1);
+            const int ya0 = (int)(yt[(size_t)y0] & 0xffffu);
+            int last = 0;
+            for (int y = y0; y <= y1; y++) last = std::max(last, std::min((int)(yt[(size_t)y] & 0xffffu) + 1, sh - 1));
+            bh = std::max(bh, last - ya0 + 1);
+        }
+    }
+    bw = (int)kfs_align_up((size_t)bw, 16);
+    if (bw <= 0 || bh <= 0 || bw > 256 || bh > 256 || bw * bh > 40 * 1024) return; // TMA box limits / shared memory: stay on k_resize
+    o->rz_bw = bw; o->rz_bh = bh;
+}
+
+// Tensor maps of the pyramid levels AS SOURCES of the next level (image or mask pyramid), box = (rz_bw, rz_bh); a level whose buffer
+// cannot be described (an unaligned caller buffer as level 0) switches the TMA resize off for the handle.
+static bool kfs_orb_resize_maps(kfs_orb *o, MapCache &C, bool mask)
+{
+    kfs_orb_tma_probe(o);
+    if (o->tma_state <= 0 || o->rz_bw <= 0) return false;
+    const OrbDev &g = o->g;
+    for (int l = 0; l + 1 < g.nlevels; l++) {
+        const uint8_t *img = mask ? o->mpyr[l] : g.lv[l].img;
+        const long long fs = mask ? o->lfs[l] : g.lv[l].img_fs;
+        const int pitch = mask ? o->lpitch[l] : g.lv[l].pitch, h = o->lh[l];
+        if (C.img[l] == img && C.fs[l] == fs && C.pitch[l] == pitch && C.h[l] == h) continue;
+        const cuuint64_t dims[3] = {(cuuint64_t)pitch, (cuuint64_t)h, 65535};
+        const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)fs};
+        const cuuint32_t box[3] = {(cuuint32_t)o->rz_bw, (cuuint32_t)o->rz_bh, 1}, estr[3] = {1, 1, 1};
+        const bool ok = img && ((uintptr_t)img % 16 == 0) && (pitch % 16 == 0) && (fs % 16 == 0) &&
+                        kfs_encode_tiled()(&C.maps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)img, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+        if (!ok) { o->resize_tma = false; return false; }
+        C.img[l] = img; C.fs[l] = fs; C.pitch[l] = pitch; C.h[l] = h;
+    }
+    return true;
 }
 
 // Regions of the fused pyramid kernel (k_pyramid): tile (i, j) of the coarsest level owns, on every level l, the box between
@@ -2063,6 +2202,8 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
             KFS_LAUNCH_CHECK(o);
         }
     }
+    const bool rz_tma = !fused && o->resize_tma && kfs_orb_resize_maps(o, o->rmaps, false);
+    const bool rz_tma_m = rz_tma && has_mask && kfs_orb_resize_maps(o, o->rmaps_m, true);
     for (int l = 1; l < L && !fused; l++) {
         const long long sfs = g.lv[l - 1].img_fs;
         const uint8_t *simg = g.lv[l - 1].img + (long long)f0 * sfs;
@@ -2073,12 +2214,22 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
         const bool fast = o->resize_fast[l] && ((uintptr_t)simg % 4 == 0) && (spitch % 4 == 0) && (sfs % 4 == 0);
         if (fast) {
             const dim3 grid(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8 * RZ_ROWS), nb);
-            k_resize<<<grid, rb, 0, st>>>(simg, sfs, spitch, o->lh[l - 1], dimg, o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l],
-                                          o->xtab4[l], o->ytab[l], 0);
+            const dim3 grid_t(kfs_div_up(o->lw[l], 128), kfs_div_up(o->lh[l], 8 * RZ_ROWS * RZ_YT), nb);
+            const size_t rsm = (size_t)o->rz_bw * o->rz_bh;
+            if (rz_tma) // source tile by TMA (KFS_ORB_RESIZE_TMA=0: k_resize's LDGs)
+                k_resize_tma<<<grid_t, rb, rsm, st>>>(o->rmaps.maps.m[l - 1], f0, o->lh[l - 1], dimg, o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l],
+                                                   o->xtab4[l], o->ytab[l], 0, o->rz_bw, o->rz_bh);
+            else
+                k_resize<<<grid, rb, 0, st>>>(simg, sfs, spitch, o->lh[l - 1], dimg, o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l],
+                                              o->xtab4[l], o->ytab[l], 0);
             KFS_LAUNCH_CHECK(o);
             if (has_mask) {
-                k_resize<<<grid, rb, 0, st>>>(smask, o->lfs[l - 1], o->lpitch[l - 1], o->lh[l - 1], dmask, o->lfs[l], o->lpitch[l],
-                                              o->lw[l], o->lh[l], o->xtab4[l], o->ytab[l], 1);
+                if (rz_tma_m)
+                    k_resize_tma<<<grid_t, rb, rsm, st>>>(o->rmaps_m.maps.m[l - 1], f0, o->lh[l - 1], dmask, o->lfs[l], o->lpitch[l], o->lw[l], o->lh[l],
+                                                       o->xtab4[l], o->ytab[l], 1, o->rz_bw, o->rz_bh);
+                else
+                    k_resize<<<grid, rb, 0, st>>>(smask, o->lfs[l - 1], o->lpitch[l - 1], o->lh[l - 1], dmask, o->lfs[l], o->lpitch[l],
+                                                  o->lw[l], o->lh[l], o->xtab4[l], o->ytab[l], 1);
                 KFS_LAUNCH_CHECK(o);
             }
         } else { // scale factor > 2 (taps of a 4-pixel group span more than 8 bytes) or an unaligned caller buffer

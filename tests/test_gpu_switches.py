@@ -9,7 +9,7 @@ from _util import synth
 
 pytestmark = pytest.mark.gpu
 
-SWITCHES = ["KFS_ORB_GRAPHS", "KFS_ORB_TMA", "KFS_ORB_FUSED_PYRAMID", "KFS_ORB_FAST_HALF", "KFS_ORB_PDL", "KFS_ORB_DESCRIBE2"]
+SWITCHES = ["KFS_ORB_GRAPHS", "KFS_ORB_TMA", "KFS_ORB_FUSED_PYRAMID", "KFS_ORB_FAST_HALF", "KFS_ORB_PDL", "KFS_ORB_DESCRIBE2", "KFS_ORB_RESIZE_TMA"]
 
 
 @pytest.fixture(scope="module")
