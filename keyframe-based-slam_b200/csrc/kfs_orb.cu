@@ -1437,11 +1437,17 @@ k_describe(const __grid_constant__ OrbDev g, int kpw)
 //   pass B  rotated BRIEF of the kpw keypoints from the blurred windows (double-buffered as well; the first two fly during the end of
 //           pass A), cos / sin / centre broadcast from lane i
 // Slots: warp w of CTA b owns slots (b * DK + w) * kpw .. + kpw - 1, so a warp walks neighbouring keypoints of the (level, y, x) order.
+// TMA: each window is ONE box (48 x 31 bytes of the level, 64 x 37 of its blurred copy; x origin rounded down to 16 bytes as before, so the
+// arithmetic does not change) issued by lane 0 on a per-(warp, buffer) mbarrier, instead of 7 + 9 16-byte cp.async per lane with their
+// address arithmetic (a fifth of the kernel's instructions).  Bytes past the row pitch arrive as zeros either way.
+constexpr int IC_PAD = (IC_BYTES + 127) / 128 * 128, WB_PAD = (WB_BYTES + 127) / 128 * 128; // TMA destinations are 128-byte aligned
+template <bool TMA>
 __global__ void __launch_bounds__(32 * DK)
-k_describe2(const __grid_constant__ OrbDev g, int kpw)
+k_describe2(const __grid_constant__ OrbDev g, int kpw, const __grid_constant__ FastMaps maps_i, const __grid_constant__ FastMaps maps_b)
 {
-    __shared__ __align__(16) uint8_t s_ic[DK][2][IC_BYTES];
-    __shared__ __align__(16) uint8_t s_wb[DK][2][WB_BYTES];
+    __shared__ __align__(128) uint8_t s_ic[DK][2][IC_PAD];
+    __shared__ __align__(128) uint8_t s_wb[DK][2][WB_PAD];
+    __shared__ __align__(8) uint64_t s_dbar[DK][4]; // [un-blurred buffer 0, 1, blurred buffer 0, 1]
     kfs_pdl_wait();
     const int f = blockIdx.y + g.frame0, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int cnt = 0;
@@ -1459,6 +1465,14 @@ k_describe2(const __grid_constant__ OrbDev g, int kpw)
     if (slot0 >= nvalid) return;                      // warp-uniform; no block-level barrier below
     const int nk = min(kpw, nvalid - slot0);          // keypoints of this warp (>= 1)
     const int q = lane & 3, rq = lane >> 2;
+    if (TMA) {
+        if (lane == 0) {
+#pragma unroll
+            for (int b = 0; b < 4; b++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(kfs_smem_u32(&s_dbar[warp][b])) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
 
     // lane i < nk: its keypoint's level, list entry
     int level_l = 0;
@@ -1486,7 +1500,18 @@ k_describe2(const __grid_constant__ OrbDev g, int kpw)
             const int level = __shfl_sync(0xffffffffu, level_l, i);
             const LevelDev &L = g.lv[level];
             const int x = xy & 0xfff, y = (xy >> 12) & 0xfff;
-            if (s < nk) {
+            if (TMA) {
+                if (lane == 0) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // the buffer's last readers (generic proxy) are done
+                    if (s < nk) {
+                        kfs_mbar_expect_tx(&s_dbar[warp][i & 1], 48 * 31);
+                        kfs_tma_load_3d(s_ic[warp][i & 1], &maps_i.m[level], (x - 15) & ~15, y - 15, f, &s_dbar[warp][i & 1]);
+                    } else {
+                        kfs_mbar_expect_tx(&s_dbar[warp][2 + (i & 1)], BW_P * 37);
+                        kfs_tma_load_3d(s_wb[warp][i & 1], &maps_b.m[level], (x - 18) & ~15, y - 18, f, &s_dbar[warp][2 + (i & 1)]);
+                    }
+                }
+            } else if (s < nk) {
                 uint8_t *ic = s_ic[warp][i & 1];
                 const int ax = (x - 15) & ~15;
                 const bool in_i = ax + 16 * q + 16 <= L.pitch;
@@ -1506,7 +1531,7 @@ k_describe2(const __grid_constant__ OrbDev g, int kpw)
                     if (rq + 8 * r < 37) kfs_cp_async16_zfill(wb + (rq + 8 * r) * BW_P + 16 * q, srb + (long long)(8 * r) * L.pitch_blur, in_b);
             }
         }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
+        if (!TMA) asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
     issue(0);
     issue(1);
@@ -1515,7 +1540,8 @@ k_describe2(const __grid_constant__ OrbDev g, int kpw)
     int m10_l = 0, m01_l = 0;
 #pragma unroll 1
     for (int i = 0; i < nk; i++) {
-        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        if (TMA) kfs_mbar_wait(&s_dbar[warp][i & 1], (uint32_t)((i >> 1) & 1)); // use (i >> 1) of this buffer
+        else asm volatile("cp.async.wait_group 1;\n" ::: "memory");
         __syncwarp();
         const int x = __shfl_sync(0xffffffffu, xy_l, i) & 0xfff;
         const uint8_t *ic = s_ic[warp][i & 1];
@@ -1571,7 +1597,8 @@ k_describe2(const __grid_constant__ OrbDev g, int kpw)
     for (int h = 0; h < 8; h++) pat[h] = __ldg(reinterpret_cast<const float4 *>(d_patf) + 32 * h + lane);
 #pragma unroll 1
     for (int i = 0; i < nk; i++) {
-        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        if (TMA) kfs_mbar_wait(&s_dbar[warp][2 + (i & 1)], (uint32_t)((i >> 1) & 1)); // use (i >> 1) of this buffer
+        else asm volatile("cp.async.wait_group 1;\n" ::: "memory");
         __syncwarp();
         const int x = __shfl_sync(0xffffffffu, xy_l, i) & 0xfff;
         const float2 ab = make_float2(__shfl_sync(0xffffffffu, cs_l, i), __shfl_sync(0xffffffffu, sn_l, i));
@@ -1666,6 +1693,7 @@ struct kfs_orb {
     bool blur_fma = true;           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
     // TMA descriptors of the levels for k_fast (re-encoded only when a level's address / pitch / size changes)
     MapCache fmaps, fmaps_h, bmaps; // k_fast's 144 x 70 (144 x 39 for half-height tiles) boxes, k_blur7's 160 x 64 boxes
+    MapCache dmaps_i, dmaps_b;      // k_describe2's window boxes: 48 x 31 over the levels, 64 x 37 over their blurred copies
     MapCache rmaps, rmaps_m;        // k_resize_tma's source boxes over the image / mask pyramid (map l = level l as a SOURCE)
     int rz_bw = 0, rz_bh = 0;       // box of k_resize_tma (0: not planned / does not fit -> k_resize)
     bool resize_tma = !(getenv("KFS_ORB_RESIZE_TMA") && atoi(getenv("KFS_ORB_RESIZE_TMA")) == 0);
@@ -2146,7 +2174,7 @@ static bool kfs_orb_pyramid_map(kfs_orb *o, PyrMap *pmap, PyrMapKeyStore *key, c
 }
 
 // (Re)builds the per-level tensor maps of one kernel's tile shape (box_w x box_h bytes).  KFS_ORB_TMA=0 forces the LDG path.
-static void kfs_orb_update_maps(kfs_orb *o, MapCache &C, int box_w, int box_h)
+static void kfs_orb_update_maps(kfs_orb *o, MapCache &C, int box_w, int box_h, bool blurred = false)
 {
     kfs_orb_tma_probe(o);
     C.maps.enabled = o->tma_state > 0;
@@ -2154,16 +2182,19 @@ static void kfs_orb_update_maps(kfs_orb *o, MapCache &C, int box_w, int box_h)
     const OrbDev &g = o->g;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelDev &L = g.lv[l];
-        if (L.list_cap <= 0) continue; // no keypoint can come from this level: neither kernel has a tile on it
-        if (C.img[l] == L.img && C.fs[l] == L.img_fs && C.pitch[l] == L.pitch && C.h[l] == L.h) continue;
-        const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.h, 65535};
-        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.img_fs};
+        if (L.list_cap <= 0) continue; // no keypoint can come from this level: no kernel has a tile or a window on it
+        const uint8_t *img = blurred ? L.blur : L.img;
+        const long long fs = blurred ? L.img_fs_blur : L.img_fs;
+        const int pitch = blurred ? L.pitch_blur : L.pitch;
+        if (C.img[l] == img && C.fs[l] == fs && C.pitch[l] == pitch && C.h[l] == L.h) continue;
+        const cuuint64_t dims[3] = {(cuuint64_t)pitch, (cuuint64_t)L.h, 65535};
+        const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)fs};
         const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1}, estr[3] = {1, 1, 1};
-        const bool ok = ((uintptr_t)L.img % 16 == 0) && (L.pitch % 16 == 0) && (L.img_fs % 16 == 0) &&
-                        kfs_encode_tiled()(&C.maps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)L.img, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+        const bool ok = ((uintptr_t)img % 16 == 0) && (pitch % 16 == 0) && (fs % 16 == 0) &&
+                        kfs_encode_tiled()(&C.maps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)img, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
         if (!ok) { o->tma_state = -1; C.maps.enabled = 0; return; } // e.g. an unaligned caller buffer: stay on the LDG path for good
-        C.img[l] = L.img; C.fs[l] = L.img_fs; C.pitch[l] = L.pitch; C.h[l] = L.h;
+        C.img[l] = img; C.fs[l] = fs; C.pitch[l] = pitch; C.h[l] = L.h;
     }
 }
 
@@ -2302,7 +2333,15 @@ static kfs_status kfs_orb_run_eager(kfs_orb *o, int f0, int nb, const uint8_t *d
     }
     if (kfs_stage_mark(o, KFS_STAGE_DESCRIBE)) return KFS_ERR_CUDA;
     const int kpw = std::max(1, std::min(KPW, nb));
-    if (o->describe2) kfs_launch_pdl(pdl, k_describe2, dim3(kfs_div_up(g.cap_out, DK * kpw), nb), dim3(32 * DK), 0, st, g, kpw);
+    if (o->describe2) {
+        // windows by TMA when both tensor-map sets exist (KFS_ORB_TMA=0 or an undescribable buffer: the cp.async instantiation)
+        kfs_orb_update_maps(o, o->dmaps_i, 48, 31);
+        kfs_orb_update_maps(o, o->dmaps_b, BW_P, 37, true);
+        if (o->dmaps_i.maps.enabled && o->dmaps_b.maps.enabled)
+            kfs_launch_pdl(pdl, k_describe2<true>, dim3(kfs_div_up(g.cap_out, DK * kpw), nb), dim3(32 * DK), 0, st, g, kpw, o->dmaps_i.maps, o->dmaps_b.maps);
+        else
+            kfs_launch_pdl(pdl, k_describe2<false>, dim3(kfs_div_up(g.cap_out, DK * kpw), nb), dim3(32 * DK), 0, st, g, kpw, o->dmaps_i.maps, o->dmaps_b.maps);
+    }
     else kfs_launch_pdl(pdl, k_describe, dim3(kfs_div_up(g.cap_out, DK * kpw), nb), dim3(32 * DK), 0, st, g, kpw);
     KFS_LAUNCH_CHECK(o);
     if (kfs_stage_mark(o, KFS_STAGE_COUNT)) return KFS_ERR_CUDA;
