@@ -1592,33 +1592,39 @@ k_describe2(const __grid_constant__ OrbDev g, int kpw, const __grid_constant__ F
     __syncwarp();
 
     // ---- pass B: rotated BRIEF (a1.10).  This lane's 8 sample pairs (pair 32h + lane) serve all nk keypoints.
-    float4 pat[8];
+    // Packed fp32x2: a sample (x, y) rides in one register pair; (x a, y b) and (x b, y a) are two mul.rn.f32x2, X = x a - y b and
+    // Y = x b + y a two scalar adds ACROSS the halves (nothing a contraction could fuse), and the two magic adds one add.rn.f32x2:
+    // 5 operations per sample instead of 8, every one the same IEEE operation on the same operands as kfs_brief_rot.
+    ulonglong2 pat[8];
 #pragma unroll
-    for (int h = 0; h < 8; h++) pat[h] = __ldg(reinterpret_cast<const float4 *>(d_patf) + 32 * h + lane);
+    for (int h = 0; h < 8; h++) pat[h] = __ldg(reinterpret_cast<const ulonglong2 *>(d_patf) + 32 * h + lane);
 #pragma unroll 1
     for (int i = 0; i < nk; i++) {
         if (TMA) kfs_mbar_wait(&s_dbar[warp][2 + (i & 1)], (uint32_t)((i >> 1) & 1)); // use (i >> 1) of this buffer
         else asm volatile("cp.async.wait_group 1;\n" ::: "memory");
         __syncwarp();
         const int x = __shfl_sync(0xffffffffu, xy_l, i) & 0xfff;
-        const float2 ab = make_float2(__shfl_sync(0xffffffffu, cs_l, i), __shfl_sync(0xffffffffu, sn_l, i));
+        const float ca = __shfl_sync(0xffffffffu, cs_l, i), sb = __shfl_sync(0xffffffffu, sn_l, i);
+        const kfs_f2 AB = kfs_pk2(ca, sb), BA = kfs_pk2(sb, ca);
         const uint8_t *wb = s_wb[warp][i & 1];
         // see k_describe: the magic-add constants carry the window origin and the shared-memory address of wb
         const int shb = (x - 18) & 15;
         const int cx = 18 + shb + (int)__cvta_generic_to_shared(wb);
-        const float mx = 12582912.f + (float)(cx & ~1), my = 12582912.f + 18.f;
+        const kfs_f2 M = kfs_pk2(12582912.f + (float)(cx & ~1), 12582912.f + 18.f);
         const uint32_t kfold = 0x4B400000u * 65u - (uint32_t)(cx & 1);
         uint32_t word = 0;
+        auto sample = [&](kfs_f2 p) -> uint32_t { // shared-memory address of the rotated, rounded sample
+            float xa, yb, xb, ya;
+            kfs_unpk2(kfs_mul2(p, AB), xa, yb);
+            kfs_unpk2(kfs_mul2(p, BA), xb, ya);
+            const kfs_f2 r = kfs_add2(kfs_pk2(__fsub_rn(xa, yb), __fadd_rn(xb, ya)), M);
+            return (uint32_t)(r >> 32) * 64u + (uint32_t)r - kfold;
+        };
 #pragma unroll
         for (int h = 0; h < 8; h++) {
-            const float4 pt = pat[h];
-            const uint32_t bx0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.x, ab.x), __fmul_rn(pt.y, ab.y)), mx));
-            const uint32_t by0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.x, ab.y), __fmul_rn(pt.y, ab.x)), my));
-            const uint32_t bx1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.z, ab.x), __fmul_rn(pt.w, ab.y)), mx));
-            const uint32_t by1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.z, ab.y), __fmul_rn(pt.w, ab.x)), my));
             uint32_t v0, v1;
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v0) : "r"(by0 * 64u + bx0 - kfold));
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v1) : "r"(by1 * 64u + bx1 - kfold));
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v0) : "r"(sample(pat[h].x)));
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v1) : "r"(sample(pat[h].y)));
             const uint32_t b = __ballot_sync(0xffffffffu, v0 < v1);
             if (lane == h) word = b;
         }
