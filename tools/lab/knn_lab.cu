@@ -221,6 +221,8 @@ int main(int argc, char **argv)
     RUN(25, 0, 4, 8, 256, 512, 2);
     RUN(24, 0, 4, 8, 256, 512, 2);
     RUN(26, 0, 4, 8, 256, 512, 2);
+    RUN(26, 2, 4, 8, 256, 1024, 2);
+    RUN(26, 2, 4, 8, 256, 256, 2);
     RUN(26, 2, 4, 8, 256, 512, 1);
     RUN(26, 2, 4, 8, 256, 512, 2);
     RUN(26, 2, 3, 8, 256, 512, 2);
