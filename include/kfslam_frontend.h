@@ -214,6 +214,38 @@ KFS_API void *kfs_bf_get_stream(kfs_bf *bf);
 KFS_API kfs_status kfs_bf_sync(kfs_bf *bf);
 KFS_API int kfs_bf_last_launches(const kfs_bf *bf);
 
+/* Matching for callers that must not allocate.  (No counterpart in the reference: cv::BFMatcher allocates freely; this entry
+ * point exists for the hosts described below.)
+ *
+ * Every other matcher call goes through a kfs_bf handle, and a handle grows device buffers with cudaMalloc whenever a call is
+ * larger than the last one (pair table, staging, the scratch of split launches).  Some hosts cannot live with that:
+ *   - a tracker thread with a per-frame deadline that shares the GPU with a mapping / bundle-adjustment thread: cudaMalloc and
+ *     cudaFree serialise against all work on the device, so one growing buffer stalls both threads in the middle of a frame;
+ *   - a process whose HBM was handed, whole, to another allocator at start-up (a framework's caching pool, a fixed robotics
+ *     memory budget): the driver has nothing left to give, cudaMalloc fails, and the descriptors the caller wants matched
+ *     already sit in memory from that pool;
+ *   - code that is handed a stream and device pointers by its own caller and may not create CUDA objects of its own.
+ * For them this call takes no handle and creates nothing — no cudaMalloc / cudaFree / cudaMallocHost, no stream, no event.  The
+ * caller passes one (query, train) problem in device memory and the result rows in device memory; the scratch of the split
+ * launch (partial top-2 lists, arrival counters, the kernel's pair table) is a fixed array compiled into the library,
+ * about 2 MiB, which every GPU that loads the library holds until the process exits.
+ *
+ * Limits and rules:
+ *   - nq <= KFS_BF_STATIC_MAX_QUERIES (the array is sized for that many query rows; more -> KFS_ERR_INVALID_ARG with a
+ *     message naming the limit — split the query rows over several calls, each is independent); nt < 2^18; k = 1 or 2;
+ *     all pointers 16-byte aligned device pointers; d_counts may be NULL.
+ *   - Results are those of kfs_bf_knn_match_pairs_device for the same rows, bit for bit (same kernel, same tie rule).
+ *   - Asynchronous on `cuda_stream` (NULL = the default stream): synchronise that stream before reading d_out.
+ *   - There is ONE array per GPU, shared by every caller in the process, and it keeps what the previous call left in it (the
+ *     call clears what has to start at zero itself).  Two calls whose kernels can overlap on the GPU — different streams
+ *     without an ordering between them, or two host threads — race on it and produce garbage.  Keep all calls for one
+ *     device on one stream, or order them with events.
+ *   - The first call for a device looks up the array's device address (and the device's SM count) and remembers them; make
+ *     that first call during start-up, outside any stream capture.  Later calls only launch two kernels. */
+#define KFS_BF_STATIC_MAX_QUERIES 16384
+KFS_API kfs_status kfs_bf_knn_match_device_static(int device, void *cuda_stream, const uint8_t *d_query, int nq,
+                                                  const uint8_t *d_train, int nt, int k, kfs_dmatch *d_out, int *d_counts);
+
 /* ---- Replay executor: the tracker's per-frame loop on batches of frames ------------------------------
  * Replaces the body of VisualOdometry::Track (VisualOdometry.cpp:129-172) up to the PnP call: ExtractFeatures
  * (:138 -> detectAndCompute :30), MatchFeatures against the last keyframe (:144 -> knnMatch :39, query = keyframe

@@ -8,4 +8,4 @@ and the synthetic frame source (synth).  Import as
 """
 from . import _native, replay, synth  # noqa: F401
 from ._native import KP_DTYPE, DM_DTYPE, NORM_HAMMING, ORB_HARRIS_SCORE, KfsError, build, lib  # noqa: F401
-from .frontend import ORB, ORB_create, BFMatcher, BFMatcher_create, Replay, TrackerFrontEnd, pipe_peak  # noqa: F401
+from .frontend import ORB, ORB_create, BFMatcher, BFMatcher_create, Replay, TrackerFrontEnd, pipe_peak, knn_match_device_static, STATIC_MAX_QUERIES  # noqa: F401

@@ -95,6 +95,7 @@ SIGNATURES = {
     "kfs_bf_last_launches": (_i, [_vp]),
     "kfs_bf_attach_orb": (_i, [_vp, _vp]),
     "kfs_bf_last_aliased": (_i, [_vp]),
+    "kfs_bf_knn_match_device_static": (_i, [_i, _vp, _vp, _i, _vp, _i, _i, _vp, _vp]),
     "kfs_replay_default_params": (None, [C.POINTER(ReplayParams)]),
     "kfs_replay_create": (_i, [C.POINTER(ReplayParams), _i, C.POINTER(_vp)]),
     "kfs_replay_destroy": (None, [_vp]),

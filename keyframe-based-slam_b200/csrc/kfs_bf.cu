@@ -18,6 +18,7 @@
 #include <vector>
 #include <unordered_map>
 #include <new>
+#include <mutex>
 
 constexpr int BF_THREADS = 256;
 constexpr int BF_QPT = 4;                       // queries per thread
@@ -738,3 +739,109 @@ kfs_status kfs_bf_knn_match_ratio(kfs_bf *b, const uint8_t *query, int nq, const
 }
 
 } // extern "C"
+
+// ---- matching without any allocation -----------------------------------------------------------------
+// kfs_bf_knn_match_device_static: the split-train launch of k_hamming_knn2<false> (the variant whose partial top-2 lists meet
+// in global scratch) for a caller that has device memory of its own but may not ask the driver for more.  Nothing of the
+// reference corresponds to this entry point; see include/kfslam_frontend.h for who needs it and why.
+//
+// Everything the launch needs beyond the caller's descriptors and result rows lives in ONE file-scope device array:
+//   [0, BF_ST_OFF_COUNTERS)                 partial lists, [tile][split][BF_QTILE] uint2           (2 MiB)
+//   [BF_ST_OFF_COUNTERS, BF_ST_OFF_PAIR)    one arrival counter per query tile                      (512 B)
+//   [BF_ST_OFF_PAIR, BF_ST_BYTES)           the one-entry pair table the kernel reads its pointers from
+// The array is part of the module image: each GPU that loads the library carries these ~2 MiB until the process exits.
+constexpr int BF_ST_MAX_NQ = KFS_BF_STATIC_MAX_QUERIES;
+constexpr int BF_ST_TILES = BF_ST_MAX_NQ / BF_QTILE;
+constexpr size_t BF_ST_OFF_COUNTERS = (size_t)BF_ST_TILES * BF_MAX_SPLIT * BF_QTILE * sizeof(uint2);
+constexpr size_t BF_ST_OFF_PAIR = BF_ST_OFF_COUNTERS + (size_t)BF_ST_TILES * sizeof(int);
+constexpr size_t BF_ST_BYTES = BF_ST_OFF_PAIR + 256;
+static_assert(BF_ST_MAX_NQ % BF_QTILE == 0, "the query limit is a whole number of tiles");
+static_assert(BF_ST_OFF_COUNTERS % 256 == 0 && BF_ST_OFF_PAIR % 256 == 0 && sizeof(BfPairDev) <= 256, "sections stay 256-byte aligned");
+static __device__ __align__(256) unsigned char g_bf_static_scratch[BF_ST_BYTES];
+
+// Stream-ordered preparation of a call, in front of the matching kernel: writes the pair table entry from kernel arguments
+// (no host-to-device copy, so no staging buffer either) and zeroes the counters this call's tiles will use.  The matching
+// kernel leaves its counters at zero, but the array outlives every call and every caller: a launch that was torn down
+// half-way (device reset of another context user, a sticky error) must not poison the next one.  Device code may name the
+// array directly; only the host needs cudaGetSymbolAddress.
+__global__ void __launch_bounds__(128) k_bf_static_prepare(BfPairDev p, int tiles)
+{
+    if (threadIdx.x == 0) *reinterpret_cast<BfPairDev *>(g_bf_static_scratch + BF_ST_OFF_PAIR) = p;
+    int *c = reinterpret_cast<int *>(g_bf_static_scratch + BF_ST_OFF_COUNTERS);
+    for (int i = threadIdx.x; i < tiles; i += blockDim.x) c[i] = 0;
+}
+
+// Per-device facts the entry point needs, resolved on the first call for that device (with that device current).  In host
+// code `g_bf_static_scratch` is only a handle for the runtime's symbol table, not an address a kernel could use.
+constexpr int BF_ST_MAX_DEVICES = 64;
+struct BfStaticDevice { unsigned char *base; int sm_count; };
+static BfStaticDevice g_bf_static_dev[BF_ST_MAX_DEVICES]; // zero-initialised; base != nullptr = resolved
+static std::mutex g_bf_static_mu;
+
+static kfs_status bf_static_device(int device, BfStaticDevice *out)
+{
+    std::lock_guard<std::mutex> lk(g_bf_static_mu);
+    BfStaticDevice &d = g_bf_static_dev[device];
+    if (!d.base) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_bf_static_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            KFS_FAIL(KFS_ERR_CUDA, "kfs_bf_knn_match_device_static: cudaGetSymbolAddress on device %d: %s", device, cudaGetErrorString(e));
+        }
+        int sms = 0;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (e != cudaSuccess) { cudaGetLastError(); KFS_FAIL(KFS_ERR_CUDA, "kfs_bf_knn_match_device_static: SM count of device %d: %s", device, cudaGetErrorString(e)); }
+        d.sm_count = sms;
+        d.base = static_cast<unsigned char *>(p);
+    }
+    *out = d;
+    return KFS_OK;
+}
+
+extern "C" kfs_status kfs_bf_knn_match_device_static(int device, void *cuda_stream, const uint8_t *d_query, int nq, const uint8_t *d_train, int nt,
+                                                     int k, kfs_dmatch *d_out, int *d_counts)
+{
+    if (k != 1 && k != 2) KFS_FAIL(KFS_ERR_UNSUPPORTED, "knnMatch: only k = 1 or 2 is built (the reference uses k = 2)");
+    if (nq < 0 || nt < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_bf_knn_match_device_static: negative row count");
+    if (nq > BF_ST_MAX_NQ)
+        KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_bf_knn_match_device_static: %d query rows exceed KFS_BF_STATIC_MAX_QUERIES = %d, the size the built-in "
+                                      "scratch was compiled for; split the query rows over several calls or use kfs_bf_knn_match_pairs_device", nq, BF_ST_MAX_NQ);
+    if (nt >= (1 << 18)) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_bf_knn_match_device_static: train rows %d >= 2^18 (OpenCV's IMGIDX_ONE limit)", nt);
+    if (nq > 0 && (!d_query || !d_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_bf_knn_match_device_static: query/out is NULL");
+    if (nq > 0 && nt > 0 && !d_train) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_bf_knn_match_device_static: train is NULL");
+    if (((uintptr_t)d_query | (uintptr_t)d_train | (uintptr_t)d_out) & 15)
+        KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_bf_knn_match_device_static: device pointers must be 16-byte aligned");
+    const int ndev = kfs_device_count();
+    if (ndev == 0) KFS_FAIL(KFS_ERR_NO_DEVICE, "no CUDA device visible; this library has no CPU path");
+    if (device < 0 || device >= ndev || device >= BF_ST_MAX_DEVICES) KFS_FAIL(KFS_ERR_INVALID_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    if (nq == 0) return KFS_OK;
+    KFS_DEVICE_GUARD(device);
+    BfStaticDevice dev;
+    kfs_status s = bf_static_device(device, &dev);
+    if (s) return s;
+
+    // same split rule as the handle's launches (bf_choose_split), without a handle: a single pair never has enough query tiles
+    // to fill the SMs on its own, so its train rows are dealt to S CTAs per tile in whole 128-row granules
+    const int tiles = kfs_div_up(nq, BF_QTILE);
+    const int nchunks = kfs_div_up(nt > 0 ? nt : 1, BF_GRAN);
+    const int want = 4 * (dev.sm_count > 0 ? dev.sm_count : 148);
+    int S = tiles >= want ? 1 : kfs_div_up(want, tiles);
+    if (S > BF_MAX_SPLIT) S = BF_MAX_SPLIT;
+    if (S > nchunks) S = nchunks;
+    if (S < 1) S = 1;
+    S = kfs_div_up(nchunks, kfs_div_up(nchunks, S));
+
+    BfPairDev p;
+    p.query = d_query; p.train = d_train; p.d_nq = nullptr; p.d_nt = nullptr; p.out = d_out; p.counts = d_counts; p.nq = nq; p.nt = nt;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    k_bf_static_prepare<<<1, 128, 0, st>>>(p, tiles);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_bf_static_prepare launch: %s", cudaGetErrorString(e));
+    k_hamming_knn2<false><<<dim3(tiles, 1, S), BF_THREADS, 0, st>>>(reinterpret_cast<const BfPairDev *>(dev.base + BF_ST_OFF_PAIR), k,
+                                                                     reinterpret_cast<uint2 *>(dev.base),
+                                                                     reinterpret_cast<int *>(dev.base + BF_ST_OFF_COUNTERS));
+    e = cudaGetLastError();
+    if (e != cudaSuccess) KFS_FAIL(KFS_ERR_CUDA, "k_hamming_knn2 (static scratch) launch: %s", cudaGetErrorString(e));
+    return KFS_OK;
+}

@@ -252,6 +252,17 @@ def BFMatcher_create(normType=NORM_HAMMING, crossCheck=False, device=0):
     return BFMatcher(normType, crossCheck, device)
 
 
+def knn_match_device_static(query_ptr, nq, train_ptr, nt, out_ptr, counts_ptr=None, k=2, device=0, stream=None):
+    """kfs_bf_knn_match_device_static: one (query, train) problem in DEVICE memory, matched without creating a handle and
+    without any allocation (the split launch's scratch is a ~2 MiB array compiled into the library).  For hosts that may not
+    call cudaMalloc while they run; see include/kfslam_frontend.h for the rules (nq <= STATIC_MAX_QUERIES, one call at a time
+    per GPU, asynchronous on `stream`).  No counterpart in the reference."""
+    N.check(N.lib().kfs_bf_knn_match_device_static(device, stream, query_ptr, nq, train_ptr, nt, k, out_ptr, counts_ptr))
+
+
+STATIC_MAX_QUERIES = 16384   # KFS_BF_STATIC_MAX_QUERIES
+
+
 def pipe_peak(device=0, what="popc"):
     """Measured integer-pipe issue rate in 1e9 ops/s (what = 'popc' | 'lop3'); matcher roofline denominator."""
     g = C.c_double()
