@@ -102,7 +102,11 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
     if (P.d_nq) nq = min(nq, *P.d_nq);
     if (P.d_nt) nt = min(nt, *P.d_nt);
     const int q0 = blockIdx.x * BF_QTILE;
-    if (q0 >= nq) return;
+    if (q0 >= nq) return; // uniform over a cluster: its CTAs differ in blockIdx.z only
+    // A CTA may touch another CTA's shared memory only once that CTA is known to have started; being launched as one cluster is
+    // not that guarantee.  Every CTA announces itself here and waits for the others just before the remote store below, so a CTA
+    // with few or no train rows cannot run ahead of rank 0's start, and nobody waits while there is scanning to do.
+    if (CLUSTER) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int qgroup = warp % BF_QWARPS, tsplit = warp / BF_QWARPS;
 
@@ -229,6 +233,7 @@ k_hamming_knn2(const BfPairDev *__restrict__ pairs, int k, uint2 *__restrict__ s
     if (CLUSTER) {
         // blockIdx.z is the rank inside the (1, 1, S) cluster.  Rank 0's s_bf_part is written by nobody but this exchange, so the
         // faster CTAs do not wait for it to finish its own rows; the barrier (release / acquire) publishes the remote stores.
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory"); // pairs with the arrive at kernel entry: rank 0 is running
         if (tid < BF_QTILE) {
             const uint32_t mine = (uint32_t)__cvta_generic_to_shared(&s_bf_part[split * BF_QTILE + tid]);
             uint32_t dst;

@@ -97,3 +97,46 @@ def test_knn_split_and_cluster_merge_do_not_change_results(kfs, nq, nt):
             assert np.array_equal(m1["trainIdx"], rm["trainIdx"][:130]) and np.array_equal(m1["distance"], rm["distance"][:130])
             r2, _ = O.knn_match(q, t[:129], 2)
             assert np.array_equal(pairs[2][0]["trainIdx"], r2["trainIdx"]) and np.array_equal(pairs[2][0]["distance"], r2["distance"])
+
+
+@pytest.mark.parametrize("live_nt", [0, 1, 3, 130, 2047])
+def test_knn_cluster_splits_with_tiny_device_side_train_count(kfs, live_nt):
+    """the launch is sized from the host-side capacity (2048 train rows -> 16 splits), the kernel clamps to the device-side
+    count, so with few live rows most CTAs of a cluster have NO train rows and reach the exchange through rank 0's shared memory
+    right after they start.  Rows must still be the oracle's, for the cluster merge and the global one."""
+    import torch
+    from oracle import oracle as O
+    N = kfs._native
+    nq, cap = 300, 2048
+    q = synth.random_descriptors(nq, seed=77)
+    t = synth.random_descriptors(cap, seed=78)
+    dev = torch.device("cuda:0")
+    dq, dt = torch.from_numpy(q).to(dev), torch.from_numpy(t).to(dev)
+    dn = torch.tensor([live_nt], dtype=torch.int32, device=dev)
+    out = torch.zeros(nq * 2 * 16, dtype=torch.uint8, device=dev)
+    cnt = torch.zeros(nq, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    rm, rc = O.knn_match(q, t[:live_nt], 2)
+    for cluster in ("2", "1", "0"):
+        saved = {k: os.environ.get(k) for k in ("KFS_BF_CLUSTER", "KFS_BF_SPLIT")}
+        os.environ.update({"KFS_BF_CLUSTER": cluster, "KFS_BF_SPLIT": "16"})
+        try:
+            bf = kfs.BFMatcher_create(kfs.NORM_HAMMING)
+        finally:
+            for k, v in saved.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
+        for _ in range(3):
+            out.zero_(); cnt.fill_(-1)
+            torch.cuda.synchronize()
+            bf.knnMatchPairsDevice([dict(query=dq.data_ptr(), nq=nq, train=dt.data_ptr(), nt=cap, d_nt=dn.data_ptr(), out=out.data_ptr(),
+                                         counts=cnt.data_ptr())], 2)
+            bf.sync()
+            m = out.cpu().numpy().view(N.DM_DTYPE).reshape(nq, 2)
+            assert np.array_equal(cnt.cpu().numpy(), rc), cluster
+            live = np.arange(2)[None, :] < rc[:, None]      # row q holds rc[q] = min(2, live_nt) entries; the tail is {q, -1, -1, FLT_MAX}
+            assert np.array_equal(m["trainIdx"][live], rm["trainIdx"][live]) and np.array_equal(m["distance"][live], rm["distance"][live]), cluster
+            assert (m["trainIdx"][~live] == -1).all() and (m["queryIdx"] == np.arange(nq)[:, None]).all(), cluster
+        bf.close()
