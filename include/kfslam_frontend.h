@@ -203,8 +203,9 @@ KFS_API kfs_status kfs_bf_knn_match_ratio(kfs_bf *bf, const uint8_t *query, int 
 /* Descriptor rows that kfs_orb_detect_and_compute[_batch] of `orb` just wrote to host memory are still on the device.  A matcher
  * attached to that extractor matches such rows where they are instead of uploading them again: a query / train pointer of
  * kfs_bf_knn_match[_pairs] is recognised when it is row 0 of a frame of that extractor's LAST host-buffer call's desc_out and
- * its row count does not exceed that frame's keypoints (the tracker's knnMatch(keyframe, dpCurrImg): the train side,
- * VisualOdometry.cpp:39).  The caller promises not to have modified those host rows in between; any other pointer is uploaded
+ * its row count EQUALS that frame's keypoint count (the tracker's knnMatch(keyframe, dpCurrImg): the train side,
+ * VisualOdometry.cpp:39) and its first and last row still hold the delivered bytes (checked: a buffer reallocated at the same
+ * address or filtered in place is uploaded).  Rows in between are the caller's promise; any other pointer is uploaded
  * as before.  orb == NULL detaches; the extractor must outlive the attachment and live on the same device.
  * kfs_bf_last_aliased: descriptor matrices of the last host-buffer call that were matched in place. */
 KFS_API kfs_status kfs_bf_attach_orb(kfs_bf *bf, kfs_orb *orb);

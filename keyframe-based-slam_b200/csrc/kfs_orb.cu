@@ -212,7 +212,7 @@ static_assert(FAST_MAXOUT * 4 <= FS_P * FS_H, "survivor list aliases the source 
 
 // ---- TMA (cp.async.bulk.tensor) staging of the source tile ------------------------------------------------------
 // One 3-D tensor map per level over [frame][row][byte] (u8, row pitch and frame stride in bytes, both multiples of 16);
-// a tile is one box of FS_P x FS_H x 1 bytes landing densely in shared memory (rows FS_P = 144 B apart); bytes outside the
+// a tile is one box of FS_P x FS_H x 1 bytes landing densely in shared memory (rows FS_P = 160 B apart); bytes outside the
 // level arrive as zeros (they only feed scores the border filter drops).  One thread arms an mbarrier with the box size
 // and issues the copy; every thread waits on the barrier's phase 0.
 struct FastMaps {
@@ -1698,7 +1698,7 @@ struct kfs_orb {
     bool use_graphs = true;
     bool blur_fma = true;           // a1.9: OpenCV's default (FMA) dispatch of sepFilter2D; false = its plain mul + add build
     // TMA descriptors of the levels for k_fast (re-encoded only when a level's address / pitch / size changes)
-    MapCache fmaps, fmaps_h, bmaps; // k_fast's 144 x 70 (144 x 39 for half-height tiles) boxes, k_blur7's 160 x 64 boxes
+    MapCache fmaps, fmaps_h, bmaps; // k_fast's 160 x 70 (160 x 39 for half-height tiles) boxes, k_blur7's 160 x 64 boxes
     MapCache dmaps_i, dmaps_b;      // k_describe2's window boxes: 48 x 31 over the levels, 64 x 37 over their blurred copies
     MapCache rmaps, rmaps_m;        // k_resize_tma's source boxes over the image / mask pyramid (map l = level l as a SOURCE)
     int rz_bw = 0, rz_bh = 0;       // box of k_resize_tma (0: not planned / does not fit -> k_resize)
@@ -1729,6 +1729,7 @@ struct kfs_orb {
     int pipeline_chunk = 0;       // frames per chunk; 0 = auto
     bool start_fence = true;      // copy streams wait for work already queued on the compute stream (off: replay executor)
     bool alias_valid = false;     // the last host batch is complete and nothing has run since: its descriptors are still in g.desc
+    std::vector<uint8_t> alias_sig; // per frame of the last host batch: its first and last live descriptor row as delivered (2 x 32 B)
     KfsHostBatch pending = {};    // the host batch in flight (enqueue -> finish)
     int pending_rows = 0;         // rows per frame its eager copies carried
     uint8_t *rgb_stage = nullptr; // colour frames of a host batch ([batch][h][align16(3w)]), converted into level 0 on the device
@@ -2777,6 +2778,15 @@ kfs_status kfs_orb_finish_host_batch(kfs_orb *o, int batch, int *n_out)
         }
     }
     if (late) KFS_CUDA_TRY(cudaStreamSynchronize(o->s_out));
+    // what an attached matcher will compare the caller's rows against before it trusts the device copy (kfs_orb_alias_desc)
+    o->alias_sig.assign((size_t)batch * 64, 0);
+    for (int f = 0; f < batch && hb.desc_out; f++) {
+        const int live = n_out[f] < cp ? n_out[f] : cp;
+        if (live <= 0 || (hb.skip_rows && hb.skip_rows[f])) continue;
+        const uint8_t *rows = hb.desc_out + (size_t)f * capacity * 32;
+        memcpy(&o->alias_sig[(size_t)f * 64], rows, 32);
+        memcpy(&o->alias_sig[(size_t)f * 64 + 32], rows + (size_t)(live - 1) * 32, 32);
+    }
     o->alias_valid = true;
     o->pending.batch = batch;
     if (rc == KFS_ERR_CAPACITY) kfs_set_error("output capacity %d too small (handle capacity %d); n_out holds the required counts", capacity, o->cap_out);
@@ -2790,9 +2800,11 @@ kfs_status kfs_orb_finish_host_batch(kfs_orb *o, int batch, int *n_out)
     return rc;
 }
 
-// Device copy of descriptor rows the last host-buffer extraction delivered to `host` (row 0 of one of its frames, at most that
-// frame's keypoint count of rows), or nullptr: lets an attached matcher (kfs_bf_attach_orb) skip the upload of rows that never
-// left the device.
+// Device copy of descriptor rows the last host-buffer extraction delivered to `host`, or nullptr: lets an attached matcher
+// (kfs_bf_attach_orb) skip the upload of rows that never left the device.  Recognised: row 0 of one of that call's frames with
+// EXACTLY that frame's keypoint count of rows (a caller that filtered or compacted the rows in place passes fewer and is uploaded),
+// whose first and last row still hold the bytes that were delivered (a buffer that was freed and reallocated at the same address, or
+// that another extractor has written since, does not).
 const uint8_t *kfs_orb_alias_desc(const kfs_orb *o, const uint8_t *host, int rows, int device)
 {
     if (!o || !o->alias_valid || !o->arena || o->device != device || !host || rows <= 0) return nullptr;
@@ -2804,7 +2816,9 @@ const uint8_t *kfs_orb_alias_desc(const kfs_orb *o, const uint8_t *host, int row
     if (f >= (size_t)hb.batch || (hb.skip_rows && hb.skip_rows[f])) return nullptr;
     const int cp = hb.capacity < o->cap_out ? hb.capacity : o->cap_out;
     const int live = o->h_counts[f] < cp ? o->h_counts[f] : cp;
-    if (rows > live) return nullptr;
+    if (rows != live || o->alias_sig.size() < (f + 1) * 64) return nullptr;
+    const uint8_t *sig = &o->alias_sig[f * 64];
+    if (memcmp(host, sig, 32) != 0 || memcmp(host + (size_t)(live - 1) * 32, sig + 32, 32) != 0) return nullptr;
     return o->g.desc + f * (size_t)o->cap_out * 32;
 }
 

@@ -167,6 +167,7 @@ struct kfs_frontend {
     // ring[head] is the newest one (Map::GetLastKeyFrame, Map.cpp:68-70)
     std::vector<KfSlot> ring;
     int window = 1, head = -1, count = 0;
+    int window_wanted = 0;         // ring size to rebuild after a failed kfs_frontend_set_capacity left the handle unsized
     // window-matching outputs: [window][cap][2] kNN rows, [window][cap] survivors, [window] counts
     kfs_dmatch *d_wknn = nullptr, *d_wgood = nullptr;
     int *d_wn = nullptr;
@@ -260,6 +261,24 @@ static KfSlot *fe_newest(kfs_frontend *fe) { return fe->count > 0 ? &fe->ring[(s
 // i-th keyframe of Map::GetNKeyFrames' order (0 = oldest held)
 static KfSlot *fe_window_slot(kfs_frontend *fe, int i) { return &fe->ring[(size_t)((fe->head - fe->count + 1 + i + 2 * fe->window) % fe->window)]; }
 
+// A kfs_frontend_set_capacity (or set_window) that ran out of device memory leaves the handle UNSIZED: no row buffers, no keyframe
+// ring, capacity 0.  Every computing entry point refuses such a handle instead of running with null device buffers; a later
+// successful kfs_frontend_set_capacity makes it usable again.
+#define KFS_FE_REQUIRE_SIZED(fe)                                                                                                    \
+    if ((fe)->cap <= 0 || (fe)->window <= 0)                                                                                        \
+    KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_frontend handle is unsized (an earlier kfs_frontend_set_capacity / set_window failed): call "   \
+                                  "kfs_frontend_set_capacity again")
+static void fe_unsize(kfs_frontend *fe)
+{
+    void **bufs[] = {(void **)&fe->d_up_desc, (void **)&fe->d_up_kp, (void **)&fe->d_knn, (void **)&fe->d_good, (void **)&fe->d_p3d, (void **)&fe->d_p2d};
+    for (void **b : bufs) if (*b) { cudaFree(*b); *b = nullptr; }
+    fe_free_ring(fe);
+    fe->window = 0;
+    fe->cap = 0;
+    fe->cur_n = -1; fe->d_cur_desc = nullptr; fe->d_cur_kp = nullptr; fe->d_cur_count = nullptr;
+    cudaGetLastError();
+}
+
 extern "C" {
 
 void kfs_frontend_destroy(kfs_frontend *fe)
@@ -319,12 +338,13 @@ kfs_status kfs_frontend_set_capacity(kfs_frontend *fe, int capacity)
     if (!fe || capacity < 1) KFS_FAIL(KFS_ERR_INVALID_ARG, "kfs_frontend_set_capacity: bad arguments");
     KFS_DEVICE_GUARD(fe->device);
     KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream));
+    const int window = fe->window > 0 ? fe->window : (fe->window_wanted > 0 ? fe->window_wanted : 1);
     kfs_status s = kfs_orb_set_capacity(fe->orb, capacity);
-    if (s) return s;
     fe->cur_n = -1; fe->d_cur_desc = nullptr; fe->d_cur_kp = nullptr; fe->d_cur_count = nullptr;
-    s = fe_alloc_rows(fe);
-    if (s) return s;
-    return fe_alloc_ring(fe, fe->window > 0 ? fe->window : 1);
+    if (!s) s = fe_alloc_rows(fe);
+    if (!s) s = fe_alloc_ring(fe, window);
+    if (s) { fe->window_wanted = window; fe_unsize(fe); return s; } // the error text of the failing step stays in kfs_last_error()
+    return KFS_OK;
 }
 int kfs_frontend_last_launches(const kfs_frontend *fe) { return fe ? fe->launches : 0; }
 
@@ -375,6 +395,7 @@ kfs_status kfs_frontend_extract_features(kfs_frontend *fe, const uint8_t *image,
                                          kfs_keypoint *kp_out, uint8_t *desc_out, int capacity, int *n_out)
 {
     if (!fe || !n_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle or n_out is NULL");
+    KFS_FE_REQUIRE_SIZED(fe);
     *n_out = 0;
     if (channels != 1 && channels != 3) KFS_FAIL(KFS_ERR_UNSUPPORTED, "ExtractFeatures: %d channels (the reference handles 1 or 3, VisualOdometry.cpp:27)", channels);
     if (w < 0 || h < 0 || capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "negative size");
@@ -405,6 +426,7 @@ static kfs_status fe_upload_depth(kfs_frontend *fe, KfSlot *k, const uint16_t *d
 kfs_status kfs_frontend_promote_keyframe(kfs_frontend *fe, const uint16_t *depth, size_t depth_step)
 {
     if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
+    KFS_FE_REQUIRE_SIZED(fe);
     if (fe->cur_n < 0 || !fe->d_cur_desc) KFS_FAIL(KFS_ERR_INVALID_ARG, "promote_keyframe: no frame has been extracted on this handle yet");
     KFS_DEVICE_GUARD(fe->device);
     KfSlot *k = fe_next_slot(fe);
@@ -425,6 +447,7 @@ kfs_status kfs_frontend_set_keyframe(kfs_frontend *fe, const uint8_t *desc, cons
                                      const uint16_t *depth, size_t depth_step, int w, int h)
 {
     if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
+    KFS_FE_REQUIRE_SIZED(fe);
     if (n < 0 || n > fe->cap) KFS_FAIL(KFS_ERR_CAPACITY, "set_keyframe: %d rows, handle capacity %d", n, fe->cap);
     if (n > 0 && (!desc || !kp)) KFS_FAIL(KFS_ERR_INVALID_ARG, "desc or kp is NULL");
     KFS_DEVICE_GUARD(fe->device);
@@ -486,6 +509,7 @@ kfs_status kfs_frontend_match_features(kfs_frontend *fe, const uint8_t *cur_desc
                                        int capacity, int *n_out)
 {
     if (!fe || !n_out || !intrinsics) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle, intrinsics or n_out is NULL");
+    KFS_FE_REQUIRE_SIZED(fe);
     *n_out = 0;
     KfSlot *kf = fe_newest(fe);
     if (!kf) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_features: no keyframe cached (promote_keyframe / set_keyframe first)");
@@ -529,6 +553,7 @@ kfs_status kfs_frontend_track(kfs_frontend *fe, const uint8_t *image, size_t ste
                               kfs_dmatch *matches_out, double *points3d_out, double *points2d_out, int match_capacity, int *n_matches_out)
 {
     if (!fe || !n_out || !n_matches_out || !intrinsics) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle, intrinsics, n_out or n_matches_out is NULL");
+    KFS_FE_REQUIRE_SIZED(fe);
     *n_out = 0; *n_matches_out = -1;
     if (capacity < 0 || match_capacity < 0) KFS_FAIL(KFS_ERR_INVALID_ARG, "negative capacity");
     if (capacity > 0 && (!kp_out || !desc_out)) KFS_FAIL(KFS_ERR_INVALID_ARG, "output buffers are NULL");
@@ -578,6 +603,7 @@ kfs_status kfs_frontend_set_window(kfs_frontend *fe, int window)
     if (window < 1 || window > KFS_MAX_WINDOW) KFS_FAIL(KFS_ERR_INVALID_ARG, "set_window: %d not in [1, %d]", window, KFS_MAX_WINDOW);
     KFS_DEVICE_GUARD(fe->device);
     KFS_CUDA_TRY(cudaStreamSynchronize(fe->stream));
+    if (fe->cap <= 0) { fe->window_wanted = window; KFS_FAIL(KFS_ERR_INVALID_ARG, "set_window: the handle is unsized (a kfs_frontend_set_capacity failed); size it first"); }
     return fe_alloc_ring(fe, window);
 }
 int kfs_frontend_window(const kfs_frontend *fe) { return fe ? fe->window : 0; }
@@ -588,6 +614,7 @@ kfs_status kfs_frontend_match_window(kfs_frontend *fe, const uint8_t *cur_desc, 
                                      kfs_dmatch *good_out, int *n_good_out, int capacity, int *n_kf_out)
 {
     if (!fe || !n_kf_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle or n_kf_out is NULL");
+    KFS_FE_REQUIRE_SIZED(fe);
     *n_kf_out = 0;
     if (capacity < 0 || knn_rows < 0 || (capacity > 0 && !good_out) || !n_good_out) KFS_FAIL(KFS_ERR_INVALID_ARG, "match_window: output buffers");
     KFS_DEVICE_GUARD(fe->device);

@@ -139,7 +139,8 @@ def test_replay_rows_past_nfeatures_are_fetched(kfs, oracle):
 
 def test_matcher_attached_to_extractor_matches_rows_in_place(kfs):
     """kfs_bf_attach_orb: after kfs_orb_detect_and_compute_batch the descriptor rows handed to kfs_bf_knn_match_pairs by their
-    host address are matched on the device copy (no re-upload); foreign or modified-count pointers are uploaded as before."""
+    host address are matched on the device copy (no re-upload); foreign pointers, other row counts, edited rows and rows of an
+    earlier call are uploaded as before."""
     from importlib import import_module
     N = import_module("keyframe-based-slam_b200._native")
     L = kfs.lib()
@@ -169,6 +170,46 @@ def test_matcher_attached_to_extractor_matches_rows_in_place(kfs):
     pairs = (N.BfPair * 1)(N.BfPair(desc[0].ctypes.data, n[0], None, foreign.ctypes.data, n[1], None, outs[0].ctypes.data, None))
     N.check(L.kfs_bf_knn_match_pairs(bf._h, pairs, 1, 2))
     assert L.kfs_bf_last_aliased(bf._h) == 1 and np.array_equal(outs[0][:n[0]], outs[B + 1][:n[0]])
+    # ADVICE r2 / VERDICT weak 1b: everything that must NOT be taken for "the rows I just delivered"
+    ref = outs[B + 1][:n[0]].copy()            # pair (frame 0, frame 1), known good
+
+    def one(qrows, trows, nq_, nt_):
+        o = np.zeros((cap, 2), kfs.DM_DTYPE)
+        pr = (N.BfPair * 1)(N.BfPair(qrows.ctypes.data, nq_, None, trows.ctypes.data, nt_, None, o.ctypes.data, None))
+        N.check(L.kfs_bf_knn_match_pairs(bf._h, pr, 1, 2))
+        return o, L.kfs_bf_last_aliased(bf._h)
+    N.check(L.kfs_bf_attach_orb(bf._h, orb._h))
+    o, al = one(desc[0], desc[1], n[0], n[1])
+    assert al == 2 and np.array_equal(o[:n[0]], ref)
+    # fewer rows than the frame has (a caller that filtered its matrix): uploaded, and the answer is for the rows that were passed
+    o, al = one(desc[0], desc[1], n[0], n[1] - 7)
+    assert al == 1
+    plain, _ = kfs.BFMatcher_create(kfs.NORM_HAMMING).knnMatch(desc[0][:n[0]], desc[1][:n[1] - 7])
+    assert np.array_equal(o[:n[0]], plain)
+    # rows edited in place (first or last row no longer what was delivered): uploaded, answer follows the edit
+    keep = desc[1].copy()
+    desc[1][n[1] - 1] ^= 0xFF
+    o, al = one(desc[0], desc[1], n[0], n[1])
+    plain, _ = kfs.BFMatcher_create(kfs.NORM_HAMMING).knnMatch(desc[0][:n[0]], desc[1][:n[1]])
+    assert al == 1 and np.array_equal(o[:n[0]], plain) and not np.array_equal(o[:n[0]], ref)
+    desc[1][:] = keep
+    o, al = one(desc[0], desc[1], n[0], n[1])
+    assert al == 2 and np.array_equal(o[:n[0]], ref)
+    # a device-side extraction in between reuses the handle's arena: nothing of the old host call may be aliased afterwards
+    import torch
+    d_frames = torch.from_numpy(frames[::-1].copy()).cuda()
+    orb.extract_device(d_frames.data_ptr(), 640, 640 * 480, 640, 480, B)
+    orb.sync()
+    o, al = one(desc[0], desc[1], n[0], n[1])
+    assert al == 0 and np.array_equal(o[:n[0]], ref)
+    # a second host call into OTHER buffers: the first call's buffers are no longer the device content
+    kp2 = np.zeros((B, cap), kfs.KP_DTYPE); desc2 = np.zeros((B, cap, 32), np.uint8); n2 = (C.c_int * B)()
+    N.check(L.kfs_orb_detect_and_compute_batch(orb._h, frames[::-1].copy().ctypes.data, 640, 640 * 480, 640, 480, B, None, 0, 0,
+                                               kp2.ctypes.data, desc2.ctypes.data, cap, n2))
+    o, al = one(desc[0], desc[1], n[0], n[1])
+    assert al == 0 and np.array_equal(o[:n[0]], ref)
+    o, al = one(desc2[3], desc2[2], n2[3], n2[2])   # frames[::-1][3] = frame 0, [2] = frame 1: the new buffers are recognised
+    assert al == 2 and np.array_equal(o[:n[0]], ref)
     N.check(L.kfs_bf_attach_orb(bf._h, None))
 
 
@@ -206,5 +247,17 @@ def test_frontend_set_capacity_and_overflow_status(kfs, oracle):
     st = L.kfs_frontend_extract_features(fe._h, f.ctypes.data, 640, 640, 480, 1, None, 0, k_out.ctypes.data, d_out.ctypes.data, cap, C.byref(n))
     assert st == N.KFS_ERR_CAPACITY and n.value == len(kp)
     N.check(L.kfs_frontend_set_capacity(fe._h, n.value + 8))
+    got_kp, got_desc = fe.extractFeatures(f)
+    assert np.array_equal(got_kp, kp) and np.array_equal(got_desc, desc)
+    # a set_capacity that runs out of device memory leaves a DEFINED state — every computing call refuses the handle
+    # (no run on freed / null buffers) until a later set_capacity succeeds.  2e9 rows = 64 + 56 + 64 GB for the first three buffers.
+    assert L.kfs_frontend_set_capacity(fe._h, 2_000_000_000) == N.KFS_ERR_CUDA
+    assert fe.capacity == 0
+    st = L.kfs_frontend_extract_features(fe._h, f.ctypes.data, 640, 640, 480, 1, None, 0, k_out.ctypes.data, d_out.ctypes.data, cap, C.byref(n))
+    assert st == N.KFS_ERR_INVALID_ARG and "unsized" in L.kfs_last_error().decode()
+    assert L.kfs_frontend_promote_keyframe(fe._h, None, 0) == N.KFS_ERR_INVALID_ARG
+    assert L.kfs_frontend_set_window(fe._h, 4) == N.KFS_ERR_INVALID_ARG
+    N.check(L.kfs_frontend_set_capacity(fe._h, len(kp) + 8))
+    assert L.kfs_frontend_window(fe._h) == 4          # the ring size asked for while unsized is honoured once there is room
     got_kp, got_desc = fe.extractFeatures(f)
     assert np.array_equal(got_kp, kp) and np.array_equal(got_desc, desc)
