@@ -13,12 +13,14 @@
 // is (re)created as n x 32 CV_8U or released when n == 0; knnMatch rows hold min(k, Nt) DMatch entries.
 // Keypoint order: ascending octave, then (y, x) inside an octave (OpenCV leaves the in-level order unspecified).
 #pragma once
-#if __has_include(<opencv2/core.hpp>) && !defined(KFS_FORCE_CV_MOCK)
+#if __has_include(<opencv2/core.hpp>) && !defined(KFS_FORCE_CV_MOCK) && !defined(KFS_CV_MOCK)
 #include <opencv2/core.hpp>
 #define KFS_HAVE_OPENCV 1
-#else
+#elif defined(KFS_CV_MOCK) || defined(KFS_FORCE_CV_MOCK)
 #include "kfslam_cv_mock.hpp" // test scaffolding (tests/cpp/, add -I tests/cpp): stand-ins for the OpenCV types when its headers are absent
 #define KFS_HAVE_OPENCV 0
+#else
+#error "kfslam_frontend_cv.hpp needs the OpenCV headers (<opencv2/core.hpp> not found). This repository's own tests build against stand-in types: add -I tests/cpp -DKFS_CV_MOCK"
 #endif
 #include "kfslam_frontend.h"
 #include <cstring>
@@ -48,11 +50,17 @@ inline void make_desc(cv::OutputArray d, int n) { if (n) d.create(n, 32, CV_8U);
 inline cv::Mat out_mat(cv::OutputArray d) { return d.getMat(); }
 // keep the first n rows of a matrix created with more, WITHOUT moving them (the matcher recognises the rows by their address)
 inline void shrink_desc(cv::OutputArray d, int n) { if (n) { cv::Mat m = d.getMat(); d.getMatRef() = m.rowRange(0, n); } else d.release(); }
+// getMatRef() is defined for a plain cv::Mat output only; cv::UMat, std::vector<uchar>, cv::Mat_<uchar> ... (all of which cv::ORB
+// accepts) get their rows through a staging matrix and copyTo instead, and are then simply never matched in place
+inline bool desc_in_place(cv::OutputArray d) { return d.kind() == cv::_InputArray::MAT; }
+inline void copy_desc(const cv::Mat &stage, int n, cv::OutputArray d) { if (n) stage.rowRange(0, n).copyTo(d); else d.release(); }
 #else
 inline const cv::Mat &as_mat(cv::InputArray a) { return a; }
 inline void make_desc(cv::OutputArray d, int n) { if (n) d.create(n, 32, cv::CV_8U); else d.release(); }
 inline cv::Mat &out_mat(cv::OutputArray d) { return d; }
 inline void shrink_desc(cv::OutputArray d, int n) { if (n) d.rows = n; else d.release(); }
+inline bool desc_in_place(cv::OutputArray) { return true; }
+inline void copy_desc(const cv::Mat &, int, cv::OutputArray) {}
 #endif
 } // namespace detail
 
@@ -97,20 +105,32 @@ public:
             // in place afterwards): no staging copy, and an attached kfs::BFMatcher finds the rows it is handed next
             // (knnMatch(keyframe, dpCurrImg), VisualOdometry.cpp:39) still on the device by their host address
             keypoints.resize((size_t)cap);
-            detail::make_desc(descriptors, cap);
-            auto d = detail::out_mat(descriptors);
+            const bool in_place = detail::desc_in_place(descriptors);
+            cv::Mat stage;
+            if (in_place) detail::make_desc(descriptors, cap);
+            else detail::make_desc(stage, cap);
+            auto d = in_place ? detail::out_mat(descriptors) : stage;
             int n = 0;
             const kfs_status st = kfs_orb_detect_and_compute(h_, img.ptr(0), (size_t)img.step, img.cols, img.rows,
                                                              msk.empty() ? nullptr : msk.ptr(0), msk.empty() ? 0 : (size_t)msk.step,
                                                              reinterpret_cast<kfs_keypoint *>(keypoints.data()), d.ptr(0), cap, &n);
             if (st == KFS_ERR_CAPACITY) { // ties pushed the count over the handle's slack: grow and redo
-                if (kfs_orb_set_capacity(h_, n + 64) != KFS_OK) detail::raise(KFS_ERR_CUDA, "kfs::ORB::detectAndCompute");
+                if (kfs_orb_set_capacity(h_, n + 64) != KFS_OK) {
+                    keypoints.clear();
+                    detail::make_desc(descriptors, 0);
+                    detail::raise(KFS_ERR_CUDA, "kfs::ORB::detectAndCompute");
+                }
                 cap = kfs_orb_capacity(h_);
                 continue;
             }
-            if (st != KFS_OK) detail::raise(st, "kfs::ORB::detectAndCompute");
+            if (st != KFS_OK) { // leave the outputs empty, not `cap` rows of whatever the buffers held
+                keypoints.clear();
+                detail::make_desc(descriptors, 0);
+                detail::raise(st, "kfs::ORB::detectAndCompute");
+            }
             keypoints.resize((size_t)n);
-            detail::shrink_desc(descriptors, n);
+            if (in_place) detail::shrink_desc(descriptors, n);
+            else detail::copy_desc(stage, n, descriptors);
             return;
         }
     }

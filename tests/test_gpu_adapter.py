@@ -17,7 +17,7 @@ def _build():
     exe = os.path.join(ROOT, "tests", "cpp", "adapter_test")
     src = os.path.join(ROOT, "tests", "cpp", "adapter_test.cpp")
     lib = os.path.join(ROOT, "keyframe-based-slam_b200")
-    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "tests", "cpp"), src, "-L", lib, "-lkfslam_frontend",
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "tests", "cpp"), "-DKFS_CV_MOCK", src, "-L", lib, "-lkfslam_frontend",
                            "-Wl,-rpath," + lib, "-o", exe])
     return exe
 
