@@ -35,7 +35,7 @@ if os.path.exists(rep):
             "sm__throughput.avg.pct_of_peak_sustained_elapsed", "smsp__issue_active.avg.pct_of_peak_sustained_active",
             "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
             "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
-            "smsp__inst_executed.sum",
+            "smsp__inst_executed.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
             "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
             "lts__t_sector_hit_rate.pct"]
     idx = [(w, hdr.index(w)) for w in want if w in hdr]
@@ -68,12 +68,13 @@ if os.path.exists(rep):
                 mul = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(units[hdr.index("dram__bytes_read.sum")], 1)
                 mulw = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(units[hdr.index("dram__bytes_write.sum")], 1)
                 traffic[n] = int(rd * mul + wr * mulw)
-                if n == "k_resize" and len(rs) >= 7:   # the pyramid stage = the 7 per-level launches of one batch
+                if n in ("k_resize", "k_resize_tma") and len(rs) >= 7:   # the pyramid stage = the 7 per-level launches of one batch
                     traffic[n] = int(sum(float(q[hdr.index("dram__bytes_read.sum")]) * mul + float(q[hdr.index("dram__bytes_write.sum")]) * mulw for q in rs[:7]))
-                    traffic["k_resize_launches_summed"] = 7
+                    traffic[n + "_launches_summed"] = 7
             except Exception:
                 pass
     traffic["frames_per_launch"] = int(os.environ.get("KFS_NCU_FRAMES", "128"))
+    traffic["source"] = "profiles/%s_kernels.md (ncu --set full of that build, not of the bench run that quotes it)" % tag
     json.dump(traffic, open(os.path.join(out_dir, "ncu_traffic.json"), "w"), indent=1)
     json.dump(issue, open(os.path.join(out_dir, "ncu_issue.json"), "w"), indent=1)
     print(open(os.path.join(out_dir, tag + "_kernels.md")).read()[:3000])
