@@ -8,6 +8,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -s 14 -c 60 --csv --lo
     python tools/ncu_step.py 4 > gpurun_out/${tag}_ncu1.log 2>&1
 echo "launch list rc=$?"
 python tools/ncu_step.py 2 > gpurun_out/${tag}_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:k_ -s 29 -c 15 -f -o gpurun_out/${tag}_prof \
+ncu --set full --clock-control none --import-source on -k regex:k_ -s 27 -c 14 -f -o gpurun_out/${tag}_prof \
     python tools/ncu_step.py 2 > gpurun_out/${tag}_ncu2.log 2>&1
 echo "full capture rc=$?"; tail -3 gpurun_out/${tag}_ncu2.log; ls -la gpurun_out/
