@@ -594,8 +594,11 @@ def run_ours(args):
 
     # the matcher is attached to the extractor (kfs_bf_attach_orb): descriptor rows the ORB call just delivered are matched where
     # they still are on the device instead of being uploaded again; a plain (detached) pass is timed beside it
+    io = {"kp": kp_h, "desc": desc_h, "match": match_h, "src": None}   # swapped for pageable arrays by the `pageable` pass below
+
     def e2e_step(s):
-        src = pinned[s % nrot].numpy()
+        src = io["src"] if io["src"] is not None else pinned[s % nrot].numpy()
+        kp_h, desc_h, match_h = io["kp"], io["desc"], io["match"]
         ta = time.perf_counter()
         N.check(L.kfs_orb_detect_and_compute_batch(orb._h, src.ctypes.data, W, W * H, W, H, B, None, 0, 0,
                                                    kp_h.ctypes.data, desc_h.ctypes.data, cap, n_h))
@@ -640,8 +643,21 @@ def run_ours(args):
     Ke = max(1, min(K, args.e2e_steps))
     plain_value, _, plain_h2d, _, _, plain_knn_ms = dropin_pass(False, 0.15)
     dropin_value, Kd, h2d, d2h, orb_ms, knn_ms_call = dropin_pass(True, max(0.15, args.e2e_seconds / 2))
+    # the same two calls on PAGEABLE buffers (plain allocations: what cv::Mat clones and std::vector outputs are in the unmodified tracker,
+    # main.cpp:34, VisualOdometry.cpp:21-39): the copies are staged by the driver and no longer overlap the kernels
+    pageable = None
+    try:
+        io.update(kp=np.empty((B, cap, 28), np.uint8), desc=np.empty((B, cap, 32), np.uint8), match=np.empty((B, cap, 2, 16), np.uint8),
+                  src=np.array(pinned[0].numpy()))
+        pg_value, pg_n, _, _, pg_orb_ms, pg_knn_ms = dropin_pass(True, 0.3)
+        pageable = {"value": round(pg_value, 1), "steps": pg_n, "ms_per_step_orb_call": round(pg_orb_ms, 3), "ms_per_step_knn_call": round(pg_knn_ms, 3),
+                    "vs_pinned": round(pg_value / dropin_value, 3),
+                    "note": "every host buffer pageable (numpy allocations), same frames every step; INTEGRATION.md section 1 says how a tracker pins its cv::Mat buffers"}
+    except Exception as ex:
+        pageable = {"error": str(ex)[:200]}
+    io.update(kp=kp_h, desc=desc_h, match=match_h, src=None)
     N.check(L.kfs_bf_attach_orb(bf._h, None))
-    dropin = {"value": round(dropin_value, 1), "unit": "frames/s", "steps": Kd, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+    dropin = {"value": round(dropin_value, 1), "pageable": pageable, "unit": "frames/s", "steps": Kd, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
               "api": "kfs_orb_detect_and_compute_batch + kfs_bf_knn_match_pairs (the two drop-in calls, each blocking) on pinned host buffers, the matcher "
                      "attached to the extractor (kfs_bf_attach_orb: rows just extracted are matched on the device, not uploaded again)",
               "ms_per_step_orb_call": round(orb_ms, 3), "ms_per_step_knn_call": round(knn_ms_call, 3),
@@ -874,6 +890,67 @@ def run_ours(args):
     except Exception as ex:  # informative block: never lose the headline line to it
         cfg5 = {"error": str(ex)[:300]}
 
+    # ---- cfg4 (BASELINE.json configs[3]): the current 1280x720 frame against a sliding window of 10 local-BA keyframes
+    #      (Map::GetNKeyFrames, /root/reference/src/lib/Map.cpp:72-78): 2000 x (10 x 2000) Hamming kNN per frame + ratio 0.6, the 10 pairs
+    #      dealt over the ranks by replay.shard_pairs.  Same host API as cfg5, at every N (round 2 ran this shape on rank 0 only).
+    cfg4 = None
+    try:
+        WIN4, R4 = 10, 0.6
+        mine4 = RP.shard_pairs(WIN4, world, rank)
+        f4 = kfs.synth.make_stream(5, H, W, seed=400)
+        p4 = torch.empty((5, H, W), dtype=torch.uint8).pin_memory()
+        p4.numpy()[...] = f4
+        fe4 = C.c_void_p()
+        par4 = N.OrbParams()
+        L.kfs_orb_default_params(C.byref(par4))
+        par4.nfeatures = NF
+        N.check(L.kfs_frontend_create(C.byref(par4), local_rank, C.byref(fe4)))
+        N.check(L.kfs_frontend_set_window(fe4, max(1, len(mine4))))
+        cap4 = L.kfs_frontend_capacity(fe4)
+        kp4 = torch.empty((cap4, 28), dtype=torch.uint8).pin_memory().numpy()
+        de4 = torch.empty((cap4, 32), dtype=torch.uint8).pin_memory().numpy()
+        good4 = torch.empty((max(1, len(mine4)), cap4, 16), dtype=torch.uint8).pin_memory().numpy()
+        depth4 = torch.full((H, W), 1500, dtype=torch.int16).pin_memory().numpy().view(np.uint16)
+        n4, nkf4 = C.c_int(), C.c_int()
+        ng4 = (C.c_int * N.KFS_MAX_WINDOW)()
+        rows4 = (C.c_int * N.KFS_MAX_WINDOW)()
+        src4 = p4.numpy()
+        for k_ in mine4:
+            N.check(L.kfs_frontend_extract_features(fe4, src4[1 + k_ % 4].ctypes.data, W, W, H, 1, None, 0, kp4.ctypes.data, de4.ctypes.data, cap4, C.byref(n4)))
+            N.check(L.kfs_frontend_promote_keyframe(fe4, depth4.ctypes.data, 2 * W))
+
+        def frame4():
+            N.check(L.kfs_frontend_extract_features(fe4, src4[0].ctypes.data, W, W, H, 1, None, 0, kp4.ctypes.data, de4.ctypes.data, cap4, C.byref(n4)))
+            if mine4:
+                N.check(L.kfs_frontend_match_window(fe4, None, 0, R4, rows4, None, 0, good4.ctypes.data, ng4, cap4, C.byref(nkf4)))
+        for _ in range(5):
+            frame4()
+        barrier()
+        n4f = args.cfg4_frames
+        t0 = time.perf_counter()
+        for _ in range(n4f):
+            frame4()
+        t_4 = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(t_4, op=dist.ReduceOp.MAX)
+        sec4 = float(t_4.item()) / n4f
+        cmp4 = float(sum(rows4[i] for i in range(nkf4.value)) * n4.value) if mine4 else 0.0
+        t_cmp4 = torch.tensor([cmp4], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(t_cmp4, op=dist.ReduceOp.SUM)
+        cfg4 = {"workload": "cfg4: %dx%d frame, nf=%d, k=2 + ratio %.2f vs a %d-keyframe window (2000 x 20000 per frame), pairs dealt by replay.shard_pairs "
+                            "over %d rank(s)" % (W, H, NF, R4, WIN4, world),
+                "frames_per_s": round(1.0 / sec4, 1), "us_per_frame": round(sec4 * 1e6, 1), "pairs_per_rank": len(mine4), "frames_timed": n4f,
+                "keypoints": int(n4.value), "survivors_per_pair_rank0": [int(ng4[i]) for i in range(min(nkf4.value, 4))],
+                "gcmp_s_e2e": round(float(t_cmp4.item()) / sec4 / 1e9, 1), "scaling": "strong",
+                "api": "kfs_frontend_extract_features + kfs_frontend_match_window per frame, blocking, pinned host frame in, keypoints + descriptors + "
+                       "survivors out; wall clock, max over ranks; every rank extracts the frame itself (the device-only rate of this shape is "
+                       "window_matching)"}
+        L.kfs_frontend_destroy(fe4)
+        del p4
+    except Exception as ex:  # informative block: never lose the headline line to it
+        cfg4 = {"error": str(ex)[:300]}
+
     if rank != 0:
         if dist is not None:
             dist.barrier()
@@ -984,7 +1061,36 @@ def run_ours(args):
         for i in range(nh):
             track1(i)
         track_us = (time.perf_counter() - t0) / nh * 1e6
+        # the same two variants on PAGEABLE memory: what the unmodified tracker hands over (cv::Mat clones, main.cpp:34; std::vector /
+        # cv::Mat outputs, VisualOdometry.cpp:22-23,38) — plain numpy allocations here, inputs and every output
+        pg_src = np.array(src[:KF_EVERY + 1])
+        pg_kp, pg_desc, pg_m = np.empty((fcap, 28), np.uint8), np.empty((fcap, 32), np.uint8), np.empty((fcap, 16), np.uint8)
+        pg_p3, pg_p2 = np.empty((fcap, 3), np.float64), np.empty((fcap, 2), np.float64)
+        pg_depth = np.array(depth_h)
+
+        def track_pg(i):
+            N.check(L.kfs_frontend_extract_features(fe, pg_src[i % (KF_EVERY + 1)].ctypes.data, W, W, H, 1, None, 0, pg_kp.ctypes.data, pg_desc.ctypes.data, fcap, C.byref(fn)))
+            if i % KF_EVERY == 0:
+                N.check(L.kfs_frontend_promote_keyframe(fe, pg_depth.ctypes.data, 2 * W))
+            N.check(L.kfs_frontend_match_features(fe, None, None, 0, intr, 0.6, pg_m.ctypes.data, pg_p3.ctypes.data, pg_p2.ctypes.data, fcap, C.byref(fg)))
+
+        def track1_pg(i):
+            N.check(L.kfs_frontend_track(fe, pg_src[i % (KF_EVERY + 1)].ctypes.data, W, W, H, 1, None, 0, intr, 0.6, pg_kp.ctypes.data, pg_desc.ctypes.data, fcap,
+                                         C.byref(fn), pg_m.ctypes.data, pg_p3.ctypes.data, pg_p2.ctypes.data, fcap, C.byref(fm)))
+            if i % KF_EVERY == 0:
+                N.check(L.kfs_frontend_promote_keyframe(fe, pg_depth.ctypes.data, 2 * W))
+        pg = {}
+        for name_, fn_ in (("host_api_pageable_frame_us", track_pg), ("host_api_pageable_track_call_us", track1_pg)):
+            for i in range(5):
+                fn_(i)
+            t0 = time.perf_counter()
+            for i in range(nh):
+                fn_(i)
+            pg[name_] = round((time.perf_counter() - t0) / nh * 1e6, 1)
         if lat is not None and "error" not in lat:
+            lat.update(pg)
+            lat["host_api_pageable"] = ("the same calls with every host buffer pageable (plain allocations, as the unmodified tracker's cv::Mat clones and "
+                                        "std::vector outputs are); ratio to pinned: %.2fx per kfs_frontend_track call" % (pg["host_api_pageable_track_call_us"] / track_us))
             lat["host_api_track_call_us"] = round(track_us, 1)
             lat["host_api_track_frames_per_s"] = round(1e6 / track_us, 1)
             lat["host_api_frame_us"] = round(host_us, 1)
@@ -1232,7 +1338,7 @@ def run_ours(args):
                     "drop_in_calls": dropin},
             "gpu_launches": int(launches),
             "roofline": roofline, "roofline_popc": roofline_popc, "kernels": kernels, "stream_latency": lat,
-            "window_matching": win, "cfg3": cfg3, "cfg5": cfg5, "reference_setting": refset, "sustain": sustain,
+            "window_matching": win, "cfg3": cfg3, "cfg4": cfg4, "cfg5": cfg5, "reference_setting": refset, "sustain": sustain,
             "cpu_baseline": cpu}
     emit_line(line)
     if dist is not None:
@@ -1300,6 +1406,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-seconds", type=float, default=0.6, help="minimum wall-clock length of the end-to-end timed region")
     ap.add_argument("--arenas", type=int, default=0, help="batches in flight in the replay executor (0 = library default)")
+    ap.add_argument("--cfg4-frames", type=int, default=300, help="frames of the sharded window-matching leg (BASELINE.json configs[3])")
     ap.add_argument("--cfg3-frames", type=int, default=10000, help="length of the sharded sequence replay (BASELINE.json configs[2])")
     ap.add_argument("--cfg5-frames", type=int, default=12, help="4K frames timed against the 32-keyframe window (configs[4])")
     ap.add_argument("--sustain", type=float, default=1.0, help="also run the resident step loop for this many seconds (clocks sampled every 20 ms)")

@@ -318,6 +318,10 @@ KFS_API int kfs_frontend_capacity(const kfs_frontend *fe);   /* rows kp_out / de
  * keypoints).  Drops the cached keyframes and the current frame.  A frame that overflows makes
  * extract_features / track return KFS_ERR_CAPACITY with *n_out = the rows it needs (cv::ORB would have returned them all). */
 KFS_API kfs_status kfs_frontend_set_capacity(kfs_frontend *fe, int capacity);
+/* kfs_orb_set_blur_fma for the tracker handle's extractor: 1 = OpenCV's default AVX2 / AVX-512 blur (fused
+ * multiply-adds, the default), 0 = the multiply-then-add build.  A tracker built against an OpenCV without FMA dispatch sets 0 to
+ * keep bit-identical descriptors.  Cached keyframes stay valid (they were described with the variant of their time). */
+KFS_API kfs_status kfs_frontend_set_blur_fma(kfs_frontend *fe, int fma);
 
 /* ExtractFeatures(rgb, mask): image = h rows of w pixels x `channels` bytes (1 = already gray, 3 = R,G,B byte order as the
  * reference receives it), rows `step` bytes apart, host memory.  Gray = (R*9798 + G*19235 + B*3735 + 16384) >> 15, which

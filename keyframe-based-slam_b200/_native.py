@@ -108,6 +108,7 @@ SIGNATURES = {
     "kfs_frontend_destroy": (None, [_vp]),
     "kfs_frontend_capacity": (_i, [_vp]),
     "kfs_frontend_set_capacity": (_i, [_vp, _i]),
+    "kfs_frontend_set_blur_fma": (_i, [_vp, _i]),
     "kfs_frontend_extract_features": (_i, [_vp, _vp, _sz, _i, _i, _i, _vp, _sz, _vp, _vp, _i, _ip]),
     "kfs_frontend_promote_keyframe": (_i, [_vp, _vp, _sz]),
     "kfs_frontend_set_keyframe": (_i, [_vp, _vp, _vp, _i, _vp, _sz, _i, _i]),

@@ -346,6 +346,11 @@ kfs_status kfs_frontend_set_capacity(kfs_frontend *fe, int capacity)
     if (s) { fe->window_wanted = window; fe_unsize(fe); return s; } // the error text of the failing step stays in kfs_last_error()
     return KFS_OK;
 }
+kfs_status kfs_frontend_set_blur_fma(kfs_frontend *fe, int fma)
+{
+    if (!fe) KFS_FAIL(KFS_ERR_INVALID_ARG, "handle is NULL");
+    return kfs_orb_set_blur_fma(fe->orb, fma);
+}
 int kfs_frontend_last_launches(const kfs_frontend *fe) { return fe ? fe->launches : 0; }
 
 // Validates the frame, uploads it (+ mask), converts colour and runs the ORB chain; nothing synchronises.  On return the

@@ -451,6 +451,10 @@ class TrackerFrontEnd:
             return kp[:k].copy(), desc[:k].copy(), None, None, None
         return kp[:k].copy(), desc[:k].copy(), p3[:nm.value].copy(), p2[:nm.value].copy(), m[:nm.value].copy()
 
+    def set_blur_fma(self, fma):
+        """Blur variant of the extractor: True = OpenCV's FMA dispatch (default), False = multiply then add."""
+        N.check(N.lib().kfs_frontend_set_blur_fma(self._h, int(bool(fma))))
+
     # ---- keyframe window (Map::GetNKeyFrames, /root/reference/src/lib/Map.cpp:72-78) ----
     def setWindow(self, window):
         """Keep the last `window` keyframes on the device (drops the cached ones)."""

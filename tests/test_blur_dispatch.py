@@ -62,3 +62,22 @@ def test_gpu_blur_both_dispatches(oracle, capsys):
         assert which, "the local cv2 matches neither blur variant"
     except ImportError:
         pass
+
+
+@pytest.mark.gpu
+def test_gpu_tracker_handle_follows_blur_dispatch(oracle):
+    """kfs_frontend_set_blur_fma: the tracker handle's extractor can be switched like a plain kfs_orb, so a tracker built against an
+    OpenCV without FMA dispatch keeps bit-identical descriptors."""
+    import kfslam_b200 as kfs
+    img = synth.make_stream(1, 720, 1280, seed=100)[0]
+    P = oracle.orb_params(nfeatures=2000)
+    fe = kfs.TrackerFrontEnd(nfeatures=2000)
+    seen = {}
+    for fma in (True, False, True):
+        fe.set_blur_fma(fma)
+        kp, desc = fe.extractFeatures(img)
+        rk, rd = oracle.detect_and_compute(img, None, P, blur_fma=fma)
+        assert np.array_equal(kp, rk) and np.array_equal(desc, rd), fma
+        seen[fma] = desc
+    assert not np.array_equal(seen[True], seen[False])   # the frame was chosen so that the variants differ in some descriptor bit
+    fe.close()

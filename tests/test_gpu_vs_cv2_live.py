@@ -54,9 +54,8 @@ def test_live_720p_masked_nf3000_rgb(kfs, host_fma):
     rgb, mask = make_rgb(720, 1280, 52, shift=2), make_refset_mask(720, 1280, 53)
     gray = cv2.cvtColor(cv2.cvtColor(rgb, cv2.COLOR_RGB2BGR), cv2.COLOR_BGR2GRAY)
     rk, rd = cv_orb(gray, mask, 3000)
-    if not host_fma:
-        pytest.skip("this host's cv2 uses the non-FMA blur; the tracker front-end keeps the default FMA variant")
     fe = kfs.TrackerFrontEnd(nfeatures=3000)
+    fe.set_blur_fma(host_fma)          # the handle follows this host's cv2 (round 2 skipped the leg on a non-FMA host)
     kp, desc = fe.extractFeatures(rgb, mask)
     assert len(kp) == len(rk) and np.array_equal(kp, rk) and np.array_equal(desc, rd)
 
@@ -92,8 +91,7 @@ def test_live_window_cfg4_shape(kfs, host_fma):
     fe.setWindow(5)
     depth = np.full((720, 1280), 1000, np.uint16)
     descs = []
-    if not host_fma:
-        pytest.skip("this host's cv2 uses the non-FMA blur; the tracker front-end keeps the default FMA variant")
+    fe.set_blur_fma(host_fma)
     for f in frames[:6]:
         _, d = fe.extractFeatures(f)
         fe.promoteKeyframe(depth)
